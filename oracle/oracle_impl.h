@@ -1,0 +1,453 @@
+/*
+ * TEST INFRASTRUCTURE ONLY.  Precision-generic body of the CPU oracle; included twice by
+ * oracle.c (once real: T=double, P(x)=orc_d##x ; once complex: T=double _Complex,
+ * P(x)=orc_z##x, ORC_COMPLEX defined).  Plain C loops, no BLAS: every routine restates
+ * the arithmetic the reference obtains from CBLAS/LAPACKE at the cited call site.
+ * (The reference generates its s/d/c precisions from the z source the same way:
+ * tools/PrecisionGenerator/subs.py:22,41-43.)
+ */
+
+/* ---------------- generators (src/cores/core_zplgsy.c:72-150, core_zplghe.c:72-154,
+ * core_zplrnt.c:68-91): element k of the LCG stream is the matrix entry with
+ * column-major linear index k = i + j*gM of the lower triangle; NBELEM states per entry. */
+static inline T P(rnd_elem)(uint64_t *ran, int conj_im)
+{
+    /* float arithmetic on purpose: `0.5f - ran * RndF_Mul` (core_zplgsy.c:89) */
+    float re = 0.5f - (float)(*ran) * ORC_RNDF_MUL;
+    *ran = ORC_RND64_A * (*ran) + ORC_RND64_C;
+#ifdef ORC_COMPLEX
+    float im = 0.5f - (float)(*ran) * ORC_RNDF_MUL;
+    *ran = ORC_RND64_A * (*ran) + ORC_RND64_C;
+    return conj_im ? (double)re - I * (double)im : (double)re + I * (double)im;
+#else
+    (void)conj_im;
+    return (double)re;
+#endif
+}
+
+/* d: CORE_dplgsy ; z: CORE_zplghe (hermitian: real diagonal, conj mirror) */
+void P(plgsy_tile)(double bump, int m, int n, T *A, int lda, int gM, int m0, int n0, uint64_t seed)
+{
+    uint64_t ran, jump = (uint64_t)m0 + (uint64_t)n0 * (uint64_t)gM;
+    if (m0 == n0) {
+        for (int j = 0; j < n; j++) {
+            ran = orc_rnd64_jump(ORC_NBELEM * jump, seed);
+            for (int i = j; i < m; i++) A[i + (size_t)j * lda] = P(rnd_elem)(&ran, 0);
+            jump += (uint64_t)gM + 1;
+        }
+        for (int j = 0; j < n; j++) {
+#ifdef ORC_COMPLEX
+            A[j + (size_t)j * lda] = creal(A[j + (size_t)j * lda]) + bump; /* core_zplghe.c:102-104 */
+#else
+            A[j + (size_t)j * lda] += bump;
+#endif
+            for (int i = 0; i < j; i++) A[i + (size_t)j * lda] = ORC_CONJ(A[j + (size_t)i * lda]);
+        }
+    } else if (m0 > n0) {
+        for (int j = 0; j < n; j++) {
+            ran = orc_rnd64_jump(ORC_NBELEM * jump, seed);
+            for (int i = 0; i < m; i++) A[i + (size_t)j * lda] = P(rnd_elem)(&ran, 0);
+            jump += (uint64_t)gM;
+        }
+    } else {
+        jump = (uint64_t)n0 + (uint64_t)m0 * (uint64_t)gM;
+        for (int i = 0; i < m; i++) {
+            ran = orc_rnd64_jump(ORC_NBELEM * jump, seed);
+            for (int j = 0; j < n; j++) A[i + (size_t)j * lda] = P(rnd_elem)(&ran, 1);
+            jump += (uint64_t)gM;
+        }
+    }
+}
+
+void P(plrnt_tile)(int m, int n, T *A, int lda, int gM, int m0, int n0, uint64_t seed)
+{
+    uint64_t ran, jump = (uint64_t)m0 + (uint64_t)n0 * (uint64_t)gM;
+    for (int j = 0; j < n; j++) {
+        ran = orc_rnd64_jump(ORC_NBELEM * jump, seed);
+        for (int i = 0; i < m; i++) A[i + (size_t)j * lda] = P(rnd_elem)(&ran, 0);
+        jump += (uint64_t)gM;
+    }
+}
+
+/* tile operator applied over the uplo part (src/zplgsy_wrapper.c:36-42 + parsec_apply) */
+void P(plgsy)(double bump, int uplo, int M, int N, int mb, int nb, T *A, int lda, uint64_t seed)
+{
+    int mt = (M + mb - 1) / mb, nt = (N + nb - 1) / nb;
+    for (int n = 0; n < nt; n++)
+        for (int m = 0; m < mt; m++) {
+            if (uplo == ORC_LOWER && m < n) continue;
+            if (uplo == ORC_UPPER && m > n) continue;
+            int tm = (m == mt - 1) ? M - m * mb : mb, tn = (n == nt - 1) ? N - n * nb : nb;
+            P(plgsy_tile)(bump, tm, tn, A + (size_t)m * mb + (size_t)n * nb * lda, lda, M, m * mb,
+                          n * nb, seed);
+        }
+}
+void P(plrnt)(int M, int N, int mb, int nb, T *A, int lda, uint64_t seed)
+{
+    int mt = (M + mb - 1) / mb, nt = (N + nb - 1) / nb;
+    for (int n = 0; n < nt; n++)
+        for (int m = 0; m < mt; m++) {
+            int tm = (m == mt - 1) ? M - m * mb : mb, tn = (n == nt - 1) ? N - n * nb : nb;
+            P(plrnt_tile)(tm, tn, A + (size_t)m * mb + (size_t)n * nb * lda, lda, M, m * mb, n * nb,
+                          seed);
+        }
+}
+
+/* ---------------- tile kernels ---------------- */
+/* CORE_zpotrf -> LAPACKE_zpotrf_work (src/cores/core_zpotrf.c:68-74).  Unblocked
+ * left-looking column Cholesky (the definition LAPACK's xPOTF2 implements); info = j+1 at
+ * the first non-positive (or NaN) pivot, factorization stops there. */
+void P(potrf_tile)(int uplo, int n, T *A, int lda, int *info)
+{
+    *info = 0;
+    for (int j = 0; j < n; j++) {
+        double d = creal(A[j + (size_t)j * lda]);
+        for (int k = 0; k < j; k++) {
+            T l = (uplo == ORC_LOWER) ? A[j + (size_t)k * lda] : A[k + (size_t)j * lda];
+            d -= creal(l * ORC_CONJ(l));
+        }
+        if (!(d > 0.0)) {
+            A[j + (size_t)j * lda] = d;
+            *info = j + 1;
+            return;
+        }
+        d = sqrt(d);
+        A[j + (size_t)j * lda] = d;
+        if (uplo == ORC_LOWER) {
+            for (int i = j + 1; i < n; i++) {
+                T s = A[i + (size_t)j * lda];
+                for (int k = 0; k < j; k++)
+                    s -= A[i + (size_t)k * lda] * ORC_CONJ(A[j + (size_t)k * lda]);
+                A[i + (size_t)j * lda] = s / d;
+            }
+        } else {
+            for (int i = j + 1; i < n; i++) { /* row j of U, columns i>j */
+                T s = A[j + (size_t)i * lda];
+                for (int k = 0; k < j; k++)
+                    s -= ORC_CONJ(A[k + (size_t)j * lda]) * A[k + (size_t)i * lda];
+                A[j + (size_t)i * lda] = s / d;
+            }
+        }
+    }
+}
+
+static inline T P(opA)(const T *A, int lda, int trans, int i, int j)
+{ /* element (i,j) of op(A) */
+    if (trans == ORC_NOTRANS) return A[i + (size_t)j * lda];
+    T v = A[j + (size_t)i * lda];
+    return (trans == ORC_CONJTRANS) ? ORC_CONJ(v) : v;
+}
+
+/* CORE_zgemm -> cblas_zgemm (src/cores/core_zgemm.c:90-103): C = alpha op(A) op(B) + beta C */
+void P(gemm_tile)(int ta, int tb, int m, int n, int k, T alpha, const T *A, int lda, const T *B,
+                  int ldb, T beta, T *C, int ldc)
+{
+    T *tmp = (T *)malloc((size_t)(m > 0 ? m : 1) * sizeof(T));
+    for (int j = 0; j < n; j++) {
+        for (int i = 0; i < m; i++) tmp[i] = 0;
+        if (ta == ORC_NOTRANS) { /* axpy form: unit stride down the column of A */
+            for (int l = 0; l < k; l++) {
+                T b = P(opA)(B, ldb, tb, l, j);
+                const T *a = A + (size_t)l * lda;
+                for (int i = 0; i < m; i++) tmp[i] += a[i] * b;
+            }
+        } else { /* dot form: unit stride along l in A */
+            for (int i = 0; i < m; i++) {
+                T s = 0;
+                for (int l = 0; l < k; l++) s += P(opA)(A, lda, ta, i, l) * P(opA)(B, ldb, tb, l, j);
+                tmp[i] = s;
+            }
+        }
+        for (int i = 0; i < m; i++)
+            C[i + (size_t)j * ldc] = alpha * tmp[i] + beta * C[i + (size_t)j * ldc];
+    }
+    free(tmp);
+}
+
+/* CORE_zherk -> cblas_zherk (src/cores/core_zherk.c:84-95); d: CORE_dsyrk.
+ * trans==NoTrans: C = alpha A A^H + beta C (A n x k); else C = alpha A^H A + beta C (A k x n).
+ * Only the uplo triangle is referenced/written; complex: imag of the diagonal forced to 0. */
+void P(herk_tile)(int uplo, int trans, int n, int k, double alpha, const T *A, int lda,
+                  double beta, T *C, int ldc)
+{
+    T *tmp = (T *)malloc((size_t)(n > 0 ? n : 1) * sizeof(T));
+    for (int j = 0; j < n; j++) {
+        int i0 = (uplo == ORC_LOWER) ? j : 0, i1 = (uplo == ORC_LOWER) ? n : j + 1;
+        for (int i = i0; i < i1; i++) tmp[i] = 0;
+        if (trans == ORC_NOTRANS) {
+            for (int l = 0; l < k; l++) {
+                T b = ORC_CONJ(A[j + (size_t)l * lda]);
+                const T *a = A + (size_t)l * lda;
+                for (int i = i0; i < i1; i++) tmp[i] += a[i] * b;
+            }
+        } else {
+            for (int i = i0; i < i1; i++) {
+                T s = 0;
+                for (int l = 0; l < k; l++)
+                    s += ORC_CONJ(A[l + (size_t)i * lda]) * A[l + (size_t)j * lda];
+                tmp[i] = s;
+            }
+        }
+        for (int i = i0; i < i1; i++) {
+            T v = alpha * tmp[i] + beta * C[i + (size_t)j * ldc];
+            C[i + (size_t)j * ldc] = (i == j) ? (T)creal(v) : v;
+        }
+    }
+    free(tmp);
+}
+
+/* CORE_ztrsm -> cblas_ztrsm (src/cores/core_ztrsm.c:80-93): solve op(A) X = alpha B
+ * (side Left) or X op(A) = alpha B (side Right), X overwrites B (m x n). */
+void P(trsm_tile)(int side, int uplo, int trans, int diag, int m, int n, T alpha, const T *A,
+                  int lda, T *B, int ldb)
+{
+    int na = (side == ORC_LEFT) ? m : n;
+    /* Is op(A) lower triangular? */
+    int lower = (uplo == ORC_LOWER) == (trans == ORC_NOTRANS);
+    for (int j = 0; j < n; j++)
+        for (int i = 0; i < m; i++) B[i + (size_t)j * ldb] *= alpha;
+    if (side == ORC_LEFT) {
+        for (int j = 0; j < n; j++) {
+            T *b = B + (size_t)j * ldb;
+            if (lower) {
+                for (int i = 0; i < na; i++) {
+                    T s = b[i];
+                    for (int l = 0; l < i; l++) s -= P(opA)(A, lda, trans, i, l) * b[l];
+                    b[i] = (diag == ORC_UNIT) ? s : s / P(opA)(A, lda, trans, i, i);
+                }
+            } else {
+                for (int i = na - 1; i >= 0; i--) {
+                    T s = b[i];
+                    for (int l = i + 1; l < na; l++) s -= P(opA)(A, lda, trans, i, l) * b[l];
+                    b[i] = (diag == ORC_UNIT) ? s : s / P(opA)(A, lda, trans, i, i);
+                }
+            }
+        }
+    } else { /* X op(A) = B: column j of X depends on columns l with op(A)(l,j) != 0 */
+        if (!lower) { /* op(A) upper: X(:,j) = (B(:,j) - sum_{l<j} X(:,l) opA(l,j)) / opA(j,j) */
+            for (int j = 0; j < na; j++) {
+                for (int l = 0; l < j; l++) {
+                    T a = P(opA)(A, lda, trans, l, j);
+                    for (int i = 0; i < m; i++) B[i + (size_t)j * ldb] -= B[i + (size_t)l * ldb] * a;
+                }
+                if (diag != ORC_UNIT) {
+                    T d = P(opA)(A, lda, trans, j, j);
+                    for (int i = 0; i < m; i++) B[i + (size_t)j * ldb] /= d;
+                }
+            }
+        } else {
+            for (int j = na - 1; j >= 0; j--) {
+                for (int l = j + 1; l < na; l++) {
+                    T a = P(opA)(A, lda, trans, l, j);
+                    for (int i = 0; i < m; i++) B[i + (size_t)j * ldb] -= B[i + (size_t)l * ldb] * a;
+                }
+                if (diag != ORC_UNIT) {
+                    T d = P(opA)(A, lda, trans, j, j);
+                    for (int i = 0; i < m; i++) B[i + (size_t)j * ldb] /= d;
+                }
+            }
+        }
+    }
+}
+
+/* ---------------- tiled Cholesky: the bodies of src/zpotrf_L.jdf:174-188,281-300,383-401,
+ * 514-535 (U: zpotrf_U.jdf) executed in the sequential insertion order of
+ * tests/testing_zpotrf_dtd.c:130-205, which is a topological order of the DAG. */
+int P(potrf)(int uplo, int N, int nb, T *A, int lda)
+{
+    int nt = (N + nb - 1) / nb, INFO = 0;
+#define TL(m, n) (A + (size_t)(m) * nb + (size_t)(n) * nb * (size_t)lda)
+#define TD(t) (((t) == nt - 1) ? N - (t) * nb : nb)
+    for (int k = 0; k < nt; k++) {
+        int iinfo = 0, tk = TD(k);
+        P(potrf_tile)(uplo, tk, TL(k, k), lda, &iinfo);
+        if (iinfo != 0 && INFO == 0) INFO = k * nb + iinfo; /* zpotrf_L.jdf:180-182 */
+        if (uplo == ORC_LOWER) {
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = k + 1; m < nt; m++)
+                P(trsm_tile)(ORC_RIGHT, ORC_LOWER, ORC_CONJTRANS, ORC_NONUNIT, TD(m), nb, 1.0,
+                             TL(k, k), lda, TL(m, k), lda);
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = k + 1; m < nt; m++) {
+                P(herk_tile)(ORC_LOWER, ORC_NOTRANS, TD(m), nb, -1.0, TL(m, k), lda, 1.0, TL(m, m),
+                             lda);
+                for (int n = k + 1; n < m; n++)
+                    P(gemm_tile)(ORC_NOTRANS, ORC_CONJTRANS, TD(m), nb, nb, -1.0, TL(m, k), lda,
+                                 TL(n, k), lda, 1.0, TL(m, n), lda);
+            }
+        } else {
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = k + 1; n < nt; n++)
+                P(trsm_tile)(ORC_LEFT, ORC_UPPER, ORC_CONJTRANS, ORC_NONUNIT, nb, TD(n), 1.0,
+                             TL(k, k), lda, TL(k, n), lda);
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = k + 1; n < nt; n++) {
+                P(herk_tile)(ORC_UPPER, ORC_CONJTRANS, TD(n), nb, -1.0, TL(k, n), lda, 1.0,
+                             TL(n, n), lda);
+                for (int m = k + 1; m < n; m++)
+                    P(gemm_tile)(ORC_CONJTRANS, ORC_NOTRANS, nb, TD(n), nb, -1.0, TL(k, m), lda,
+                                 TL(k, n), lda, 1.0, TL(m, n), lda);
+            }
+        }
+    }
+    return INFO;
+}
+
+/* ---------------- dplasma_ztrsm, Left side (src/ztrsm_wrapper.c:94-163 picks the DAG):
+ * LLN ztrsm_LLN.jdf:40-51,122-135 ; LLT ztrsm_LLT.jdf:40-51,123-136 ; LUN / LUT mirror.
+ * Returns the reference's argument-check codes (ztrsm_wrapper.c:274-296). */
+int P(trsm)(int side, int uplo, int trans, int diag, int M, int NRHS, int mb, int nbr, T alpha,
+            const T *A, int lda, T *B, int ldb)
+{
+    if (side != ORC_LEFT && side != ORC_RIGHT) return -1;
+    if (uplo != ORC_UPPER && uplo != ORC_LOWER) return -2;
+    if (trans != ORC_NOTRANS && trans != ORC_TRANS && trans != ORC_CONJTRANS) return -3;
+    if (diag != ORC_UNIT && diag != ORC_NONUNIT) return -4;
+    if (side != ORC_LEFT) return -1; /* oracle restates only the Left variants (posv path) */
+    int mt = (M + mb - 1) / mb, nt = (NRHS + nbr - 1) / nbr;
+    int forward = (uplo == ORC_LOWER) == (trans == ORC_NOTRANS);
+    for (int kk = 0; kk < mt; kk++) {
+        int k = forward ? kk : mt - 1 - kk;
+        int tk = (k == mt - 1) ? M - k * mb : mb;
+        T lalpha = (kk == 0) ? alpha : (T)1.0;
+        for (int n = 0; n < nt; n++) {
+            int tn = (n == nt - 1) ? NRHS - n * nbr : nbr;
+            P(trsm_tile)(ORC_LEFT, uplo, trans, diag, tk, tn, lalpha,
+                         A + (size_t)k * mb + (size_t)k * mb * lda, lda,
+                         B + (size_t)k * mb + (size_t)n * nbr * ldb, ldb);
+        }
+        int lo = forward ? k + 1 : 0, hi = forward ? mt : k;
+#pragma omp parallel for schedule(dynamic, 1)
+        for (int m = lo; m < hi; m++)
+            for (int n = 0; n < nt; n++) {
+                int tm = (m == mt - 1) ? M - m * mb : mb;
+                int tn = (n == nt - 1) ? NRHS - n * nbr : nbr;
+                const T *Bk = B + (size_t)k * mb + (size_t)n * nbr * ldb;
+                T *Bm = B + (size_t)m * mb + (size_t)n * nbr * ldb;
+                if (trans == ORC_NOTRANS)
+                    P(gemm_tile)(ORC_NOTRANS, ORC_NOTRANS, tm, tn, tk, -1.0,
+                                 A + (size_t)m * mb + (size_t)k * mb * lda, lda, Bk, ldb, lalpha, Bm,
+                                 ldb);
+                else
+                    P(gemm_tile)(trans, ORC_NOTRANS, tm, tn, tk, -1.0,
+                                 A + (size_t)k * mb + (size_t)m * mb * lda, lda, Bk, ldb, lalpha, Bm,
+                                 ldb);
+            }
+    }
+    return 0;
+}
+
+/* src/zpotrs_wrapper.c:58-98 */
+int P(potrs)(int uplo, int N, int NRHS, int nb, int nbr, const T *A, int lda, T *B, int ldb)
+{
+    if (uplo != ORC_UPPER && uplo != ORC_LOWER) return -1;
+    if (uplo == ORC_UPPER) {
+        P(trsm)(ORC_LEFT, uplo, ORC_CONJTRANS, ORC_NONUNIT, N, NRHS, nb, nbr, 1.0, A, lda, B, ldb);
+        P(trsm)(ORC_LEFT, uplo, ORC_NOTRANS, ORC_NONUNIT, N, NRHS, nb, nbr, 1.0, A, lda, B, ldb);
+    } else {
+        P(trsm)(ORC_LEFT, uplo, ORC_NOTRANS, ORC_NONUNIT, N, NRHS, nb, nbr, 1.0, A, lda, B, ldb);
+        P(trsm)(ORC_LEFT, uplo, ORC_CONJTRANS, ORC_NONUNIT, N, NRHS, nb, nbr, 1.0, A, lda, B, ldb);
+    }
+    return 0;
+}
+/* src/zposv_wrapper.c:64-114 */
+int P(posv)(int uplo, int N, int NRHS, int nb, int nbr, T *A, int lda, T *B, int ldb)
+{
+    if (uplo != ORC_UPPER && uplo != ORC_LOWER) return -1;
+    int info = P(potrf)(uplo, N, nb, A, lda);
+    if (info == 0) P(potrs)(uplo, N, NRHS, nb, nbr, A, lda, B, ldb);
+    return info;
+}
+
+/* ---------------- norms and checks (src/dplasma_zcheck.c) ---------------- */
+/* dplasma_zlanhe(InfNorm, uplo): max row sum of the hermitian matrix stored in uplo */
+double P(lanhe_inf)(int uplo, int N, const T *A, int lda)
+{
+    double *rs = (double *)calloc((size_t)N, sizeof(double)), r = 0.0;
+    for (int j = 0; j < N; j++) {
+        int i0 = (uplo == ORC_LOWER) ? j : 0, i1 = (uplo == ORC_LOWER) ? N : j + 1;
+        for (int i = i0; i < i1; i++) {
+            double a = (i == j) ? fabs(creal(A[i + (size_t)j * lda])) : ORC_ABS(A[i + (size_t)j * lda]);
+            rs[i] += a;
+            if (i != j) rs[j] += a;
+        }
+    }
+    for (int i = 0; i < N; i++) {
+        if (rs[i] > r || isnan(rs[i])) r = rs[i];
+    }
+    free(rs);
+    return r;
+}
+double P(lange_inf)(int M, int N, const T *A, int lda)
+{
+    double *rs = (double *)calloc((size_t)M, sizeof(double)), r = 0.0;
+    for (int j = 0; j < N; j++)
+        for (int i = 0; i < M; i++) rs[i] += ORC_ABS(A[i + (size_t)j * lda]);
+    for (int i = 0; i < M; i++)
+        if (rs[i] > r || isnan(rs[i])) r = rs[i];
+    free(rs);
+    return r;
+}
+
+/* check_zpotrf (src/dplasma_zcheck.c:64-134): R = L L^H - A0 on the uplo triangle (U^H U
+ * for Upper), result = ||R||_inf(hermitian) / (||A0||_inf N eps), eps = dlamch('e') = 2^-53;
+ * returns 1 ("suspicious") iff result is not finite or > 60. */
+int P(check_potrf)(int uplo, int N, const T *A, int lda, const T *A0, int lda0, double *result,
+                   double *Rnorm_out, double *Anorm_out)
+{
+    T *R = (T *)calloc((size_t)N * N, sizeof(T));
+#pragma omp parallel for schedule(dynamic, 8)
+    for (int j = 0; j < N; j++) {
+        int i0 = (uplo == ORC_LOWER) ? j : 0, i1 = (uplo == ORC_LOWER) ? N : j + 1;
+        for (int i = i0; i < i1; i++) {
+            T s = 0;
+            int kmax = (i < j ? i : j) + 1;
+            if (uplo == ORC_LOWER)
+                for (int k = 0; k < kmax; k++)
+                    s += A[i + (size_t)k * lda] * ORC_CONJ(A[j + (size_t)k * lda]);
+            else
+                for (int k = 0; k < kmax; k++)
+                    s += ORC_CONJ(A[k + (size_t)i * lda]) * A[k + (size_t)j * lda];
+            R[i + (size_t)j * N] = s - A0[i + (size_t)j * lda0];
+        }
+    }
+    double Anorm = P(lanhe_inf)(uplo, N, A0, lda0);
+    double Rnorm = P(lanhe_inf)(uplo, N, R, N);
+    double eps = 0x1.0p-53;
+    double res = Rnorm / (Anorm * N * eps);
+    free(R);
+    if (result) *result = res;
+    if (Rnorm_out) *Rnorm_out = Rnorm;
+    if (Anorm_out) *Anorm_out = Anorm;
+    return (isnan(Rnorm) || isinf(Rnorm) || isnan(res) || isinf(res) || res > 60.0) ? 1 : 0;
+}
+
+/* check_zaxmb (src/dplasma_zcheck.c:180-225): b <- b - A x (A hermitian, stored in uplo);
+ * result = ||b||_inf / ((||A|| ||x|| + ||b0||) N eps); b is overwritten like the reference. */
+int P(check_axmb)(int uplo, int N, int NRHS, const T *A, int lda, T *b, int ldb, const T *x,
+                  int ldx, double *result)
+{
+    double Anorm = P(lanhe_inf)(uplo, N, A, lda);
+    double Bnorm = P(lange_inf)(N, NRHS, b, ldb);
+    double Xnorm = P(lange_inf)(N, NRHS, x, ldx);
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int c = 0; c < NRHS; c++)
+        for (int i = 0; i < N; i++) {
+            T s = 0;
+            for (int j = 0; j < N; j++) {
+                T a;
+                if (i == j) a = (T)creal(A[i + (size_t)i * lda]);
+                else if ((uplo == ORC_LOWER) == (i > j)) a = A[i + (size_t)j * lda];
+                else a = ORC_CONJ(A[j + (size_t)i * lda]);
+                s += a * x[j + (size_t)c * ldx];
+            }
+            b[i + (size_t)c * ldb] -= s;
+        }
+    double Rnorm = P(lange_inf)(N, NRHS, b, ldb);
+    double eps = 0x1.0p-53;
+    double res = Rnorm / ((Anorm * Xnorm + Bnorm) * N * eps);
+    if (result) *result = res;
+    return (isnan(Xnorm) || isinf(Xnorm) || isnan(res) || isinf(res) || res > 60.0) ? 1 : 0;
+}
+#undef TL
+#undef TD
