@@ -1,0 +1,379 @@
+// FP64 tensor-core (DMMA) GEMM engine for sm_100a -- the dense contraction behind every
+// Level-3 step of the tiled Cholesky path.
+//
+// Replaces, inside the reference's task bodies, the per-tile library calls
+//   cublasDgemm  (src/zpotrf_L.jdf:463-468)   C(m,n) -= L(m,k) L(n,k)^T
+//   cublasDsyrk  (src/zpotrf_L.jdf:342-346)   C(m,m) -= L(m,k) L(m,k)^T   (lower part only)
+// and, through inverted diagonal blocks, cublasDtrsm (src/zpotrf_L.jdf:236-240).
+//
+// FP64 has no tcgen05 / TMEM kind on sm_100a: the FP64 tensor path is the warp-level
+// mma.sync.m8n8k4.f64 (SASS DMMA.8x8x4) with register accumulators.  The kernel is therefore
+// an Ampere-style register-tiled GEMM fed by a Blackwell-style pipeline: one producer warp
+// stages operand panels into shared memory with cp.async.bulk (SASS UBLKCP, the non-tensor
+// TMA path) completing on mbarriers; consumer warps wait on the full barrier, run DMMA from
+// conflict-free padded shared-memory rows, and release stages through empty barriers.
+//
+// Operand form is "NT": C[i][j] (+)= sum_k A[i][k] * B[j][k], A and B column-major with the
+// contraction index as the slow dimension (a column of A is contiguous) -- exactly the
+// layout of a column-major tile L(m,k).  "Kmajor" operands (rows of op(A) contiguous along k,
+// i.e. A^T stored column-major) are supported by a transposing producer for the upper /
+// solve variants.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dpb {
+
+// ---------------------------------------------------------------------------------------
+// Work description.  One launch covers either a single GEMM/SYRK, or the whole trailing
+// update of one factorization step over tile storage ("grouped" form of SURVEY 8(b) B2).
+// ---------------------------------------------------------------------------------------
+enum GemmMode : int { GEMM_SINGLE = 0, GEMM_TRAILING = 1 };
+static constexpr int kMaxCols = 160;  // max local tile columns in one trailing update
+
+struct GemmDesc {
+    int mode;
+    // common
+    double alpha, beta;  // C = beta*C + alpha*A*B^T
+    int K;               // contraction length
+    int fast;            // 1: 16B-aligned bulk-copy producer; 0: element-wise producer
+    int a_kmajor, b_kmajor;  // 0: operand stored M-major (NT form); 1: stored K-major
+    // K may span several tiles of a tile-row: element (i,kk) of A is at
+    //   A + (kk / kTile)*aKTileStride + (kk % kTile)*lda + i      (M-major)
+    int kTile;
+    long long aKTileStride, bKTileStride;
+    // ---- GEMM_SINGLE ----
+    const double* A;
+    const double* B;
+    double* C;
+    int M, N, lda, ldb, ldc;
+    int lower;   // 1: SYRK-like, touch only elements with (rowOff+i) >= (colOff+j); 2: only <=
+    int rowOff, colOff;
+    int gridM, gridN;
+    int batch;                // independent problems, strided; the last one may have fewer rows
+    long long batchStrideA, batchStrideB, batchStrideC;
+    int lastBatchM;
+    // ---- GEMM_TRAILING ----  (tile storage: tile (i,j) of the local array at
+    //      Cbase + (i + j*tileLdT)*tileElems, each tile column-major with ld = nb)
+    double* Cbase;
+    const double* rowPanel;   // tile for local tile-row i at rowPanel + i*rowPanelStride
+    const double* colPanel;   // tile for local tile-col j at colPanel + j*colPanelStride
+    long long rowPanelStride, colPanelStride, tileElems;
+    int tileLdT;              // local tile rows (stride between tile columns, in tiles)
+    int nb;                   // tile size
+    int bpt;                  // CTA blocks per tile edge = ceil(nb / BM)  (BM == BN)
+    int ncols;                // number of local tile columns in this update
+    int colFirst;             // first local tile column j0
+    int P, Q, prow, pcol;     // process grid and my coordinates: global m = i*P+prow, n = j*Q+pcol
+    int lastM, lastN;         // rows in the last global tile-row / cols in last tile-col (ragged edge)
+    int mtGlobal, ntGlobal;   // global tile counts
+    int rowFirst[kMaxCols];   // per column: first local tile row with global m >= global n
+    int rowEnd;               // local tile rows end (exclusive)
+    int itemStart[kMaxCols + 1];  // prefix sum of work items (CTA tiles) per column
+};
+
+// ---------------------------------------------------------------------------------------
+// PTX helpers
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 1-D bulk async copy global -> shared (TMA engine, SASS UBLKCP), completes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+// ---------------------------------------------------------------------------------------
+// Tile configuration
+// ---------------------------------------------------------------------------------------
+template <int BM_, int BN_, int WM_, int STAGES_>
+struct GemmCfg {
+    static constexpr int BM = BM_, BN = BN_, BK = 16, WM = WM_, WN = 32, STAGES = STAGES_;
+    static constexpr int MF = WM / 8, NF = WN / 8;  // 8x8 fragments per warp tile
+    static constexpr int WARPS_M = BM / WM, WARPS_N = BN / WN;
+    static constexpr int CONSUMER_WARPS = WARPS_M * WARPS_N;
+    static constexpr int THREADS = (CONSUMER_WARPS + 1) * 32;
+    // Padded shared-memory row strides (doubles), chosen so the fragment loads below are
+    // bank-conflict free: LDS.128 of 8 contiguous doubles/thread needs stride = 2 (mod 16);
+    // the paired 2+2 layout needs stride = 4 (mod 16).
+    static constexpr int LDA_S = (WM == 64) ? BM + 2 : BM + 4;
+    static constexpr int LDB_S = BN + 4;
+    static constexpr int A_STAGE = BK * LDA_S, B_STAGE = BK * LDB_S;  // doubles
+    static constexpr size_t SMEM = (size_t)STAGES * (A_STAGE + B_STAGE) * 8 + 2 * STAGES * 8 + 16;
+};
+using CfgBig = GemmCfg<128, 128, 64, 4>;   // 8 consumer warps, 64x32 warp tiles, 134 KB smem
+using CfgSmall = GemmCfg<64, 64, 32, 4>;   // 4 consumer warps, 32x32 warp tiles, 70 KB smem
+
+// row (within the warp tile) of fragment f, fragment-row g
+template <int WM>
+__device__ __forceinline__ int frag_row(int g, int f) {
+    if (WM == 64) return 8 * g + f;               // thread owns 8 contiguous rows
+    return 2 * g + (f & 1) + 16 * (f >> 1);       // thread owns 2+2 rows, 16 apart
+}
+// column (within the 32-wide warp tile) for B fragment f and fragment-col g
+__device__ __forceinline__ int frag_col(int g, int f) { return 2 * g + (f & 1) + 16 * (f >> 1); }
+
+struct BlockWork {
+    const double* A;
+    const double* B;
+    double* C;
+    int M, N;        // valid rows/cols in this CTA tile (<= BM/BN)
+    int lda, ldb, ldc;
+    int lower;       // mask: write only gi >= gj
+    int gi0, gj0;    // global (within-problem) offsets of this CTA tile for the mask
+    bool valid;
+};
+
+template <class Cfg>
+__device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
+    BlockWork w;
+    w.valid = true;
+    if (d.mode == GEMM_SINGLE) {
+        // CTA tiles enumerated column-block major so that consecutive CTAs share the B panel
+        const int per = d.gridM * d.gridN;
+        const int bt = bid / per, r = bid - bt * per;
+        int bj = r / d.gridM, bi = r - bj * d.gridM;
+        int i0 = bi * Cfg::BM, j0 = bj * Cfg::BN;
+        const int Mtot = (bt == d.batch - 1) ? d.lastBatchM : d.M;
+        w.M = min(Cfg::BM, Mtot - i0);
+        w.N = min(Cfg::BN, d.N - j0);
+        if (w.M <= 0 || w.N <= 0) { w.valid = false; return w; }
+        w.lda = d.lda; w.ldb = d.ldb; w.ldc = d.ldc;
+        const double* Ab = d.A + (size_t)bt * d.batchStrideA;
+        const double* Bb = d.B + (size_t)bt * d.batchStrideB;
+        w.A = d.a_kmajor ? Ab + (size_t)i0 * d.lda : Ab + i0;
+        w.B = d.b_kmajor ? Bb + (size_t)j0 * d.ldb : Bb + j0;
+        w.C = d.C + (size_t)bt * d.batchStrideC + i0 + (size_t)j0 * d.ldc;
+        w.lower = d.lower;
+        w.gi0 = d.rowOff + i0; w.gj0 = d.colOff + j0;
+        if (d.lower == 1 && (w.gi0 + w.M - 1 < w.gj0)) w.valid = false;  // entirely above diagonal
+        if (d.lower == 2 && (w.gj0 + w.N - 1 < w.gi0)) w.valid = false;  // entirely below diagonal
+        return w;
+    }
+    // GEMM_TRAILING: find the local tile column by binary search over the prefix array
+    int lo = 0, hi = d.ncols;
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (d.itemStart[mid] <= bid) lo = mid; else hi = mid;
+    }
+    int c = lo;
+    int r = bid - d.itemStart[c];
+    int j = d.colFirst + c;                 // local tile column
+    int rowsInCol = (d.rowEnd - d.rowFirst[c]) * d.bpt;   // CTA block-rows in this tile column
+    int bj = r / rowsInCol;                 // CTA block column inside the tile
+    int rr = r - bj * rowsInCol;
+    int i = d.rowFirst[c] + rr / d.bpt;     // local tile row
+    int bi = rr - (rr / d.bpt) * d.bpt;
+    int gm = i * d.P + d.prow, gn = j * d.Q + d.pcol;   // global tile coordinates
+    int tm = (gm == d.mtGlobal - 1) ? d.lastM : d.nb;
+    int tn = (gn == d.ntGlobal - 1) ? d.lastN : d.nb;
+    int i0 = bi * Cfg::BM, j0 = bj * Cfg::BN;
+    w.M = min(Cfg::BM, tm - i0);
+    w.N = min(Cfg::BN, tn - j0);
+    if (w.M <= 0 || w.N <= 0) { w.valid = false; return w; }
+    w.lda = w.ldb = w.ldc = d.nb;
+    w.A = d.rowPanel + (size_t)i * d.rowPanelStride + i0;
+    w.B = d.colPanel + (size_t)j * d.colPanelStride + j0;
+    w.C = d.Cbase + ((size_t)i + (size_t)j * d.tileLdT) * d.tileElems + i0 + (size_t)j0 * d.nb;
+    w.lower = (gm == gn);
+    w.gi0 = i0; w.gj0 = j0;
+    if (w.lower && (i0 + w.M - 1 < j0)) w.valid = false;
+    return w;
+}
+
+// ---------------------------------------------------------------------------------------
+// The kernel
+// ---------------------------------------------------------------------------------------
+template <class Cfg>
+__global__ void __launch_bounds__(Cfg::THREADS, 1) gemm_dmma_kernel(const __grid_constant__ GemmDesc d) {
+    constexpr int BM = Cfg::BM, BN = Cfg::BN, BK = Cfg::BK, STAGES = Cfg::STAGES;
+    constexpr int LDA_S = Cfg::LDA_S, LDB_S = Cfg::LDB_S, MF = Cfg::MF, NF = Cfg::NF;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double* sA = reinterpret_cast<double*>(smem_raw);
+    double* sB = sA + (size_t)STAGES * Cfg::A_STAGE;
+    uint64_t* full = reinterpret_cast<uint64_t*>(sB + (size_t)STAGES * Cfg::B_STAGE);
+    uint64_t* empty = full + STAGES;
+
+    const BlockWork w = decode_work<Cfg>(d, blockIdx.x);
+    if (!w.valid) return;  // uniform per CTA
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], Cfg::CONSUMER_WARPS);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int nChunks = (d.K + BK - 1) / BK;
+
+    if (warp == Cfg::CONSUMER_WARPS) {
+        // ============================ producer warp ============================
+        const bool fast = d.fast && !d.a_kmajor && !d.b_kmajor && !(w.M & 1) && !(w.N & 1);
+        for (int c = 0; c < nChunks; c++) {
+            const int s = c % STAGES;
+            const uint32_t ph = (c / STAGES) & 1;
+            if (c >= STAGES) mbar_wait(&empty[s], ph ^ 1);
+            double* dA = sA + (size_t)s * Cfg::A_STAGE;
+            double* dB = sB + (size_t)s * Cfg::B_STAGE;
+            const int kk0 = c * BK;
+            const int kt = kk0 / d.kTile, kin = kk0 - kt * d.kTile;
+            if (fast) {
+                // K % 16 == 0 and kTile % 16 == 0 are guaranteed by the host in fast mode.
+                if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)((w.M + w.N) * BK * 8));
+                __syncwarp();
+                // one k-row per lane: lanes 0-15 -> A rows, 16-31 -> B rows
+                if (lane < 16) {
+                    const double* src = w.A + (size_t)kt * d.aKTileStride + (size_t)(kin + lane) * w.lda;
+                    bulk_g2s(dA + lane * LDA_S, src, (uint32_t)w.M * 8, &full[s]);
+                } else {
+                    const int r = lane - 16;
+                    const double* src = w.B + (size_t)kt * d.bKTileStride + (size_t)(kin + r) * w.ldb;
+                    bulk_g2s(dB + r * LDB_S, src, (uint32_t)w.N * 8, &full[s]);
+                }
+            } else {
+                // generic producer: element loads, zero fill, optional transpose (K-major operand)
+                for (int r = 0; r < BK; r++) {
+                    const int kk = kk0 + r;
+                    const bool kin_range = kk < d.K;
+                    const int kt2 = kk / d.kTile, kin2 = kk - kt2 * d.kTile;
+                    for (int i = lane; i < BM; i += 32) {
+                        double v = 0.0;
+                        if (kin_range && i < w.M)
+                            v = d.a_kmajor ? w.A[(size_t)kt2 * d.aKTileStride + kin2 + (size_t)i * w.lda]
+                                           : w.A[(size_t)kt2 * d.aKTileStride + (size_t)kin2 * w.lda + i];
+                        dA[r * LDA_S + i] = v;
+                    }
+                    for (int j = lane; j < BN; j += 32) {
+                        double v = 0.0;
+                        if (kin_range && j < w.N)
+                            v = d.b_kmajor ? w.B[(size_t)kt2 * d.bKTileStride + kin2 + (size_t)j * w.ldb]
+                                           : w.B[(size_t)kt2 * d.bKTileStride + (size_t)kin2 * w.ldb + j];
+                        dB[r * LDB_S + j] = v;
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&full[s]);
+            }
+        }
+        return;
+    }
+
+    // ================================ consumer warps ================================
+    const int wm = warp % Cfg::WARPS_M, wn = warp / Cfg::WARPS_M;
+    const int g = lane >> 2, t = lane & 3;
+    const int wm0 = wm * Cfg::WM, wn0 = wn * Cfg::WN;
+
+    double acc[MF][NF][2];
+#pragma unroll
+    for (int i = 0; i < MF; i++)
+#pragma unroll
+        for (int j = 0; j < NF; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    // per-thread fragment base offsets inside a stage
+    const int aoff = (Cfg::WM == 64) ? (wm0 + 8 * g) : (wm0 + 2 * g);
+    const int boff = wn0 + 2 * g;
+
+    for (int c = 0; c < nChunks; c++) {
+        const int s = c % STAGES;
+        mbar_wait(&full[s], (c / STAGES) & 1);
+        const double* pA = sA + (size_t)s * Cfg::A_STAGE + aoff;
+        const double* pB = sB + (size_t)s * Cfg::B_STAGE + boff;
+#pragma unroll
+        for (int ks = 0; ks < BK / 4; ks++) {
+            double a[MF], b[NF];
+            const double* ra = pA + (ks * 4 + t) * LDA_S;
+            const double* rb = pB + (ks * 4 + t) * LDB_S;
+            if (Cfg::WM == 64) {
+#pragma unroll
+                for (int v = 0; v < 4; v++) {
+                    double2 x = *reinterpret_cast<const double2*>(ra + 2 * v);
+                    a[2 * v] = x.x; a[2 * v + 1] = x.y;
+                }
+            } else {
+#pragma unroll
+                for (int v = 0; v < MF / 2; v++) {
+                    double2 x = *reinterpret_cast<const double2*>(ra + 16 * v);
+                    a[2 * v] = x.x; a[2 * v + 1] = x.y;
+                }
+            }
+#pragma unroll
+            for (int v = 0; v < NF / 2; v++) {
+                double2 x = *reinterpret_cast<const double2*>(rb + 16 * v);
+                b[2 * v] = x.x; b[2 * v + 1] = x.y;
+            }
+#pragma unroll
+            for (int i = 0; i < MF; i++)
+#pragma unroll
+                for (int j = 0; j < NF; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+    }
+
+    // ================================ epilogue ================================
+    // thread holds, for fragment (i,j): rows wm0+frag_row(g,i); columns wn0+frag_col(2t,j) and
+    // wn0+frag_col(2t+1,j)   (the C fragment's column index plays the role of B's g)
+    const double alpha = d.alpha, beta = d.beta;
+#pragma unroll
+    for (int j = 0; j < NF; j++) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int col = wn0 + frag_col(2 * t + h, j);
+            if (col >= w.N) continue;
+            double* cp = w.C + (size_t)col * w.ldc;
+            const int gj = w.gj0 + col;
+#pragma unroll
+            for (int i = 0; i < MF; i++) {
+                const int row = wm0 + frag_row<Cfg::WM>(g, i);
+                if (row >= w.M) continue;
+                if (w.lower == 1 && (w.gi0 + row < gj)) continue;
+                if (w.lower == 2 && (w.gi0 + row > gj)) continue;
+                double v = alpha * acc[i][j][h];
+                if (beta != 0.0) v += beta * cp[row];
+                cp[row] = v;
+            }
+        }
+    }
+}
+
+// host side (gemm_dmma.cu)
+int gemm_launch(const GemmDesc& d, int nItems, bool smallCfg, cudaStream_t stream);
+int gemm_init_attributes();
+
+}  // namespace dpb

@@ -1,0 +1,137 @@
+// Internal structures of libdplasma_b200 (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <cstdio>
+#include <vector>
+#include "../../include/dplasma_b200.h"
+#include "gemm_dmma.cuh"
+
+namespace dpb {
+
+constexpr int IB = 64;  // leaf block of the in-tile recursion (diagonal blocks are inverted at this size)
+
+#define DPB_CUDA(call)                                                                       \
+    do {                                                                                     \
+        cudaError_t e__ = (call);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            fprintf(stderr, "dplasma_b200: CUDA error %s at %s:%d: %s\n", #call, __FILE__,   \
+                    __LINE__, cudaGetErrorString(e__));                                      \
+            return (int)e__;                                                                 \
+        }                                                                                    \
+    } while (0)
+
+// Working layout in HBM: the regular local tile grid of a 2D block-cyclic matrix.
+// Local tile (il, jl) <-> global tile (il*P + prow, jl*Q + pcol); tile at
+// base + (il + jl*lmt) * tileElems, column-major, leading dimension mb.
+struct DevMatrix {
+    double* base = nullptr;
+    int mb = 0, nb = 0;
+    long long tileElems = 0;
+    int lmt = 0, lnt = 0;  // local tile rows / cols
+    int M = 0, N = 0;      // global size
+    int mt = 0, nt = 0;    // global tile counts
+    int P = 1, Q = 1, prow = 0, pcol = 0;
+    bool owned = false;    // staged copy allocated by the library
+    __host__ __device__ double* tile(int il, int jl) const { return base + ((size_t)il + (size_t)jl * lmt) * tileElems; }
+    __host__ __device__ int rowsOfTile(int gm) const { return gm == mt - 1 ? M - gm * mb : mb; }
+    __host__ __device__ int colsOfTile(int gn) const { return gn == nt - 1 ? N - gn * nb : nb; }
+    // first local tile row whose global index is >= gm
+    __host__ __device__ int firstLocalRowGE(int gm) const { return gm <= prow ? 0 : (gm - prow + P - 1) / P; }
+    __host__ __device__ int firstLocalColGE(int gn) const { return gn <= pcol ? 0 : (gn - pcol + Q - 1) / Q; }
+};
+
+struct NcclApi;  // comm.cu
+
+}  // namespace dpb
+
+enum TaskKind { TP_POTRF = 1 };
+
+struct parsec_taskpool_s {
+    int kind;
+    int uplo;
+    parsec_tiled_matrix_t* A;
+    int* info;
+    int hmb;
+    dpb::DevMatrix dA;
+    bool staged;
+};
+
+struct parsec_context_s {
+    int device = 0;
+    int rank = 0, nranks = 1;
+    cudaStream_t sPanel = nullptr, sUpdate = nullptr, sComm = nullptr, sCopy = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    std::vector<cudaEvent_t> evPool;
+    int* dInfo = nullptr;       // device int
+    int* hInfo = nullptr;       // pinned host int
+    double* wInv = nullptr;     // inverted diagonal blocks, 2 slots of (maxNB/IB)*IB*IB doubles
+    size_t wInvSlot = 0;
+    double* wNorm = nullptr;    // row-sum scratch for norms
+    size_t wNormLen = 0;
+    double* panelBuf[2] = {nullptr, nullptr};  // multi-GPU panel workspaces
+    size_t panelBufElems = 0;
+    double lastElapsed = 0.0;
+    double lastCheck = 0.0;
+    long long launches = 0;
+    std::vector<parsec_taskpool_s*> queue;
+    dpb::NcclApi* nccl = nullptr;
+    void* commWorld = nullptr;
+    void* commRow = nullptr;
+    void* commCol = nullptr;
+    int gridP = 0, gridQ = 0;
+    // optional per-kernel profile of the trailing-update launches (bench.py roofline leg)
+    int profile = 0;
+    std::vector<cudaEvent_t> profEv;   // pairs (start, stop)
+    std::vector<double> profFlops;
+};
+
+namespace dpb {
+// kernels.cu
+int launch_potrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
+                      int* dInfo, int infoBase);
+int launch_generate(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int kind /*0 plgsy,1 plrnt*/,
+                    double bump, int uplo, unsigned long long seed);
+int launch_rowsum_sym(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int uplo, double* rowsum);
+int launch_rowsum_ge(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, double* rowsum);
+int launch_absmax(parsec_context_s* ctx, cudaStream_t s, const double* v, long long n, double* out);
+int launch_copy_tril(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst, int ldd,
+                     int n, int uplo, int symmetrize);
+int launch_fill(parsec_context_s* ctx, cudaStream_t s, double* p, long long n, double v);
+int launch_trtri_leaf(parsec_context_s* ctx, cudaStream_t s, const double* A, int lda, int n, int uplo, int unit,
+                      double* winv);
+int launch_transpose_grid(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A);
+int launch_transpose_upper_into(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst,
+                                int ldd, int n);
+int launch_transpose(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst, int ldd,
+                     int m, int n);
+// tile_ops.cu
+int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, double alpha, const double* A,
+                int lda, bool aK, const double* B, int ldb, bool bK, double beta, double* C, int ldc,
+                int lower, int batch = 1, long long sA = 0, long long sB = 0, long long sC = 0,
+                int lastBatchM = -1);
+int potrf_tile_lower(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
+                     int* dInfo, int infoBase);
+int trsm_panel_lower(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, int n, const double* winv,
+                     double* B, int ldb, int M, int batch, long long strideB, int lastBatchM);
+int trsm_left(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, int diag, int m, int n, double alpha,
+              const double* T, int ldt, double* B, int ldb, double* winv);
+int ensure_winv(parsec_context_s* ctx, int nb);
+int ensure_wnorm(parsec_context_s* ctx, size_t n);
+// staging.cu
+int stage_in(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* out, bool copyData, int uploOnly);
+int stage_out(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int uploOnly);
+void stage_free(DevMatrix* dm);
+// comm.cu
+int sum_allreduce(parsec_context_s* ctx, double* dbuf, size_t n, cudaStream_t s);
+int bcast(parsec_context_s* ctx, void* comm, const double* send, double* recv, size_t count, int root, cudaStream_t s);
+int group_start(parsec_context_s* ctx);
+int group_end(parsec_context_s* ctx);
+int ensure_grid_comms(parsec_context_s* ctx, int P, int Q);
+void comm_destroy(parsec_context_s* ctx);
+// potrf.cu
+int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp);
+int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,
+                    long long rowStride, const double* colPanel, long long colStride, int gnFirst,
+                    int gnEnd, double alpha, int K);
+}  // namespace dpb

@@ -1,0 +1,439 @@
+// Small kernels around the DMMA engine: the leaf Cholesky (+ inverse of the factor), the
+// bit-exact matrix generators, norms and tile copies.
+#include <cstdio>
+#include "internal.h"
+
+namespace dpb {
+
+// X <- inverse of the lower-triangular S (both IB x IB in shared memory, X zeroed on entry):
+// 16x16 diagonal blocks by substitution, then two doubling levels
+// inv([L11 0; L21 L22]) = [X11 0; -X22 L21 X11, X22].
+__device__ __forceinline__ void invert_lower_64(double (*S)[IB + 1], double (*X)[IB + 1], int tid) {
+    if (tid < IB) {
+        const int r0 = (tid >> 4) << 4, c = tid & 15;
+        X[r0 + c][r0 + c] = 1.0 / S[r0 + c][r0 + c];
+        for (int i = c + 1; i < 16; i++) {
+            double sum = 0.0;
+            for (int l = c; l < i; l++) sum += S[r0 + i][r0 + l] * X[r0 + l][r0 + c];
+            X[r0 + i][r0 + c] = -sum / S[r0 + i][r0 + i];
+        }
+    }
+    __syncthreads();
+    for (int b = 16; b < IB; b <<= 1) {
+        const int E = (IB / (2 * b)) * b * b;
+        // T = L21 * X11, parked (transposed) in the unused upper triangle of X
+        for (int e = tid; e < E; e += 256) {
+            const int p = e / (b * b), r = e - p * b * b, i = r % b, c = r / b, r0 = p * 2 * b;
+            double t = 0.0;
+            for (int l = c; l < b; l++) t += S[r0 + b + i][r0 + l] * X[r0 + l][r0 + c];
+            X[r0 + c][r0 + b + i] = t;
+        }
+        __syncthreads();
+        // X21 = -X22 * T
+        for (int e = tid; e < E; e += 256) {
+            const int p = e / (b * b), r = e - p * b * b, i = r % b, c = r / b, r0 = p * 2 * b;
+            double x = 0.0;
+            for (int l = 0; l <= i; l++) x += X[r0 + b + i][r0 + b + l] * X[r0 + c][r0 + b + l];
+            X[r0 + b + i][r0 + c] = -x;
+        }
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Leaf of the in-tile recursion: factor an n x n (n <= 64) diagonal block A = L L^T in
+// shared memory and invert L.  Replaces cusolverDnDpotrf on the innermost block
+// (src/zpotrf_L.jdf:143); the inverse turns every triangular solve against this block
+// (cublasDtrsm, src/zpotrf_L.jdf:236-240) into a DMMA product.
+//   winv : 64 x 64 column-major (ld 64), lower triangular inverse, zero padded / identity
+//          beyond n.
+//   info : first non-positive pivot -> *dInfo = infoBase + j + 1 (if *dInfo was 0), the
+//          reference's global index rule (src/zpotrf_L.jdf:180-182).
+// ---------------------------------------------------------------------------------------
+constexpr int LEAF_LD = IB + 1;
+__global__ void __launch_bounds__(256) potrf_leaf_kernel(double* __restrict__ A, int lda, int n,
+                                                         double* __restrict__ winv, int* dInfo, int infoBase) {
+    extern __shared__ double leaf_smem[];
+    double(*S)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem);
+    double(*X)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem + IB * LEAF_LD);
+    __shared__ int failed;
+    const int tid = threadIdx.x;
+    for (int e = tid; e < IB * IB; e += 256) {
+        int i = e % IB, j = e / IB;
+        double v = (i == j) ? 1.0 : 0.0;
+        if (i < n && j < n && i >= j) v = A[i + (size_t)j * lda];
+        S[i][j] = v;
+        X[i][j] = 0.0;
+    }
+    if (tid == 0) failed = 0;
+    __syncthreads();
+    // right-looking unblocked Cholesky
+    for (int j = 0; j < n; j++) {
+        const double d = S[j][j];
+        if (tid == 0 && !(d > 0.0) && !failed) {
+            failed = 1;
+            if (*dInfo == 0) *dInfo = infoBase + j + 1;
+        }
+        const double s = sqrt(d), inv = 1.0 / s;
+        __syncthreads();
+        if (tid < IB) {
+            if (tid == j) S[j][j] = s;
+            else if (tid > j && tid < n) S[tid][j] *= inv;
+        }
+        __syncthreads();
+        const int i = tid & (IB - 1);
+        const double lij = S[i][j];
+        for (int c = j + 1 + (tid >> 6); c < n; c += 4)
+            if (i >= c && i < n) S[i][c] -= lij * S[c][j];
+        __syncthreads();
+    }
+    // write the factor back (lower part only: the strict upper part of the tile is not ours)
+    for (int e = tid; e < IB * IB; e += 256) {
+        int i = e % IB, j = e / IB;
+        if (i < n && j < n && i >= j) A[i + (size_t)j * lda] = S[i][j];
+    }
+    invert_lower_64(S, X, tid);
+    for (int e = tid; e < IB * IB; e += 256) {
+        int i = e % IB, j = e / IB;
+        winv[e] = (i >= j) ? X[i][j] : 0.0;
+    }
+}
+
+// Inverse of the IB x IB diagonal block of a triangular tile (the trtri step that lets the
+// solves of src/ztrsm_LLN.jdf:48 / ztrsm_LLT.jdf:48 run as DMMA products).  Upper blocks are
+// loaded transposed, so winv always holds the inverse of a LOWER block: inv(U) = winv^T.
+__global__ void __launch_bounds__(256) trtri_leaf_kernel(const double* __restrict__ A, int lda, int n, int uplo,
+                                                         int unit, double* __restrict__ winv) {
+    extern __shared__ double leaf_smem[];
+    double(*S)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem);
+    double(*X)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem + IB * LEAF_LD);
+    const int tid = threadIdx.x;
+    for (int e = tid; e < IB * IB; e += 256) {
+        int i = e % IB, j = e / IB;
+        double v = (i == j) ? 1.0 : 0.0;
+        if (i < n && j < n && i >= j) {
+            if (i == j && unit) v = 1.0;
+            else v = (uplo == dplasmaLower) ? A[i + (size_t)j * lda] : A[j + (size_t)i * lda];
+        }
+        S[i][j] = v;
+        X[i][j] = 0.0;
+    }
+    __syncthreads();
+    invert_lower_64(S, X, tid);
+    for (int e = tid; e < IB * IB; e += 256) {
+        int i = e % IB, j = e / IB;
+        winv[e] = (i >= j) ? X[i][j] : 0.0;
+    }
+}
+
+int launch_trtri_leaf(parsec_context_s* ctx, cudaStream_t s, const double* A, int lda, int n, int uplo, int unit,
+                      double* winv) {
+    static bool attr = false;
+    const int smem = 2 * IB * LEAF_LD * (int)sizeof(double);
+    if (!attr) {
+        DPB_CUDA(cudaFuncSetAttribute(trtri_leaf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr = true;
+    }
+    trtri_leaf_kernel<<<1, 256, smem, s>>>(A, lda, n, uplo, unit, winv);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+int launch_potrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
+                      int* dInfo, int infoBase) {
+    static bool attr = false;
+    const int smem = 2 * IB * LEAF_LD * (int)sizeof(double);
+    if (!attr) {
+        DPB_CUDA(cudaFuncSetAttribute(potrf_leaf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr = true;
+    }
+    potrf_leaf_kernel<<<1, 256, smem, s>>>(A, lda, n, winv, dInfo, infoBase);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Matrix generators, bit-exact with CORE_dplgsy / CORE_dplrnt
+// (src/cores/core_zplgsy.c:72-150, core_zplrnt.c:68-91, random.h:19-41).
+// Entry (I,J) of the symmetric matrix is produced by LCG state number
+// max(I,J) + min(I,J)*gM; plrnt uses I + J*gM.  The jump-ahead is evaluated per element from
+// a table of the 64 squarings (a_k, c_k) -- popcount(index) affine steps.
+// ---------------------------------------------------------------------------------------
+__constant__ unsigned long long c_jumpA[64];
+__constant__ unsigned long long c_jumpC[64];
+static bool g_jumpInit[64] = {false};
+
+static int init_jump_tables(int device) {
+    if (device < 64 && g_jumpInit[device]) return 0;
+    unsigned long long a[64], c[64];
+    unsigned long long a_k = 6364136223846793005ULL, c_k = 1ULL;
+    for (int i = 0; i < 64; i++) {
+        a[i] = a_k;
+        c[i] = c_k;
+        c_k *= (a_k + 1);
+        a_k *= a_k;
+    }
+    DPB_CUDA(cudaMemcpyToSymbol(c_jumpA, a, sizeof(a)));
+    DPB_CUDA(cudaMemcpyToSymbol(c_jumpC, c, sizeof(c)));
+    if (device < 64) g_jumpInit[device] = true;
+    return 0;
+}
+
+__device__ __forceinline__ unsigned long long rnd64_jump(unsigned long long n, unsigned long long seed) {
+    unsigned long long ran = seed;
+    while (n) {
+        const int k = __ffsll((long long)n) - 1;
+        ran = c_jumpA[k] * ran + c_jumpC[k];
+        n &= n - 1;
+    }
+    return ran;
+}
+__device__ __forceinline__ double rnd_value(unsigned long long ran) {
+    // `0.5f - ran * RndF_Mul` evaluated in float without contraction (core_zplgsy.c:89)
+    return (double)__fsub_rn(0.5f, __fmul_rn(__ull2float_rn(ran), 5.4210108624275222e-20f));
+}
+
+__global__ void __launch_bounds__(256) generate_kernel(DevMatrix A, int kind, double bump, int uplo,
+                                                       unsigned long long seed) {
+    const int t = blockIdx.y;  // local tile index
+    const int il = t % A.lmt, jl = t / A.lmt;
+    const int gm = il * A.P + A.prow, gn = jl * A.Q + A.pcol;
+    if (gm >= A.mt || gn >= A.nt) return;
+    if (kind == 0) {
+        if (uplo == dplasmaLower && gm < gn) return;
+        if (uplo == dplasmaUpper && gm > gn) return;
+    }
+    const int tm = A.rowsOfTile(gm), tn = A.colsOfTile(gn);
+    double* T = A.tile(il, jl);
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < tm * tn; e += gridDim.x * blockDim.x) {
+        const int i = e % tm, j = e / tm;
+        const unsigned long long I = (unsigned long long)gm * A.mb + i, J = (unsigned long long)gn * A.nb + j;
+        unsigned long long idx;
+        if (kind == 0) idx = (I >= J) ? I + J * (unsigned long long)A.M : J + I * (unsigned long long)A.M;
+        else idx = I + J * (unsigned long long)A.M;
+        double v = rnd_value(rnd64_jump(idx, seed));
+        if (kind == 0 && I == J) v += bump;
+        T[i + (size_t)j * A.mb] = v;
+    }
+}
+
+int launch_generate(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int kind, double bump, int uplo,
+                    unsigned long long seed) {
+    int rc = init_jump_tables(ctx->device);
+    if (rc) return rc;
+    const int tiles = A.lmt * A.lnt;
+    if (tiles == 0) return 0;
+    int bx = (int)((A.tileElems + 256 * 8 - 1) / (256 * 8));
+    if (bx < 1) bx = 1;
+    dim3 grid(bx, tiles);
+    generate_kernel<<<grid, 256, 0, s>>>(A, kind, bump, uplo, seed);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Norm helpers (dplasma_zlanhe / dplasma_zlange, InfNorm: src/dplasma_zcheck.c:101-103,194-196)
+// rowsum[I] accumulates sum_J |A(I,J)| of the symmetric matrix whose uplo triangle is stored.
+// One warp per tile column; lanes stride down the rows.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) rowsum_kernel(DevMatrix A, int sym, int uplo, double* __restrict__ rowsum) {
+    const int t = blockIdx.y;
+    const int il = t % A.lmt, jl = t / A.lmt;
+    const int gm = il * A.P + A.prow, gn = jl * A.Q + A.pcol;
+    if (gm >= A.mt || gn >= A.nt) return;
+    if (sym && uplo == dplasmaLower && gm < gn) return;
+    if (sym && uplo == dplasmaUpper && gm > gn) return;
+    const int tm = A.rowsOfTile(gm), tn = A.colsOfTile(gn);
+    const double* T = A.tile(il, jl);
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int j = warp; j < tn; j += nwarps) {
+        const long long J = (long long)gn * A.nb + j;
+        double colsum = 0.0;
+        for (int i = lane; i < tm; i += 32) {
+            const long long I = (long long)gm * A.mb + i;
+            if (sym) {
+                if (uplo == dplasmaLower ? (I < J) : (I > J)) continue;  // other triangle of a diagonal tile
+            }
+            const double v = fabs(T[i + (size_t)j * A.mb]);
+            atomicAdd(&rowsum[I], v);
+            if (sym && I != J) colsum += v;
+        }
+        if (sym) {
+            for (int o = 16; o; o >>= 1) colsum += __shfl_xor_sync(0xffffffffu, colsum, o);
+            if (lane == 0 && colsum != 0.0) atomicAdd(&rowsum[J], colsum);
+            // NaN must propagate even though NaN != 0.0 is true -> handled: NaN != 0.0 is true
+        }
+    }
+}
+
+int launch_rowsum_sym(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int uplo, double* rowsum) {
+    const int tiles = A.lmt * A.lnt;
+    if (tiles == 0) return 0;
+    int bx = (A.nb + 7) / 8;
+    dim3 grid(bx, tiles);
+    rowsum_kernel<<<grid, 256, 0, s>>>(A, 1, uplo, rowsum);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+int launch_rowsum_ge(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, double* rowsum) {
+    const int tiles = A.lmt * A.lnt;
+    if (tiles == 0) return 0;
+    int bx = (A.nb + 7) / 8;
+    dim3 grid(bx, tiles);
+    rowsum_kernel<<<grid, 256, 0, s>>>(A, 0, dplasmaUpperLower, rowsum);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+// max |v[i]| with NaN propagation; single block
+__global__ void __launch_bounds__(1024) absmax_kernel(const double* __restrict__ v, long long n, double* out) {
+    __shared__ double sm[32];
+    __shared__ int snan[32];
+    double m = 0.0;
+    int isn = 0;
+    for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+        double x = fabs(v[i]);
+        if (x != x) isn = 1;
+        else if (x > m) m = x;
+    }
+    for (int o = 16; o; o >>= 1) {
+        m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+        isn |= __shfl_xor_sync(0xffffffffu, isn, o);
+    }
+    if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5] = m; snan[threadIdx.x >> 5] = isn; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 0; w < (blockDim.x >> 5); w++) { m = fmax(m, sm[w]); isn |= snan[w]; }
+        *out = isn ? nan("") : m;
+    }
+}
+int launch_absmax(parsec_context_s* ctx, cudaStream_t s, const double* v, long long n, double* out) {
+    absmax_kernel<<<1, 1024, 0, s>>>(v, n, out);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+// dst <- triangle of src (n x n); the other triangle zeroed (symmetrize=0) or mirrored (1)
+__global__ void copy_tril_kernel(const double* __restrict__ src, int lds, double* __restrict__ dst, int ldd,
+                                 int n, int uplo, int symmetrize) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < (long long)n * n;
+         e += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(e % n), j = (int)(e / n);
+        const bool stored = (uplo == dplasmaLower) ? (i >= j) : (i <= j);
+        double v;
+        if (stored) v = src[i + (size_t)j * lds];
+        else if (symmetrize == 2) continue;  // leave the other triangle of dst alone
+        else v = symmetrize ? src[j + (size_t)i * lds] : 0.0;
+        dst[i + (size_t)j * ldd] = v;
+    }
+}
+int launch_copy_tril(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst, int ldd,
+                     int n, int uplo, int symmetrize) {
+    if (n <= 0) return 0;
+    int blocks = (int)(((long long)n * n + 255) / 256);
+    if (blocks > 1184) blocks = 1184;
+    copy_tril_kernel<<<blocks, 256, 0, s>>>(src, lds, dst, ldd, n, uplo, symmetrize);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Transposition (the Upper variants run as the Lower algorithm on the transposed tiles:
+// U(k,n) = L(n,k)^T, src/zpotrf_U.jdf computes exactly the transposed operations).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) transpose_kernel(const double* __restrict__ src, int lds,
+                                                        double* __restrict__ dst, int ldd, int m, int n) {
+    __shared__ double t[32][33];
+    const int bi = blockIdx.x * 32, bj = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int j = ty; j < 32; j += 8)
+        if (bi + tx < m && bj + j < n) t[j][tx] = src[(bi + tx) + (size_t)(bj + j) * lds];
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8)
+        if (bj + tx < n && bi + j < m) dst[(bj + tx) + (size_t)(bi + j) * ldd] = t[tx][j];
+}
+// dst(upper triangle incl. diagonal) <- src(lower triangle)^T ; the strict lower part of dst is not written
+__global__ void __launch_bounds__(256) transpose_upper_into_kernel(const double* __restrict__ src, int lds,
+                                                                   double* __restrict__ dst, int ldd, int n) {
+    __shared__ double t[32][33];
+    const int bi = blockIdx.x * 32, bj = blockIdx.y * 32;  // block of src
+    if (bi < bj) return;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int j = ty; j < 32; j += 8)
+        if (bi + tx < n && bj + j < n) t[j][tx] = src[(bi + tx) + (size_t)(bj + j) * lds];
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        const int r = bj + tx, c = bi + j;  // dst(r,c) = src(c,r)
+        if (r < n && c < n && r <= c) dst[r + (size_t)c * ldd] = t[tx][j];
+    }
+}
+int launch_transpose_upper_into(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst,
+                                int ldd, int n) {
+    if (n <= 0) return 0;
+    dim3 grid((n + 31) / 32, (n + 31) / 32);
+    transpose_upper_into_kernel<<<grid, 256, 0, s>>>(src, lds, dst, ldd, n);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+int launch_transpose(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst, int ldd,
+                     int m, int n) {
+    if (m <= 0 || n <= 0) return 0;
+    dim3 grid((m + 31) / 32, (n + 31) / 32);
+    transpose_kernel<<<grid, 256, 0, s>>>(src, lds, dst, ldd, m, n);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+// In-place transposition of a whole single-process tile grid (square tiles, P = Q = 1):
+// tile (m,n) <-> tile (n,m)^T.  One CTA per 32x32 block pair.
+__global__ void __launch_bounds__(256) transpose_grid_kernel(DevMatrix A) {
+    __shared__ double ta[32][33], tb[32][33];
+    // blockIdx.z enumerates tile pairs m >= n; x,y the 32x32 blocks of tile (m,n)
+    int pz = blockIdx.z, m = 0;
+    while ((m + 1) * (m + 2) / 2 <= pz) m++;
+    const int n = pz - m * (m + 1) / 2;
+    if (m >= A.mt || n >= A.nt) return;
+    const int bi = blockIdx.x * 32, bj = blockIdx.y * 32;
+    if (m == n && bi < bj) return;
+    double* Ta = A.tile(m, n);
+    double* Tb = A.tile(n, m);
+    const int ld = A.mb, nb = A.mb;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int j = ty; j < 32; j += 8) {
+        if (bi + tx < nb && bj + j < nb) ta[j][tx] = Ta[(bi + tx) + (size_t)(bj + j) * ld];
+        if (bj + tx < nb && bi + j < nb) tb[j][tx] = Tb[(bj + tx) + (size_t)(bi + j) * ld];
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        // Tb block (bj.., bi..) <- (Ta block)^T ; Ta block (bi.., bj..) <- (Tb block)^T
+        if (bj + tx < nb && bi + j < nb) Tb[(bj + tx) + (size_t)(bi + j) * ld] = ta[tx][j];
+        if (bi + tx < nb && bj + j < nb) Ta[(bi + tx) + (size_t)(bj + j) * ld] = tb[tx][j];
+    }
+}
+int launch_transpose_grid(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A) {
+    if (A.P * A.Q != 1 || A.mb != A.nb || A.mt != A.nt) return -3;
+    const int nblk = (A.mb + 31) / 32;
+    const long long pairs = (long long)A.mt * (A.mt + 1) / 2;
+    if (pairs > 65535) return -4;
+    dim3 grid(nblk, nblk, (unsigned)pairs);
+    transpose_grid_kernel<<<grid, 256, 0, s>>>(A);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+__global__ void fill_kernel(double* p, long long n, double v) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < n;
+         e += (long long)gridDim.x * blockDim.x)
+        p[e] = v;
+}
+int launch_fill(parsec_context_s* ctx, cudaStream_t s, double* p, long long n, double v) {
+    if (n <= 0) return 0;
+    long long blocks = (n + 255) / 256;
+    if (blocks > 1184) blocks = 1184;
+    fill_kernel<<<(int)blocks, 256, 0, s>>>(p, n, v);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+}  // namespace dpb

@@ -1,0 +1,298 @@
+// Tiled Cholesky driver: the static, look-ahead schedule that replaces the PaRSEC task graph
+// of src/zpotrf_L.jdf (task classes potrf_zpotrf / potrf_ztrsm / potrf_zherk / potrf_zgemm,
+// flows :109-114,209-217,321-325,423-428) and the public wrappers of src/zpotrf_wrapper.c.
+//
+// Schedule per step k (lower):
+//   panel stream (high priority):  POTRF(k,k) -> TRSM(k+1..,k) -> update of tile column k+1
+//   update stream:                 update of tile columns k+2.. with panel k  (one grouped launch)
+// so that the panel of step k+1 is factored underneath the bulk update of step k, the same
+// critical-path-first order the reference expresses with task priorities (:116,219,327,430).
+#include <cstdio>
+#include <cstdlib>
+#include <algorithm>
+#include "internal.h"
+
+namespace dpb {
+
+static cudaEvent_t get_event(parsec_context_s* ctx, size_t idx) {
+    while (ctx->evPool.size() <= idx) {
+        cudaEvent_t e;
+        cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+        ctx->evPool.push_back(e);
+    }
+    return ctx->evPool[idx];
+}
+
+// C(gm,gn) += alpha * rowPanel[il] * colPanel[jl]^T for the local tiles with
+// gnFirst <= gn < gnEnd and gm >= gn; diagonal tiles only in their lower part (SYRK).
+int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,
+                    long long rowStride, const double* colPanel, long long colStride, int gnFirst, int gnEnd,
+                    double alpha, int K) {
+    const int jl0 = C.firstLocalColGE(gnFirst), jl1 = std::min(C.firstLocalColGE(gnEnd), C.lnt);
+    const int rowEnd = std::min(C.firstLocalRowGE(C.mt), C.lmt);
+    for (int c0 = jl0; c0 < jl1; c0 += kMaxCols) {
+        const int ncols = std::min(kMaxCols, jl1 - c0);
+        GemmDesc d;
+        d.mode = GEMM_TRAILING;
+        d.alpha = alpha; d.beta = 1.0; d.K = K;
+        d.a_kmajor = d.b_kmajor = 0;
+        d.kTile = 1 << 30; d.aKTileStride = d.bKTileStride = 0;
+        d.Cbase = C.base; d.rowPanel = rowPanel; d.colPanel = colPanel;
+        d.rowPanelStride = rowStride; d.colPanelStride = colStride; d.tileElems = C.tileElems;
+        d.tileLdT = C.lmt; d.nb = C.nb;
+        d.ncols = ncols; d.colFirst = c0;
+        d.P = C.P; d.Q = C.Q; d.prow = C.prow; d.pcol = C.pcol;
+        d.lastM = C.rowsOfTile(C.mt - 1); d.lastN = C.colsOfTile(C.nt - 1);
+        d.mtGlobal = C.mt; d.ntGlobal = C.nt;
+        d.rowEnd = rowEnd;
+        d.fast = ((C.nb % 2 == 0) && (K % 16 == 0) && ((reinterpret_cast<uintptr_t>(rowPanel) & 15) == 0) &&
+                  ((reinterpret_cast<uintptr_t>(colPanel) & 15) == 0) && (rowStride % 2 == 0) &&
+                  (colStride % 2 == 0))
+                     ? 1 : 0;
+        long long tiles = 0;
+        for (int c = 0; c < ncols; c++) {
+            const int gn = (c0 + c) * C.Q + C.pcol;
+            d.rowFirst[c] = std::min(C.firstLocalRowGE(gn), rowEnd);
+            tiles += rowEnd - d.rowFirst[c];
+        }
+        if (tiles == 0) continue;
+        const int bptBig = (C.nb + 127) / 128;
+        const bool small = tiles * bptBig * bptBig < 120;
+        d.bpt = small ? (C.nb + 63) / 64 : bptBig;
+        long long items = 0;
+        for (int c = 0; c < ncols; c++) {
+            d.itemStart[c] = (int)items;
+            items += (long long)(rowEnd - d.rowFirst[c]) * d.bpt * d.bpt;
+        }
+        d.itemStart[ncols] = (int)items;
+        ctx->launches++;
+        cudaEvent_t pe0 = nullptr, pe1 = nullptr;
+        if (ctx->profile) {
+            cudaEventCreate(&pe0);
+            cudaEventCreate(&pe1);
+            cudaEventRecord(pe0, s);
+        }
+        int rc = gemm_launch(d, (int)items, small, s);
+        if (ctx->profile) {
+            cudaEventRecord(pe1, s);
+            // algorithmic flops of this launch: 2 nb^2 K per GEMM tile, nb (nb+1) K per SYRK tile
+            double fl = 0.0;
+            for (int c = 0; c < ncols; c++) {
+                const int gn = (c0 + c) * C.Q + C.pcol;
+                for (int il = d.rowFirst[c]; il < rowEnd; il++) {
+                    const int gm = il * C.P + C.prow;
+                    const double tm = C.rowsOfTile(gm), tn = C.colsOfTile(gn);
+                    fl += (gm == gn) ? tm * (tm + 1.0) * K : 2.0 * tm * tn * K;
+                }
+            }
+            ctx->profEv.push_back(pe0);
+            ctx->profEv.push_back(pe1);
+            ctx->profFlops.push_back(fl);
+        }
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+// ---- single-process schedule (P = Q = 1): panels are read in place from the matrix ----
+static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
+    const int nt = A.nt, nb = A.nb;
+    int rc = ensure_winv(ctx, nb);
+    if (rc) return rc;
+    cudaStream_t sp = ctx->sPanel, su = ctx->sUpdate;
+    // the update stream must see everything enqueued on the panel stream so far (staging copies)
+    cudaEvent_t ev0 = get_event(ctx, 0);
+    DPB_CUDA(cudaEventRecord(ev0, sp));
+    DPB_CUDA(cudaStreamWaitEvent(su, ev0, 0));
+    size_t evi = 1;
+    cudaEvent_t evUpdPrev = nullptr;
+    for (int k = 0; k < nt; k++) {
+        const int tk = A.rowsOfTile(k);
+        double* winv = ctx->wInv + (size_t)(k & 1) * ctx->wInvSlot;
+        double* Akk = A.tile(k, k);
+        rc = potrf_tile_lower(ctx, sp, Akk, A.mb, tk, winv, ctx->dInfo, k * nb);
+        if (rc) return rc;
+        const int below = nt - k - 1;
+        if (below <= 0) break;
+        rc = trsm_panel_lower(ctx, sp, Akk, A.mb, tk, winv, A.tile(k + 1, k), A.mb, A.mb, below, A.tileElems,
+                              A.rowsOfTile(nt - 1));
+        if (rc) return rc;
+        cudaEvent_t evPanel = get_event(ctx, evi++);
+        DPB_CUDA(cudaEventRecord(evPanel, sp));
+        const double* panel = A.tile(0, k);  // tile (i,k) at panel + i*tileElems
+        // look-ahead: tile column k+1 on the panel stream (after the previous bulk update wrote it)
+        if (evUpdPrev) DPB_CUDA(cudaStreamWaitEvent(sp, evUpdPrev, 0));
+        rc = trailing_update(ctx, sp, A, panel, A.tileElems, panel, A.tileElems, k + 1, k + 2, -1.0, nb);
+        if (rc) return rc;
+        // bulk: tile columns k+2.. on the update stream
+        if (k + 2 < nt) {
+            DPB_CUDA(cudaStreamWaitEvent(su, evPanel, 0));
+            rc = trailing_update(ctx, su, A, panel, A.tileElems, panel, A.tileElems, k + 2, nt, -1.0, nb);
+            if (rc) return rc;
+            cudaEvent_t evUpd = get_event(ctx, evi++);
+            DPB_CUDA(cudaEventRecord(evUpd, su));
+            evUpdPrev = evUpd;
+        } else {
+            evUpdPrev = nullptr;
+        }
+    }
+    // join: the panel stream is the one wait() synchronises / times
+    cudaEvent_t evEnd = get_event(ctx, evi++);
+    DPB_CUDA(cudaEventRecord(evEnd, su));
+    DPB_CUDA(cudaStreamWaitEvent(sp, evEnd, 0));
+    return 0;
+}
+
+int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp);  // potrf_dist.cu
+
+int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp) {
+    DevMatrix& A = tp->dA;
+    if (A.mb != A.nb) return -3;
+    if (tp->uplo == dplasmaLower) {
+        if (A.P * A.Q == 1) return potrf_lower_1gpu(ctx, A);
+        return potrf_multi(ctx, tp);
+    }
+    // dplasmaUpper (src/zpotrf_U.jdf): U(k,n) = L(n,k)^T and every tile operation of the upper
+    // DAG is the transpose of its lower counterpart, so the factorization runs as the lower
+    // schedule on the transposed tile grid and is transposed back (two HBM-bound passes).
+    if (A.P * A.Q != 1) {
+        fprintf(stderr, "dplasma_b200: dplasmaUpper on a process grid is not available yet\n");
+        return -2;
+    }
+    int rc = launch_transpose_grid(ctx, ctx->sPanel, A);
+    if (!rc) rc = potrf_lower_1gpu(ctx, A);
+    if (!rc) rc = launch_transpose_grid(ctx, ctx->sPanel, A);
+    return rc;
+}
+
+}  // namespace dpb
+
+using namespace dpb;
+
+extern "C" {
+
+parsec_taskpool_t* dplasma_dpotrf_New(dplasma_enum_t uplo, parsec_tiled_matrix_t* A, int* info) {
+    if (uplo != dplasmaUpper && uplo != dplasmaLower) {
+        // dplasma_error("dplasma_zpotrf_New", "illegal value of uplo")  (src/zpotrf_wrapper.c:187-190)
+        fprintf(stderr, "dplasma_dpotrf_New: illegal value of uplo\n");
+        return nullptr;
+    }
+    if (info) *info = 0;  // src/zpotrf_wrapper.c:192
+    parsec_taskpool_s* tp = new parsec_taskpool_s();
+    tp->kind = TP_POTRF;
+    tp->uplo = uplo;
+    tp->A = A;
+    tp->info = info;
+    tp->hmb = 0;
+    tp->staged = false;
+    return tp;
+}
+
+void dplasma_dpotrf_setrecursive(parsec_taskpool_t* tp, int hmb) {
+    if (tp) tp->hmb = hmb;  // accepted; the in-tile recursion block is fixed (IB)
+}
+
+void dplasma_dpotrf_Destruct(parsec_taskpool_t* tp) {
+    if (!tp) return;
+    stage_free(&tp->dA);
+    delete tp;
+}
+void dplasma_dpotrf_Destroy(parsec_taskpool_t* tp) { dplasma_dpotrf_Destruct(tp); }
+
+int parsec_context_add_taskpool(parsec_context_t* ctx, parsec_taskpool_t* tp) {
+    if (!ctx || !tp) return -1;
+    ctx->queue.push_back(tp);
+    return 0;
+}
+
+// Enqueue all GPU work of the queued taskpools; returns without waiting for the GPU.
+int parsec_context_start(parsec_context_t* ctx) {
+    if (!ctx) return -1;
+    cudaSetDevice(ctx->device);
+    DPB_CUDA(cudaMemsetAsync(ctx->dInfo, 0, sizeof(int), ctx->sPanel));
+    for (parsec_taskpool_s* tp : ctx->queue) {
+        if (tp->kind != TP_POTRF) continue;
+        int rc = stage_in(ctx, tp->A, &tp->dA, true, tp->uplo);
+        if (rc) return rc;
+        tp->staged = true;
+    }
+    DPB_CUDA(cudaEventRecord(ctx->evStart, ctx->sPanel));
+    for (parsec_taskpool_s* tp : ctx->queue) {
+        int rc = potrf_enqueue(ctx, tp);
+        if (rc) return rc;
+    }
+    DPB_CUDA(cudaEventRecord(ctx->evStop, ctx->sPanel));
+    for (parsec_taskpool_s* tp : ctx->queue) {
+        int rc = stage_out(ctx, tp->A, &tp->dA, tp->uplo);
+        if (rc) return rc;
+    }
+    DPB_CUDA(cudaMemcpyAsync(ctx->hInfo, ctx->dInfo, sizeof(int), cudaMemcpyDeviceToHost, ctx->sPanel));
+    return 0;
+}
+
+int parsec_context_wait(parsec_context_t* ctx) {
+    if (!ctx) return -1;
+    DPB_CUDA(cudaStreamSynchronize(ctx->sPanel));
+    DPB_CUDA(cudaStreamSynchronize(ctx->sUpdate));
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ctx->evStart, ctx->evStop) == cudaSuccess) ctx->lastElapsed = ms * 1e-3;
+    for (parsec_taskpool_s* tp : ctx->queue) {
+        if (tp->info && *tp->info == 0) *tp->info = *ctx->hInfo;  // rank-local until the wrapper reduces it
+        stage_free(&tp->dA);
+    }
+    ctx->queue.clear();
+    return 0;
+}
+
+int info_allreduce_max(parsec_context_s* ctx, int info);  // comm.cu
+
+int dplasma_dpotrf(parsec_context_t* parsec, dplasma_enum_t uplo, parsec_tiled_matrix_t* A) {
+    if (!parsec) return -1;
+    int info = 0;
+    parsec_taskpool_t* tp = dplasma_dpotrf_New(uplo, A, &info);
+    if (!tp) return -101;  // src/zpotrf_wrapper.c:318-319 region: New failed
+    int rc = parsec_context_add_taskpool(parsec, tp);
+    if (!rc) rc = parsec_context_start(parsec);
+    int rc2 = parsec_context_wait(parsec);
+    dplasma_dpotrf_Destruct(tp);
+    if (rc) return rc < 0 ? rc : -rc - 1000;
+    if (rc2) return rc2 < 0 ? rc2 : -rc2 - 1000;
+    if (A->super.nodes > 1) info = info_allreduce_max(parsec, info);  // src/zpotrf_wrapper.c:331-332
+    return info;
+}
+
+// profile of the grouped trailing-update launches (the dominant kernel): mode 1 starts
+// collecting, dplasma_b200_profile_read sums event-timed seconds / algorithmic flops / launches
+void dplasma_b200_profile(parsec_context_t* ctx, int on) {
+    if (!ctx) return;
+    for (cudaEvent_t e : ctx->profEv) cudaEventDestroy(e);
+    ctx->profEv.clear();
+    ctx->profFlops.clear();
+    ctx->profile = on;
+}
+int dplasma_b200_profile_read(parsec_context_t* ctx, double* seconds, double* flops, int* launches,
+                              double* best_tflops) {
+    if (!ctx) return -1;
+    cudaDeviceSynchronize();
+    double t = 0.0, f = 0.0, best = 0.0;
+    const size_t n = ctx->profFlops.size();
+    for (size_t i = 0; i < n; i++) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ctx->profEv[2 * i], ctx->profEv[2 * i + 1]) != cudaSuccess) continue;
+        t += ms * 1e-3;
+        f += ctx->profFlops[i];
+        if (ms > 0.5f) best = std::max(best, ctx->profFlops[i] / (ms * 1e-3) / 1e12);
+    }
+    if (seconds) *seconds = t;
+    if (flops) *flops = f;
+    if (launches) *launches = (int)n;
+    if (best_tflops) *best_tflops = best;
+    return 0;
+}
+
+int dplasma_dpotrf_rec(parsec_context_t* parsec, dplasma_enum_t uplo, parsec_tiled_matrix_t* A, int hmb) {
+    (void)hmb;
+    return dplasma_dpotrf(parsec, uplo, A);
+}
+
+}  // extern "C"

@@ -1,0 +1,285 @@
+// Host-side runtime of libdplasma_b200: the per-process context that takes PaRSEC's place on
+// this path (streams, workspaces, taskpool queue), the 2D block-cyclic descriptors, and the
+// staging of caller matrices (host / sym-packed / LAPACK storage) into the regular tile grid
+// the kernels work on (the role of stage_in/stage_out in src/dplasmajdf_lapack_dtt.h:131-275).
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include "internal.h"
+
+using namespace dpb;
+
+extern "C" {
+
+const char* dplasma_b200_version(void) { return "dplasma_b200 0.1 (sm_100a)"; }
+
+parsec_context_t* parsec_init(int nb_cores, int* pargc, char** pargv[]) {
+    (void)nb_cores; (void)pargc; (void)pargv;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        fprintf(stderr, "dplasma_b200: no CUDA device -- this library has no CPU fallback\n");
+        return nullptr;
+    }
+    parsec_context_s* ctx = new parsec_context_s();
+    cudaGetDevice(&ctx->device);
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);  // hi is the numerically lowest = highest priority
+    bool ok = cudaStreamCreateWithPriority(&ctx->sPanel, cudaStreamNonBlocking, hi) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&ctx->sUpdate, cudaStreamNonBlocking, lo) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&ctx->sComm, cudaStreamNonBlocking, hi) == cudaSuccess &&
+              cudaStreamCreateWithPriority(&ctx->sCopy, cudaStreamNonBlocking, lo) == cudaSuccess &&
+              cudaEventCreate(&ctx->evStart) == cudaSuccess && cudaEventCreate(&ctx->evStop) == cudaSuccess &&
+              cudaMalloc(&ctx->dInfo, 64) == cudaSuccess &&
+              cudaHostAlloc(&ctx->hInfo, 64, cudaHostAllocDefault) == cudaSuccess &&
+              gemm_init_attributes() == 0;
+    if (!ok) {
+        fprintf(stderr, "dplasma_b200: context creation failed: %s\n", cudaGetErrorString(cudaGetLastError()));
+        delete ctx;
+        return nullptr;
+    }
+    cudaMemset(ctx->dInfo, 0, 64);
+    return ctx;
+}
+
+int parsec_fini(parsec_context_t** pctx) {
+    if (!pctx || !*pctx) return -1;
+    parsec_context_s* ctx = *pctx;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    comm_destroy(ctx);
+    for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
+    if (ctx->wInv) cudaFree(ctx->wInv);
+    if (ctx->wNorm) cudaFree(ctx->wNorm);
+    for (int i = 0; i < 2; i++)
+        if (ctx->panelBuf[i]) cudaFree(ctx->panelBuf[i]);
+    cudaFree(ctx->dInfo);
+    cudaFreeHost(ctx->hInfo);
+    cudaEventDestroy(ctx->evStart);
+    cudaEventDestroy(ctx->evStop);
+    cudaStreamDestroy(ctx->sPanel);
+    cudaStreamDestroy(ctx->sUpdate);
+    cudaStreamDestroy(ctx->sComm);
+    cudaStreamDestroy(ctx->sCopy);
+    delete ctx;
+    *pctx = nullptr;
+    return 0;
+}
+
+void* parsec_data_allocate(size_t bytes) {
+    void* p = nullptr;
+    if (bytes == 0) bytes = 8;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+        fprintf(stderr, "dplasma_b200: pinned allocation of %zu bytes failed\n", bytes);
+        return nullptr;
+    }
+    return p;
+}
+void parsec_data_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+void* dplasma_b200_device_allocate(size_t bytes) {
+    void* p = nullptr;
+    if (bytes == 0) bytes = 8;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) {
+        fprintf(stderr, "dplasma_b200: device allocation of %zu bytes failed\n", bytes);
+        return nullptr;
+    }
+    return p;
+}
+void dplasma_b200_device_free(void* p) {
+    if (p) cudaFree(p);
+}
+
+double dplasma_b200_last_elapsed(parsec_context_t* ctx) { return ctx ? ctx->lastElapsed : 0.0; }
+double dplasma_b200_last_check_result(parsec_context_t* ctx) { return ctx ? ctx->lastCheck : 0.0; }
+long long dplasma_b200_kernel_launches(parsec_context_t* ctx) { return ctx ? ctx->launches : 0; }
+
+double dplasma_b200_flops_dpotrf(double n) { return n * n * n / 3.0 + n * n / 2.0 + n / 6.0; }
+double dplasma_b200_flops_dpotrs(double n, double nrhs) { return 2.0 * nrhs * n * n; }
+
+// ---------------------------------------------------------------------------------------
+// descriptors
+// ---------------------------------------------------------------------------------------
+static int local_tiles(int nt, int P, int p) { return nt > p ? (nt - p + P - 1) / P : 0; }
+
+static void init_common(parsec_matrix_block_cyclic_t* dc, int mtype, int storage, int myrank, int mb, int nb,
+                        int lm, int ln, int i, int j, int m, int n, int P, int Q, int kp, int kq, int ip,
+                        int jq) {
+    memset(dc, 0, sizeof(*dc));
+    parsec_tiled_matrix_t* t = &dc->super;
+    if (P < 1) P = 1;
+    if (Q < 1) Q = 1;
+    t->super.nodes = (uint32_t)(P * Q);
+    t->super.myrank = (uint32_t)myrank;
+    t->mtype = mtype;
+    t->storage = storage;
+    t->mb = mb; t->nb = nb; t->bsiz = mb * nb;
+    t->lm = lm; t->ln = ln;
+    t->lmt = (lm + mb - 1) / mb; t->lnt = (ln + nb - 1) / nb;
+    t->i = i; t->j = j; t->m = m; t->n = n;
+    t->mt = (m + mb - 1) / mb; t->nt = (n + nb - 1) / nb;
+    dc->grid.rank = myrank; dc->grid.rows = P; dc->grid.cols = Q;
+    dc->grid.rrank = myrank / Q; dc->grid.crank = myrank % Q;  // row-major grid (Cblacs_gridinit "Row")
+    dc->grid.krows = kp; dc->grid.kcols = kq; dc->grid.ip = ip; dc->grid.jq = jq;
+    const int prow = (dc->grid.rrank - ip + P) % P, pcol = (dc->grid.crank - jq + Q) % Q;
+    dc->nb_elem_r = local_tiles(t->lmt, P, prow);
+    dc->nb_elem_c = local_tiles(t->lnt, Q, pcol);
+    // local element counts (numroc)
+    int lr = 0, lc = 0;
+    for (int g = prow; g < t->lmt; g += P) lr += (g == t->lmt - 1) ? lm - g * mb : mb;
+    for (int g = pcol; g < t->lnt; g += Q) lc += (g == t->lnt - 1) ? ln - g * nb : nb;
+    t->llm = lr; t->lln = lc; t->slm = lr; t->sln = lc;
+    t->nb_local_tiles = dc->nb_elem_r * dc->nb_elem_c;
+    dc->uplo = dplasmaUpperLower;
+    dc->mat = nullptr;
+}
+
+void parsec_matrix_block_cyclic_init(parsec_matrix_block_cyclic_t* dc, int mtype, int storage, int myrank,
+                                     int mb, int nb, int lm, int ln, int i, int j, int m, int n, int P, int Q,
+                                     int kp, int kq, int ip, int jq) {
+    init_common(dc, mtype, storage, myrank, mb, nb, lm, ln, i, j, m, n, P, Q, kp, kq, ip, jq);
+}
+
+void parsec_matrix_sym_block_cyclic_init(parsec_matrix_sym_block_cyclic_t* dc, int mtype, int myrank, int mb,
+                                         int nb, int lm, int ln, int i, int j, int m, int n, int P, int Q,
+                                         int uplo) {
+    init_common(dc, mtype, PARSEC_MATRIX_TILE, myrank, mb, nb, lm, ln, i, j, m, n, P, Q, 1, 1, 0, 0);
+    dc->uplo = uplo;
+    // count the tiles of the stored triangle that live here
+    int cnt = 0;
+    const int prow = dc->grid.rrank, pcol = dc->grid.crank;
+    for (int gn = pcol; gn < dc->super.lnt; gn += Q)
+        for (int gm = prow; gm < dc->super.lmt; gm += P)
+            if (uplo == dplasmaLower ? gm >= gn : gm <= gn) cnt++;
+    dc->super.nb_local_tiles = cnt;
+}
+
+void parsec_matrix_block_cyclic_lapack_init(parsec_matrix_block_cyclic_t* dc, int mtype, int storage, int myrank,
+                                            int mb, int nb, int lm, int ln, int i, int j, int m, int n, int P,
+                                            int Q, int kp, int kq, int ip, int jq, int mloc, int nloc) {
+    init_common(dc, mtype, storage, myrank, mb, nb, lm, ln, i, j, m, n, P, Q, kp, kq, ip, jq);
+    dc->super.llm = mloc;  // leading dimension of the caller's local array (LLD)
+    dc->super.lln = nloc;
+}
+
+void parsec_tiled_matrix_destroy(parsec_tiled_matrix_t* dc) { (void)dc; }
+
+int dplasma_b200_rank_of(const parsec_tiled_matrix_t* A, int m, int n) {
+    const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
+    const int pr = (m + bc->grid.ip) % bc->grid.rows, pc = (n + bc->grid.jq) % bc->grid.cols;
+    return pr * bc->grid.cols + pc;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// staging
+// ---------------------------------------------------------------------------------------
+namespace dpb {
+
+static bool is_device_ptr(const void* p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+static int describe(const parsec_tiled_matrix_t* A, DevMatrix* dm) {
+    const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
+    if (A->mtype != PARSEC_MATRIX_DOUBLE) return -1;
+    if (bc->grid.krows != 1 || bc->grid.kcols != 1) return -2;
+    if (A->i != 0 || A->j != 0 || A->m != A->lm || A->n != A->ln) return -3;  // whole-matrix descriptors only
+    dm->mb = A->mb; dm->nb = A->nb; dm->tileElems = (long long)A->mb * A->nb;
+    dm->M = A->m; dm->N = A->n; dm->mt = A->mt; dm->nt = A->nt;
+    dm->P = bc->grid.rows; dm->Q = bc->grid.cols;
+    dm->prow = (bc->grid.rrank - bc->grid.ip + dm->P) % dm->P;
+    dm->pcol = (bc->grid.crank - bc->grid.jq + dm->Q) % dm->Q;
+    dm->lmt = bc->nb_elem_r; dm->lnt = bc->nb_elem_c;
+    return 0;
+}
+
+// Copies between the caller's layout and the regular device tile grid.  dir 0: in, 1: out.
+static int copy_layout(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int dir, int uploOnly) {
+    const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
+    double* user = (double*)bc->mat;
+    cudaStream_t s = ctx->sPanel;
+    const bool sym = bc->uplo != dplasmaUpperLower;
+    const int part = sym ? bc->uplo : uploOnly;  // which tiles move
+    if (A->storage == PARSEC_MATRIX_TILE) {
+        size_t packed = 0;  // running tile offset in a sym-packed array
+        for (int jl = 0; jl < dm->lnt; jl++) {
+            const int gn = jl * dm->Q + dm->pcol;
+            int i0 = 0, i1 = dm->lmt;
+            if (part == dplasmaLower) i0 = dm->firstLocalRowGE(gn);
+            else if (part == dplasmaUpper) i1 = dm->firstLocalRowGE(gn + 1);
+            if (i1 > dm->lmt) i1 = dm->lmt;
+            if (i0 >= i1) continue;
+            const size_t cnt = (size_t)(i1 - i0) * dm->tileElems;
+            double* dev = dm->tile(i0, jl);
+            double* usr = sym ? user + packed * dm->tileElems
+                              : user + ((size_t)i0 + (size_t)jl * dm->lmt) * dm->tileElems;
+            packed += (size_t)(i1 - i0);
+            if (dir == 0) DPB_CUDA(cudaMemcpyAsync(dev, usr, cnt * sizeof(double), cudaMemcpyDefault, s));
+            else DPB_CUDA(cudaMemcpyAsync(usr, dev, cnt * sizeof(double), cudaMemcpyDefault, s));
+        }
+    } else {
+        // LAPACK storage: pitched copies, one per tile (src/dplasmajdf_lapack_dtt.h:161-178,238-255)
+        const size_t lld = (size_t)A->llm;
+        for (int jl = 0; jl < dm->lnt; jl++) {
+            const int gn = jl * dm->Q + dm->pcol;
+            const int tn = dm->colsOfTile(gn);
+            for (int il = 0; il < dm->lmt; il++) {
+                const int gm = il * dm->P + dm->prow;
+                if (part == dplasmaLower && gm < gn) continue;
+                if (part == dplasmaUpper && gm > gn) continue;
+                const int tm = dm->rowsOfTile(gm);
+                double* dev = dm->tile(il, jl);
+                double* usr = user + (size_t)il * dm->mb + (size_t)jl * dm->nb * lld;
+                if (dir == 0)
+                    DPB_CUDA(cudaMemcpy2DAsync(dev, (size_t)dm->mb * 8, usr, lld * 8, (size_t)tm * 8, tn,
+                                               cudaMemcpyDefault, s));
+                else
+                    DPB_CUDA(cudaMemcpy2DAsync(usr, lld * 8, dev, (size_t)dm->mb * 8, (size_t)tm * 8, tn,
+                                               cudaMemcpyDefault, s));
+            }
+        }
+    }
+    return 0;
+}
+
+int stage_in(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, bool copyData, int uploOnly) {
+    int rc = describe(A, dm);
+    if (rc) {
+        fprintf(stderr, "dplasma_b200: unsupported descriptor (code %d)\n", rc);
+        return -100 + rc;
+    }
+    const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
+    if (!bc->mat) return -110;
+    const bool regular = A->storage == PARSEC_MATRIX_TILE && bc->uplo == dplasmaUpperLower;
+    if (regular && is_device_ptr(bc->mat)) {
+        dm->base = (double*)bc->mat;
+        dm->owned = false;
+        return 0;
+    }
+    size_t elems = (size_t)dm->lmt * dm->lnt * dm->tileElems;
+    if (elems == 0) elems = 1;
+    DPB_CUDA(cudaMalloc(&dm->base, elems * sizeof(double)));
+    dm->owned = true;
+    if (copyData) return copy_layout(ctx, A, dm, 0, uploOnly);
+    return 0;
+}
+
+int stage_out(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int uploOnly) {
+    if (!dm->owned) return 0;
+    return copy_layout(ctx, A, dm, 1, uploOnly);
+}
+
+void stage_free(DevMatrix* dm) {
+    if (dm->owned && dm->base) cudaFree(dm->base);
+    dm->base = nullptr;
+    dm->owned = false;
+}
+
+}  // namespace dpb

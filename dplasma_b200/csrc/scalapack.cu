@@ -1,0 +1,76 @@
+// ScaLAPACK-compatible entry point pdpotrf_ (src/scalapack_wrappers/dplasma_wrapper_pdpotrf.c:133-297):
+// Fortran calling convention, ScaLAPACK array descriptor, block-cyclic LAPACK-storage local
+// array owned by the caller.  The reference wraps the caller's memory zero-copy in a
+// parsec_matrix_block_cyclic (LAPACK storage) descriptor (:177-188); here the same descriptor
+// is built and the blocking dplasma_dpotrf stages it through the GPU tile grid.
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include "internal.h"
+
+namespace {
+struct GridInfo { int nprow, npcol, myrow, mycol; };
+std::map<int, GridInfo> g_grids;
+parsec_context_t* g_wrapper_ctx = nullptr;
+bool g_wrapper_owned = false;
+}  // namespace
+
+extern "C" {
+
+void dplasma_b200_blacs_gridinit(int ictxt, int nprow, int npcol, int myrow, int mycol) {
+    g_grids[ictxt] = GridInfo{nprow, npcol, myrow, mycol};
+}
+
+// parsec_init_wrapper_ / parsec_fini_wrapper_: dplasma_wrapper_parsec_init.c:98-124
+void parsec_init_wrapper_(void) {
+    if (!g_wrapper_ctx) {
+        g_wrapper_ctx = parsec_init(-1, nullptr, nullptr);
+        g_wrapper_owned = true;
+    }
+}
+void parsec_fini_wrapper_(void) {
+    if (g_wrapper_ctx && g_wrapper_owned) parsec_fini(&g_wrapper_ctx);
+    g_wrapper_ctx = nullptr;
+}
+// lets an application that already owns a context (and its NCCL communicators) lend it to the wrapper
+void dplasma_b200_wrapper_set_context(parsec_context_t* ctx) {
+    g_wrapper_ctx = ctx;
+    g_wrapper_owned = false;
+}
+
+void pdpotrf_(char* UPLO, int* N, double* A, int* IA, int* JA, int* DESCA, int* info) {
+    *info = 0;                      // :146
+    if (*N == 0) return;            // :148-150
+    const int ictxt = DESCA[1], gM = DESCA[2], gN = DESCA[3], MB = DESCA[4], NB = DESCA[5];
+    const int RSRC = DESCA[6], CSRC = DESCA[7], LLD = DESCA[8];  // common.h:283-292
+    GridInfo g{1, 1, 0, 0};
+    auto it = g_grids.find(ictxt);
+    if (it != g_grids.end()) g = it->second;
+    if (MB != NB) {
+        fprintf(stderr, "pdpotrf_: square blocks required (MB=%d NB=%d)\n", MB, NB);  // :83
+        *info = -606;
+        return;
+    }
+    if ((*IA - 1) % MB != 0 || (*JA - 1) % NB != 0 || *IA != 1 || *JA != 1 || *N != gM || *N != gN) {
+        // the reference asserts tile-aligned offsets (:209-211); sub-matrix views are not built here
+        fprintf(stderr, "pdpotrf_: only IA=JA=1 and N equal to the global size are supported\n");
+        *info = -4;
+        return;
+    }
+    const char u = *UPLO;
+    const int uplo = (u == 'U' || u == 'u') ? dplasmaUpper : dplasmaLower;
+    if (!g_wrapper_ctx) parsec_init_wrapper_();
+    if (!g_wrapper_ctx) { *info = -1000; return; }
+    const int rank = g.myrow * g.npcol + g.mycol;
+    parsec_matrix_block_cyclic_t dcA;
+    // numroc for the local column count (common.h:235-263)
+    parsec_matrix_block_cyclic_lapack_init(&dcA, PARSEC_MATRIX_DOUBLE, PARSEC_MATRIX_LAPACK, rank, MB, NB, gM, gN, 0, 0,
+                                           *N, *N, g.nprow, g.npcol, 1, 1, RSRC, CSRC, LLD, 0);
+    dcA.super.lln = dcA.super.sln;
+    dcA.mat = A;
+    // NB: like the reference wrapper (:219-222) the local info is returned without a MAX-reduce
+    int rc = dplasma_dpotrf(g_wrapper_ctx, uplo, (parsec_tiled_matrix_t*)&dcA);
+    *info = rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,170 @@
+// Tile-level operations built on the DMMA engine: the recursive in-tile Cholesky, the panel
+// triangular solve through inverted diagonal blocks, and the kernel-seam entry points that
+// take the place of the reference's per-tile cuSOLVER / cuBLAS calls
+// (src/zpotrf_L.jdf:143,236-240,342-346,463-468).
+#include <cstdio>
+#include "internal.h"
+
+namespace dpb {
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// C = beta*C + alpha * op(A) * op(B)^T over a batch of equally strided problems.
+//   aK / bK : operand stored K-major (op(A)(i,k) at A[k + i*lda]) instead of M-major (A[i + k*lda])
+//   lower   : touch only i >= j (SYRK)
+int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, double alpha, const double* A,
+                int lda, bool aK, const double* B, int ldb, bool bK, double beta, double* C, int ldc,
+                int lower, int batch, long long sA, long long sB, long long sC, int lastBatchM) {
+    if (M <= 0 || N <= 0 || batch <= 0) return 0;
+    if (lastBatchM < 0) lastBatchM = M;
+    GemmDesc d;
+    d.mode = GEMM_SINGLE;
+    d.alpha = alpha; d.beta = beta; d.K = K;
+    d.a_kmajor = aK; d.b_kmajor = bK;
+    d.kTile = 1 << 30; d.aKTileStride = d.bKTileStride = 0;
+    d.A = A; d.B = B; d.C = C;
+    d.M = M; d.N = N; d.lda = lda; d.ldb = ldb; d.ldc = ldc;
+    d.lower = lower; d.rowOff = d.colOff = 0;
+    d.batch = batch; d.batchStrideA = sA; d.batchStrideB = sB; d.batchStrideC = sC;
+    d.lastBatchM = lastBatchM;
+    d.fast = (!aK && !bK && (K % 16 == 0) && (lda % 2 == 0) && (ldb % 2 == 0) && aligned16(A) &&
+              aligned16(B) && (sA % 2 == 0) && (sB % 2 == 0))
+                 ? 1 : 0;
+    // tile configuration: the 128x128 CTA tile only when it still fills the machine
+    const long long bigItems = (long long)((M + 127) / 128) * ((N + 127) / 128) * batch;
+    const bool small = bigItems < 120;
+    const int bm = small ? 64 : 128;
+    d.gridM = (M + bm - 1) / bm;
+    d.gridN = (N + bm - 1) / bm;
+    const long long items = (long long)d.gridM * d.gridN * batch;
+    ctx->launches++;
+    return gemm_launch(d, (int)items, small, s);
+}
+
+int ensure_winv(parsec_context_s* ctx, int nb) {
+    const size_t slot = (size_t)((nb + IB - 1) / IB) * IB * IB;
+    if (ctx->wInv && ctx->wInvSlot >= slot) return 0;
+    if (ctx->wInv) cudaFree(ctx->wInv);
+    ctx->wInv = nullptr;
+    DPB_CUDA(cudaMalloc(&ctx->wInv, 2 * slot * sizeof(double)));
+    ctx->wInvSlot = slot;
+    return 0;
+}
+int ensure_wnorm(parsec_context_s* ctx, size_t n) {
+    if (ctx->wNorm && ctx->wNormLen >= n) return 0;
+    if (ctx->wNorm) cudaFree(ctx->wNorm);
+    ctx->wNorm = nullptr;
+    DPB_CUDA(cudaMalloc(&ctx->wNorm, (n + 8) * sizeof(double)));
+    ctx->wNormLen = n;
+    return 0;
+}
+
+// split point of the recursion: a multiple of IB, about half
+static inline int split_of(int n) {
+    int blocks = (n + IB - 1) / IB;
+    return (blocks / 2) * IB;
+}
+
+// B(:, j0:j0+n) <- B(:, j0:j0+n) * L(j0:j0+n, j0:j0+n)^-T, L lower triangular with the inverses
+// of its IB x IB diagonal blocks in winv (block b at winv + b*IB*IB, ld IB).
+static int trsm_rec(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, const double* winv, int j0,
+                    int n, double* B, int ldb, int M, int batch, long long strideB, int lastBatchM) {
+    if (n <= IB) {
+        // in place: every CTA owns whole rows and has consumed all of A before its epilogue
+        return gemm_single(ctx, s, M, n, n, 1.0, B + (size_t)j0 * ldb, ldb, false,
+                           winv + (size_t)(j0 / IB) * IB * IB, IB, false, 0.0, B + (size_t)j0 * ldb, ldb, 0,
+                           batch, strideB, 0, strideB, lastBatchM);
+    }
+    const int n1 = split_of(n), n2 = n - n1;
+    int rc = trsm_rec(ctx, s, L, ldl, winv, j0, n1, B, ldb, M, batch, strideB, lastBatchM);
+    if (rc) return rc;
+    rc = gemm_single(ctx, s, M, n2, n1, -1.0, B + (size_t)j0 * ldb, ldb, false,
+                     L + (j0 + n1) + (size_t)j0 * ldl, ldl, false, 1.0, B + (size_t)(j0 + n1) * ldb, ldb, 0,
+                     batch, strideB, 0, strideB, lastBatchM);
+    if (rc) return rc;
+    return trsm_rec(ctx, s, L, ldl, winv, j0 + n1, n2, B, ldb, M, batch, strideB, lastBatchM);
+}
+
+int trsm_panel_lower(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, int n, const double* winv,
+                     double* B, int ldb, int M, int batch, long long strideB, int lastBatchM) {
+    if (batch <= 0 || M <= 0) return 0;
+    return trsm_rec(ctx, s, L, ldl, winv, 0, n, B, ldb, M, batch, strideB, lastBatchM);
+}
+
+static int potrf_rec(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, double* winv, int j0, int n,
+                     int* dInfo, int infoBase) {
+    double* Ajj = A + j0 + (size_t)j0 * lda;
+    if (n <= IB) return launch_potrf_leaf(ctx, s, Ajj, lda, n, winv + (size_t)(j0 / IB) * IB * IB, dInfo, infoBase + j0);
+    const int n1 = split_of(n), n2 = n - n1;
+    int rc = potrf_rec(ctx, s, A, lda, winv, j0, n1, dInfo, infoBase);
+    if (rc) return rc;
+    // A21 <- A21 * L11^-T
+    double* A21 = A + (j0 + n1) + (size_t)j0 * lda;
+    rc = trsm_rec(ctx, s, Ajj, lda, winv + (size_t)(j0 / IB) * IB * IB, 0, n1, A21, lda, n2, 1, 0, n2);
+    if (rc) return rc;
+    // A22 <- A22 - A21 A21^T (lower)
+    double* A22 = A + (j0 + n1) + (size_t)(j0 + n1) * lda;
+    rc = gemm_single(ctx, s, n2, n2, n1, -1.0, A21, lda, false, A21, lda, false, 1.0, A22, lda, 1);
+    if (rc) return rc;
+    return potrf_rec(ctx, s, A, lda, winv, j0 + n1, n2, dInfo, infoBase);
+}
+
+// In-place lower Cholesky of one n x n tile; leaves the inverses of the diagonal IB-blocks
+// in winv for the panel solve that follows.
+int potrf_tile_lower(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv, int* dInfo,
+                     int infoBase) {
+    if (n <= 0) return 0;
+    return potrf_rec(ctx, s, A, lda, winv, 0, n, dInfo, infoBase);
+}
+
+}  // namespace dpb
+
+using namespace dpb;
+
+extern "C" {
+
+int dplasma_b200_dpotrf_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t uplo, int n, double* A, int lda,
+                             int* d_info, int info_offset) {
+    if (!ctx) return -1;
+    if (uplo != dplasmaLower && uplo != dplasmaUpper) return -3;
+    if (n < 0) return -4;
+    if (lda < (n > 1 ? n : 1)) return -6;
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = ensure_winv(ctx, n);
+    if (rc) return rc;
+    int* info = d_info ? d_info : ctx->dInfo + 2;
+    if (uplo == dplasmaLower) return potrf_tile_lower(ctx, s, A, lda, n, ctx->wInv, info, info_offset);
+    // Upper: factor the transposed tile (U = L^T) in a scratch tile
+    double* tmp = nullptr;
+    DPB_CUDA(cudaMallocAsync(&tmp, (size_t)n * n * sizeof(double), s));
+    rc = launch_transpose(ctx, s, A, lda, tmp, n, n, n);
+    if (!rc) rc = potrf_tile_lower(ctx, s, tmp, n, n, ctx->wInv, info, info_offset);
+    // only the upper triangle of A is ours to write: transpose the lower factor back into it
+    if (!rc) rc = launch_transpose_upper_into(ctx, s, tmp, n, A, lda, n);
+    cudaFreeAsync(tmp, s);
+    return rc;
+}
+
+int dplasma_b200_dsyrk_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t uplo, dplasma_enum_t trans, int n,
+                            int k, double alpha, const double* A, int lda, double beta, double* C, int ldc) {
+    if (!ctx) return -1;
+    if (uplo != dplasmaLower && uplo != dplasmaUpper) return -3;
+    cudaStream_t s = (cudaStream_t)stream;
+    const bool aK = trans != dplasmaNoTrans;  // C = alpha A^T A + beta C : op(A)(i,kk) = A[kk + i*lda]
+    if (uplo == dplasmaLower) return gemm_single(ctx, s, n, n, k, alpha, A, lda, aK, A, lda, aK, beta, C, ldc, 1);
+    return gemm_single(ctx, s, n, n, k, alpha, A, lda, aK, A, lda, aK, beta, C, ldc, 2);
+}
+
+int dplasma_b200_dgemm_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t transA, dplasma_enum_t transB,
+                            int m, int n, int k, double alpha, const double* A, int lda, const double* B, int ldb,
+                            double beta, double* C, int ldc) {
+    if (!ctx) return -1;
+    cudaStream_t s = (cudaStream_t)stream;
+    // engine form: C[i][j] = sum_kk A'[i][kk] B'[j][kk].  A' = op(A): NoTrans -> M-major, Trans -> K-major.
+    // B'[j][kk] = op(B)[kk][j]: NoTrans -> B[kk + j*ldb] (K-major), Trans -> B[j + kk*ldb] (M-major).
+    const bool aK = transA != dplasmaNoTrans;
+    const bool bK = transB == dplasmaNoTrans;
+    return gemm_single(ctx, s, m, n, k, alpha, A, lda, aK, B, ldb, bK, beta, C, ldc, 0);
+}
+
+}  // extern "C"

@@ -1,0 +1,368 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle and the
+golden fixtures, on the same seeded inputs.  Tolerances:
+  * generators: bit-exact;
+  * factor / solve values: 1e-11 relative to max|.| (fp64, different summation order);
+  * the reference's own acceptance test: residual <= 60 (src/dplasma_zcheck.c:119,215)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import dplasma_b200 as dp
+from oracle.oracle import NoTrans, Trans, NonUnit, Unit, Left, Right
+from tests.util import full_to_local, local_to_full, lapack_local
+
+pytestmark = pytest.mark.gpu
+Lower, Upper, UpperLower = dp.Lower, dp.Upper, dp.UpperLower
+SEED_A, SEED_B, SEED_B_POSV = 3872, 3873, 2354
+VTOL = 1e-11
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = dp.Context()
+    yield c
+    c.close()
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+def make_host(ctx, A, mb, nb, kind="tile", uplo=UpperLower):
+    M, N = A.shape
+    d = dp.BlockCyclic(ctx.lib, M, N, mb, nb, kind=kind, uplo=uplo, where="host")
+    d.host_array()[:d.elems] = full_to_local(A, mb, nb, sym_uplo=(uplo if kind == "sym" else None))
+    return d
+
+
+def read_host(d, M, N, mb, nb, kind="tile", uplo=UpperLower, out=None):
+    return local_to_full(d.host_array()[:d.elems], M, N, mb, nb, sym_uplo=(uplo if kind == "sym" else None), out=out)
+
+
+# ------------------------------------------------------------------ generators (bit-exact)
+@pytest.mark.parametrize("N,nb", [(8, 4), (378, 93), (1024, 128)])
+@pytest.mark.parametrize("uplo", [Lower, Upper, UpperLower])
+def test_dplgsy_bit_exact(ctx, oracle, golden, N, nb, uplo):
+    d = dp.BlockCyclic(ctx.lib, N, N, nb, nb, where="host")
+    d.host_array()[:] = 0.0
+    assert ctx.lib.dplasma_dplgsy(ctx.ptr, float(N), uplo, d.ref, SEED_A) == 0
+    got = read_host(d, N, N, nb, nb)
+    want = oracle.plgsy(float(N), uplo, N, nb, SEED_A)
+    assert np.array_equal(got, want)
+    if N == 8 and uplo == UpperLower:
+        assert np.array_equal(got, golden["d8_A"])
+    if N == 378 and uplo == Lower:
+        assert np.array_equal(got.ravel(order="F")[::31], golden["d378_A0_L_s31"])
+    d.free()
+
+
+def test_dplgsy_sym_descriptor_and_dplrnt(ctx, oracle, golden):
+    N, nb = 378, 93
+    d = dp.BlockCyclic(ctx.lib, N, N, nb, nb, kind="sym", uplo=Lower, where="host")
+    assert ctx.lib.dplasma_dplgsy(ctx.ptr, float(N), Lower, d.ref, SEED_A) == 0
+    got = read_host(d, N, N, nb, nb, "sym", Lower)
+    assert np.array_equal(got, oracle.plgsy(float(N), Lower, N, nb, SEED_A))
+    d.free()
+    b = dp.BlockCyclic(ctx.lib, N, 367, nb, nb, where="host")
+    assert ctx.lib.dplasma_dplrnt(ctx.ptr, 0, b.ref, SEED_B_POSV) == 0
+    got = read_host(b, N, 367, nb, nb)
+    assert np.array_equal(got, oracle.plrnt(N, 367, nb, nb, SEED_B_POSV))
+    assert np.array_equal(got.ravel(order="F")[::41], golden["d378_B_s41"])
+    b.free()
+
+
+# ------------------------------------------------------------------ kernel seam (B2)
+def dev(t):
+    return C.c_void_p(t.data_ptr())
+
+
+@pytest.mark.parametrize("m,n,k", [(128, 128, 128), (512, 512, 512), (93, 93, 93), (6, 93, 93), (200, 136, 64), (1024, 256, 512)])
+def test_dgemm_tile_matches_oracle(ctx, oracle, m, n, k):
+    import torch
+    rng = np.random.default_rng(m * 7 + n)
+    A = np.asfortranarray(rng.standard_normal((m, k)))
+    B = np.asfortranarray(rng.standard_normal((n, k)))
+    C0 = np.asfortranarray(rng.standard_normal((m, n)))
+    want = C0.copy(order="F")
+    oracle.gemm_tile(NoTrans, Trans, -1.0, A, B, 1.0, want)   # the K4 form: C -= A B^T
+    tA, tB, tC = (torch.from_numpy(x.T.copy()).cuda() for x in (A, B, C0))  # row-major of X^T == col-major of X
+    rc = ctx.lib.dplasma_b200_dgemm_tile(ctx.ptr, None, NoTrans, Trans, m, n, k, -1.0, dev(tA), m, dev(tB), n, 1.0, dev(tC), m)
+    assert rc == 0
+    torch.cuda.synchronize()
+    got = tC.cpu().numpy().T
+    assert relerr(got, want) < 1e-13
+    # general transposes go through the element-wise producer: C = 0.5 A^T B + 2 C
+    A2 = np.asfortranarray(rng.standard_normal((k, m)))
+    B2 = np.asfortranarray(rng.standard_normal((k, n)))
+    want = C0.copy(order="F")
+    oracle.gemm_tile(Trans, NoTrans, 0.5, A2, B2, 2.0, want)
+    tA, tB, tC = (torch.from_numpy(x.T.copy()).cuda() for x in (A2, B2, C0))
+    assert ctx.lib.dplasma_b200_dgemm_tile(ctx.ptr, None, Trans, NoTrans, m, n, k, 0.5, dev(tA), k, dev(tB), k, 2.0, dev(tC), m) == 0
+    torch.cuda.synchronize()
+    assert relerr(tC.cpu().numpy().T, want) < 1e-13
+
+
+@pytest.mark.parametrize("n,k", [(512, 512), (93, 93), (256, 64)])
+def test_dsyrk_tile_lower_only(ctx, oracle, n, k):
+    import torch
+    rng = np.random.default_rng(n)
+    A = np.asfortranarray(rng.standard_normal((n, k)))
+    C0 = np.asfortranarray(rng.standard_normal((n, n)))
+    want = C0.copy(order="F")
+    oracle.herk_tile(Lower, NoTrans, -1.0, A, 1.0, want)      # K3
+    tA, tC = (torch.from_numpy(x.T.copy()).cuda() for x in (A, C0))
+    assert ctx.lib.dplasma_b200_dsyrk_tile(ctx.ptr, None, Lower, NoTrans, n, k, -1.0, dev(tA), n, 1.0, dev(tC), n) == 0
+    torch.cuda.synchronize()
+    got = tC.cpu().numpy().T
+    assert relerr(np.tril(got), np.tril(want)) < 1e-13
+    assert np.array_equal(np.triu(got, 1), np.triu(C0, 1))   # strict upper part untouched
+
+
+@pytest.mark.parametrize("n", [64, 93, 512, 1024])
+@pytest.mark.parametrize("uplo", [Lower, Upper])
+def test_dpotrf_tile(ctx, oracle, n, uplo):
+    import torch
+    A0 = oracle.plgsy(float(n), UpperLower, n, n, 11)
+    want = A0.copy(order="F")
+    assert oracle.potrf_tile(uplo, want) == 0
+    tA = torch.from_numpy(A0.T.copy()).cuda()
+    info = torch.zeros(1, dtype=torch.int32, device="cuda")
+    assert ctx.lib.dplasma_b200_dpotrf_tile(ctx.ptr, None, uplo, n, dev(tA), n, dev(info), 0) == 0
+    torch.cuda.synchronize()
+    got = tA.cpu().numpy().T
+    assert int(info.item()) == 0
+    tri = np.tril if uplo == Lower else np.triu
+    assert relerr(tri(got), tri(want)) < VTOL
+    other = (lambda M: np.triu(M, 1)) if uplo == Lower else (lambda M: np.tril(M, -1))
+    assert np.array_equal(other(got), other(A0))              # the other triangle is untouched
+    # not positive definite -> info = offset + index of first bad pivot (src/zpotrf_L.jdf:180-182)
+    Abad = A0.copy(order="F")
+    j = n // 2
+    Abad[j, j] = -1.0
+    ref = Abad.copy(order="F")
+    winfo = oracle.potrf_tile(uplo, ref)
+    tA = torch.from_numpy(Abad.T.copy()).cuda()
+    info.zero_()
+    assert ctx.lib.dplasma_b200_dpotrf_tile(ctx.ptr, None, uplo, n, dev(tA), n, dev(info), 1000) == 0
+    torch.cuda.synchronize()
+    assert int(info.item()) == 1000 + winfo == 1000 + j + 1
+
+
+@pytest.mark.parametrize("m,n", [(512, 512), (93, 93), (6, 93), (1000, 256)])
+def test_dtrsm_tile_right_lower_trans(ctx, oracle, m, n):
+    import torch
+    rng = np.random.default_rng(m + n)
+    T = oracle.plgsy(float(n), UpperLower, n, n, 5)
+    assert oracle.potrf_tile(Lower, T) == 0
+    B0 = np.asfortranarray(rng.standard_normal((m, n)))
+    want = B0.copy(order="F")
+    oracle.trsm_tile(Right, Lower, Trans, NonUnit, 1.0, T, want)   # K2
+    tT, tB = (torch.from_numpy(x.T.copy()).cuda() for x in (T, B0))
+    assert ctx.lib.dplasma_b200_dtrsm_tile(ctx.ptr, None, Right, Lower, Trans, NonUnit, m, n, 1.0, dev(tT), n, dev(tB), m) == 0
+    torch.cuda.synchronize()
+    assert relerr(tB.cpu().numpy().T, want) < VTOL
+
+
+@pytest.mark.parametrize("uplo,trans", [(Lower, NoTrans), (Lower, Trans), (Upper, NoTrans), (Upper, Trans)])
+@pytest.mark.parametrize("m,n,diag", [(256, 100, NonUnit), (93, 37, NonUnit), (130, 64, Unit)])
+def test_dtrsm_tile_left(ctx, oracle, uplo, trans, m, n, diag):
+    import torch
+    rng = np.random.default_rng(m * n)
+    T = oracle.plgsy(float(m), UpperLower, m, m, 5)
+    assert oracle.potrf_tile(uplo, T) == 0
+    if diag == Unit:
+        T = np.asfortranarray(T / 50.0)
+    B0 = np.asfortranarray(rng.standard_normal((m, n)))
+    want = B0.copy(order="F")
+    oracle.trsm_tile(Left, uplo, trans, diag, 0.75, T, want)      # CORE_ztrsm at ztrsm_LLN.jdf:48
+    tT, tB = (torch.from_numpy(x.T.copy()).cuda() for x in (T, B0))
+    assert ctx.lib.dplasma_b200_dtrsm_tile(ctx.ptr, None, Left, uplo, trans, diag, m, n, 0.75, dev(tT), m, dev(tB), m) == 0
+    torch.cuda.synchronize()
+    assert relerr(tB.cpu().numpy().T, want) < VTOL
+
+
+# ------------------------------------------------------------------ dpotrf: public API
+@pytest.mark.parametrize("name,uplo", [("L", Lower), ("U", Upper)])
+@pytest.mark.parametrize("kind", ["tile", "sym", "lapack"])
+def test_dpotrf_378_93_reference_ctest_case(ctx, oracle, golden, name, uplo, kind):
+    """tests/Testings.cmake:89  testing_dpotrf -N 378 -t 93 (ragged last tile, odd tile size)"""
+    N, nb = 378, 93
+    A0 = oracle.plgsy(float(N), uplo, N, nb, SEED_A)
+    if kind == "lapack":
+        d = dp.BlockCyclic(ctx.lib, N, N, nb, nb, kind="lapack", where="host")
+        d.host_array()[:N * N] = A0.ravel(order="F")
+    else:
+        d = make_host(ctx, A0, nb, nb, kind, uplo)
+    info = ctx.lib.dplasma_dpotrf(ctx.ptr, uplo, d.ref)
+    assert info == 0
+    if kind == "lapack":
+        F = d.host_array()[:N * N].reshape((N, N), order="F").copy(order="F")
+    else:
+        F = read_host(d, N, N, nb, nb, kind, uplo, out=A0.copy(order="F") if kind == "sym" else None)
+    want = A0.copy(order="F")
+    assert oracle.potrf(uplo, want, nb) == 0
+    tri = np.tril if uplo == Lower else np.triu
+    assert relerr(tri(F), tri(want)) < VTOL
+    assert relerr(F.ravel(order="F")[::31], golden[f"d378_F_{name}_s31"]) < VTOL
+    # the reference's own acceptance test, evaluated by the oracle on the GPU result
+    bad, res, _, _ = oracle.check_potrf(uplo, F, A0)
+    assert bad == 0 and res < 60.0
+    d.free()
+
+
+@pytest.mark.parametrize("N,nb", [(1024, 128), (2048, 512), (1536, 256), (1700, 320)])
+@pytest.mark.parametrize("uplo", [Lower, Upper])
+def test_dpotrf_fast_path_vs_oracle(ctx, oracle, N, nb, uplo):
+    A0 = oracle.plgsy(float(N), uplo, N, nb, SEED_A)
+    d = make_host(ctx, A0, nb, nb)
+    assert ctx.lib.dplasma_dpotrf(ctx.ptr, uplo, d.ref) == 0
+    F = read_host(d, N, N, nb, nb)
+    want = A0.copy(order="F")
+    assert oracle.potrf(uplo, want, nb) == 0
+    tri = np.tril if uplo == Lower else np.triu
+    assert relerr(tri(F), tri(want)) < VTOL
+    other = (lambda M: np.triu(M, 1)) if uplo == Lower else (lambda M: np.tril(M, -1))
+    assert np.array_equal(other(F), other(A0))
+    d.free()
+
+
+def test_dpotrf_new_start_wait_destruct_device_resident(ctx, oracle):
+    """the 3-call pattern of tests/common.h:253-267 on a matrix that lives in HBM"""
+    import torch
+    N, nb = 1024, 128
+    A0 = oracle.plgsy(float(N), Lower, N, nb, SEED_A)
+    t = torch.from_numpy(full_to_local(A0, nb, nb)).cuda()
+    d = dp.BlockCyclic(ctx.lib, N, N, nb, nb, where=t.data_ptr())
+    info = C.c_int(-1)
+    tp = ctx.lib.dplasma_dpotrf_New(Lower, d.ref, C.byref(info))
+    assert tp and info.value == 0
+    assert ctx.lib.parsec_context_add_taskpool(ctx.ptr, tp) == 0
+    n0 = ctx.lib.dplasma_b200_kernel_launches(ctx.ptr)
+    assert ctx.lib.parsec_context_start(ctx.ptr) == 0
+    assert ctx.lib.parsec_context_wait(ctx.ptr) == 0
+    ctx.lib.dplasma_dpotrf_Destruct(tp)
+    assert info.value == 0
+    assert ctx.lib.dplasma_b200_kernel_launches(ctx.ptr) > n0
+    assert ctx.lib.dplasma_b200_last_elapsed(ctx.ptr) > 0.0
+    F = local_to_full(t.cpu().numpy(), N, N, nb, nb)
+    want = A0.copy(order="F")
+    oracle.potrf(Lower, want, nb)
+    assert relerr(np.tril(F), np.tril(want)) < VTOL
+
+
+def test_info_semantics(ctx, oracle, golden):
+    N, nb = 200, 64
+    for uplo, key in ((Lower, "d200_nonspd_info_L"), (Upper, "d200_nonspd_info_U")):
+        A = oracle.plgsy(0.0, uplo, N, nb, SEED_A)
+        d = make_host(ctx, A, nb, nb)
+        assert ctx.lib.dplasma_dpotrf(ctx.ptr, uplo, d.ref) == int(golden[key][0])
+        d.free()
+    A = oracle.plgsy(200.0, Lower, N, nb, SEED_A)
+    A[150, 150] = -1.0
+    d = make_host(ctx, A, nb, nb)
+    assert ctx.lib.dplasma_dpotrf(ctx.ptr, Lower, d.ref) == 151 == int(golden["d200_pivot150_info_L"][0])
+    d.free()
+    # bad uplo: New fails -> -101 like the reference's blocking wrappers
+    d = make_host(ctx, A, nb, nb)
+    assert ctx.lib.dplasma_dpotrf(ctx.ptr, 999, d.ref) == -101
+    d.free()
+
+
+# ------------------------------------------------------------------ checks and solves
+@pytest.mark.parametrize("uplo", [Lower, Upper])
+def test_checks_match_oracle(ctx, oracle, uplo):
+    N, nb, K = 378, 93, 367
+    A0 = oracle.plgsy(float(N), uplo, N, nb, SEED_A)
+    F = A0.copy(order="F")
+    oracle.potrf(uplo, F, nb)
+    dF, dA0 = make_host(ctx, F, nb, nb), make_host(ctx, A0, nb, nb)
+    assert ctx.lib.check_dpotrf(ctx.ptr, 0, uplo, dF.ref, dA0.ref) == 0
+    res = ctx.lib.dplasma_b200_last_check_result(ctx.ptr)
+    _, want, _, anorm = oracle.check_potrf(uplo, F, A0)
+    assert 0.0 <= res < 60.0 and abs(res - want) < 0.5 * max(want, 0.05)
+    assert ctx.lib.dplasma_dlansy(ctx.ptr, dp.InfNorm, uplo, dA0.ref) == pytest.approx(anorm, rel=1e-13)
+    # a corrupted factor must be flagged
+    Fbad = F.copy(order="F")
+    Fbad[200, 200] += 1e-3
+    dFb = make_host(ctx, Fbad, nb, nb)
+    assert ctx.lib.check_dpotrf(ctx.ptr, 0, uplo, dFb.ref, dA0.ref) == 1
+    # solve residual
+    B = oracle.plrnt(N, K, nb, nb, SEED_B_POSV)
+    X = B.copy(order="F")
+    oracle.potrs(uplo, F, X, nb, nb)
+    dB, dX = make_host(ctx, B, nb, nb), make_host(ctx, X, nb, nb)
+    assert ctx.lib.dplasma_dlange(ctx.ptr, dp.InfNorm, dB.ref) == pytest.approx(oracle.lange_inf(B), rel=1e-13)
+    assert ctx.lib.check_daxmb(ctx.ptr, 0, uplo, dA0.ref, dB.ref, dX.ref) == 0
+    res = ctx.lib.dplasma_b200_last_check_result(ctx.ptr)
+    _, want = oracle.check_axmb(uplo, A0, B.copy(order="F"), X)
+    assert 0.0 <= res < 60.0 and abs(res - want) < 0.5 * max(want, 0.05)
+    for d in (dF, dA0, dFb, dB, dX):
+        d.free()
+
+
+@pytest.mark.parametrize("name,uplo", [("L", Lower), ("U", Upper)])
+def test_dposv_378_93_367(ctx, oracle, golden, name, uplo):
+    """tests/Testings.cmake:90  testing_dposv -N 378 -t 93 -K 367"""
+    N, nb, K = 378, 93, 367
+    A0 = oracle.plgsy(float(N), uplo, N, nb, SEED_A)
+    B = oracle.plrnt(N, K, nb, nb, SEED_B_POSV)
+    dA, dB = make_host(ctx, A0, nb, nb), make_host(ctx, B, nb, nb)
+    assert ctx.lib.dplasma_dposv(ctx.ptr, uplo, dA.ref, dB.ref) == 0
+    X = read_host(dB, N, K, nb, nb)
+    want = B.copy(order="F")
+    Aw = A0.copy(order="F")
+    assert oracle.posv(uplo, Aw, want, nb, nb) == 0
+    assert relerr(X, want) < 1e-10
+    assert relerr(X.ravel(order="F")[::41], golden[f"d378_X_{name}_s41"]) < 1e-10
+    bad, res = oracle.check_axmb(uplo, A0, B.copy(order="F"), X)
+    assert bad == 0 and res < 60.0
+    dA.free(); dB.free()
+
+
+@pytest.mark.parametrize("uplo,trans", [(Lower, NoTrans), (Lower, Trans), (Upper, NoTrans), (Upper, Trans)])
+def test_dtrsm_tiled_left(ctx, oracle, uplo, trans):
+    N, nb, K, nbr = 300, 64, 100, 48
+    T = oracle.plgsy(float(N), uplo, N, nb, SEED_A)
+    oracle.potrf(uplo, T, nb)
+    B = oracle.plrnt(N, K, nb, nbr, 7)
+    want = B.copy(order="F")
+    assert oracle.trsm(Left, uplo, trans, NonUnit, 1.5, T, want, nb, nbr) == 0
+    dT, dB = make_host(ctx, T, nb, nb), make_host(ctx, B, nb, nbr)
+    assert ctx.lib.dplasma_dtrsm(ctx.ptr, Left, uplo, trans, NonUnit, 1.5, dT.ref, dB.ref) == 0
+    assert relerr(read_host(dB, N, K, nb, nbr), want) < 1e-10
+    dT.free(); dB.free()
+
+
+def test_pdpotrf_single_process(ctx, oracle):
+    """tools/cscalapack/pdpotrf.c:94: pdpotrf_("L", &n, A, &i1, &i1, descA, &info) on a 1x1 grid"""
+    N, nb = 500, 64
+    A0 = oracle.plgsy(float(N), UpperLower, N, nb, SEED_A)
+    for u, uplo in ((b"L", Lower), (b"U", Upper)):
+        A = np.asfortranarray(A0.copy())
+        ctx.lib.dplasma_b200_blacs_gridinit(0, 1, 1, 0, 0)
+        desc = (C.c_int * 9)(1, 0, N, N, nb, nb, 0, 0, N)
+        n, one, info = C.c_int(N), C.c_int(1), C.c_int(-7)
+        ctx.lib.pdpotrf_(u, C.byref(n), A.ctypes.data_as(C.c_void_p), C.byref(one), C.byref(one), desc, C.byref(info))
+        assert info.value == 0
+        want = A0.copy(order="F")
+        oracle.potrf(uplo, want, nb)
+        tri = np.tril if uplo == Lower else np.triu
+        assert relerr(tri(A), tri(want)) < VTOL
+
+
+# ------------------------------------------------------------------ BASELINE sizes through properties
+@pytest.mark.parametrize("N,nb", [(4096, 256), (32768, 512)])
+def test_baseline_configs_residual_on_gpu(ctx, N, nb):
+    """C1 / C2 of BASELINE.json: generate in HBM, factor in place, evaluate the reference's
+    check (||L L^T - A|| / (||A|| N eps) <= 60) on the GPU."""
+    lib = ctx.lib
+    dA = dp.BlockCyclic(lib, N, N, nb, nb, where="device")
+    dA0 = dp.BlockCyclic(lib, N, N, nb, nb, where="device")
+    assert lib.dplasma_dplgsy(ctx.ptr, float(N), Lower, dA.ref, SEED_A) == 0
+    assert lib.dplasma_dplgsy(ctx.ptr, float(N), Lower, dA0.ref, SEED_A) == 0
+    assert lib.dplasma_dpotrf(ctx.ptr, Lower, dA.ref) == 0
+    assert lib.check_dpotrf(ctx.ptr, 0, Lower, dA.ref, dA0.ref) == 0
+    res = lib.dplasma_b200_last_check_result(ctx.ptr)
+    assert 0.0 < res < 60.0
+    dA.free(); dA0.free()
