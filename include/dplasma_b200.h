@@ -193,6 +193,15 @@ long long dplasma_b200_kernel_launches(parsec_context_t *parsec);
  * info_offset + j + 1 for the first non-positive pivot j if it was 0 before. */
 int dplasma_b200_dpotrf_tile(parsec_context_t *ctx, void *stream, dplasma_enum_t uplo, int n, double *A,
                              int lda, int *d_info, int info_offset);
+/* No counterpart in the reference.  Same computation as dplasma_b200_dpotrf_tile(Lower) for
+ * callers that are not allowed to allocate device memory (a task body under a runtime that
+ * owns the whole HBM, a no-sync inner loop, a fixed memory budget): the workspace lives in a
+ * 512 KiB array inside the library image, so n <= 1024, nothing is allocated or freed, and no
+ * context is needed.  d_info is required.  The first call on a device performs a one-time
+ * set-up and must happen outside stream capture; calls that overlap on the GPU race on the
+ * shared workspace.  Returns 0, a cudaError_t, or a negative argument index (-3: n too large). */
+int dplasma_b200_dpotrf_tile_noalloc(void *stream, dplasma_enum_t uplo, int n, double *A, int lda,
+                                     int *d_info, int info_offset);
 /* cublasDtrsm, src/zpotrf_L.jdf:236-240 (K2).  Right/Lower/Trans/NonUnit and
  * Left/Upper/Trans/NonUnit as used by the factorization, and Left/{Lower,Upper}/{N,T} as
  * used by the solves (CORE_ztrsm at src/ztrsm_LLN.jdf:48). */
