@@ -295,7 +295,7 @@ def run_ours(args):
     # ---- CPU baseline beside it (rank 0, N=1 only): the reference's own tile kernels ----
     cpu = None
     if rank == 0 and n_gpus == 1 and not args.no_cpu:
-        cn, cnb = 12288, 256
+        cn, cnb = 24576, 256
         kind, cores, blas, ts = cpu_reference_run(cn, cnb, 1, 0)
         cpu = {"value": flops_dpotrf(cn) / ts[0] / 1e12, "unit": "TFLOP/s", "cores": cores, "kind": kind,
                "sample": f"dpotrf N={cn} NB={cnb} lower, one run of {ts[0]:.1f} s; reference CORE_d* kernels ({blas}) "

@@ -61,7 +61,7 @@ struct GemmDesc {
     long long rowPanelStride, colPanelStride, tileElems;
     int tileLdT;              // local tile rows (stride between tile columns, in tiles)
     int nb;                   // tile size
-    int bpt;                  // CTA blocks per tile edge = ceil(nb / BM)  (BM == BN)
+    int bptM, bptN;           // CTA blocks per tile edge = ceil(nb / BM), ceil(nb / BN)
     int ncols;                // number of local tile columns in this update
     int colFirst;             // first local tile column j0
     int P, Q, prow, pcol;     // process grid and my coordinates: global m = i*P+prow, n = j*Q+pcol
@@ -111,7 +111,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
         : "memory");
 }
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
-    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+    // volatile: keeps every DMMA ordered against the (volatile) mbarrier waits/arrives, see the
+    // stage-release note in the consumer loop
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                  : "+d"(c0), "+d"(c1)
                  : "d"(a), "d"(b));
 }
@@ -119,9 +121,9 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 // ---------------------------------------------------------------------------------------
 // Tile configuration
 // ---------------------------------------------------------------------------------------
-template <int BM_, int BN_, int WM_, int STAGES_>
+template <int BM_, int BN_, int WM_, int STAGES_, int MINB_>
 struct GemmCfg {
-    static constexpr int BM = BM_, BN = BN_, BK = 16, WM = WM_, WN = 32, STAGES = STAGES_;
+    static constexpr int BM = BM_, BN = BN_, BK = 16, WM = WM_, WN = 32, STAGES = STAGES_, MINB = MINB_;
     static constexpr int MF = WM / 8, NF = WN / 8;  // 8x8 fragments per warp tile
     static constexpr int WARPS_M = BM / WM, WARPS_N = BN / WN;
     static constexpr int CONSUMER_WARPS = WARPS_M * WARPS_N;
@@ -134,8 +136,10 @@ struct GemmCfg {
     static constexpr int A_STAGE = BK * LDA_S, B_STAGE = BK * LDB_S;  // doubles
     static constexpr size_t SMEM = (size_t)STAGES * (A_STAGE + B_STAGE) * 8 + 2 * STAGES * 8 + 16;
 };
-using CfgBig = GemmCfg<128, 128, 64, 4>;   // 8 consumer warps, 64x32 warp tiles, 134 KB smem
-using CfgSmall = GemmCfg<64, 64, 32, 4>;   // 4 consumer warps, 32x32 warp tiles, 70 KB smem
+using CfgBig = GemmCfg<128, 128, 64, 4, 1>;   // 8 consumer warps, 64x32 warp tiles, 134 KB smem, 1 CTA/SM
+using CfgWide = GemmCfg<128, 64, 64, 4, 2>;   // 4 consumer warps, 64x32 warp tiles, 101 KB smem, 2 CTAs/SM
+using CfgSmall = GemmCfg<64, 64, 32, 4, 3>;   // 4 consumer warps, 32x32 warp tiles, 70 KB smem, 3 CTAs/SM
+enum GemmCfgId : int { CFG_BIG = 0, CFG_WIDE = 1, CFG_SMALL = 2 };
 
 // row (within the warp tile) of fragment f, fragment-row g
 template <int WM>
@@ -192,11 +196,11 @@ __device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
     int c = lo;
     int r = bid - d.itemStart[c];
     int j = d.colFirst + c;                 // local tile column
-    int rowsInCol = (d.rowEnd - d.rowFirst[c]) * d.bpt;   // CTA block-rows in this tile column
+    int rowsInCol = (d.rowEnd - d.rowFirst[c]) * d.bptM;   // CTA block-rows in this tile column
     int bj = r / rowsInCol;                 // CTA block column inside the tile
     int rr = r - bj * rowsInCol;
-    int i = d.rowFirst[c] + rr / d.bpt;     // local tile row
-    int bi = rr - (rr / d.bpt) * d.bpt;
+    int i = d.rowFirst[c] + rr / d.bptM;    // local tile row
+    int bi = rr - (rr / d.bptM) * d.bptM;
     int gm = i * d.P + d.prow, gn = j * d.Q + d.pcol;   // global tile coordinates
     int tm = (gm == d.mtGlobal - 1) ? d.lastM : d.nb;
     int tn = (gn == d.ntGlobal - 1) ? d.lastN : d.nb;
@@ -218,7 +222,7 @@ __device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
 // The kernel
 // ---------------------------------------------------------------------------------------
 template <class Cfg>
-__global__ void __launch_bounds__(Cfg::THREADS, 1) gemm_dmma_kernel(const __grid_constant__ GemmDesc d) {
+__global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(const __grid_constant__ GemmDesc d) {
     constexpr int BM = Cfg::BM, BN = Cfg::BN, BK = Cfg::BK, STAGES = Cfg::STAGES;
     constexpr int LDA_S = Cfg::LDA_S, LDB_S = Cfg::LDB_S, MF = Cfg::MF, NF = Cfg::NF;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -299,11 +303,53 @@ __global__ void __launch_bounds__(Cfg::THREADS, 1) gemm_dmma_kernel(const __grid
     const int g = lane >> 2, t = lane & 3;
     const int wm0 = wm * Cfg::WM, wn0 = wn * Cfg::WN;
 
+    // Accumulators start as (beta/alpha)*C: the read of C overlaps the pipeline fill instead of
+    // sitting, un-overlapped, in the epilogue; the epilogue only stores alpha*acc.
+    // thread holds, for fragment (i,j): rows wm0+frag_row(g,i); columns wn0+frag_col(2t,j) and
+    // wn0+frag_col(2t+1,j)   (the C fragment's column index plays the role of B's g)
+    const double alpha = d.alpha, beta = d.beta;
+    const double cscale = (beta == 0.0) ? 0.0 : beta / alpha;
+    constexpr int RUN = (Cfg::WM == 64) ? 8 : 2;  // contiguous rows a thread owns per fragment group
+    const bool vec = (w.M == BM) && (w.N == BN) && (w.lower == 0) && ((w.ldc & 1) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(w.C) & 15) == 0);
     double acc[MF][NF][2];
+    if (cscale == 0.0) {
 #pragma unroll
-    for (int i = 0; i < MF; i++)
+        for (int i = 0; i < MF; i++)
 #pragma unroll
-        for (int j = 0; j < NF; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+            for (int j = 0; j < NF; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+    } else if (vec) {
+#pragma unroll
+        for (int j = 0; j < NF; j++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const double* cp = w.C + (size_t)(wn0 + frag_col(2 * t + h, j)) * w.ldc + wm0;
+#pragma unroll
+                for (int i = 0; i < MF; i += 2) {
+                    const double2 x = *reinterpret_cast<const double2*>(cp + frag_row<Cfg::WM>(g, i));
+                    acc[i][j][h] = cscale * x.x;
+                    acc[i + 1][j][h] = cscale * x.y;
+                }
+            }
+    } else {
+#pragma unroll
+        for (int j = 0; j < NF; j++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const int col = wn0 + frag_col(2 * t + h, j);
+                const double* cp = w.C + (size_t)col * w.ldc;
+                const int gj = w.gj0 + col;
+#pragma unroll
+                for (int i = 0; i < MF; i++) {
+                    const int row = wm0 + frag_row<Cfg::WM>(g, i);
+                    bool ok = (col < w.N) && (row < w.M);
+                    if (w.lower == 1 && (w.gi0 + row < gj)) ok = false;
+                    if (w.lower == 2 && (w.gi0 + row > gj)) ok = false;
+                    acc[i][j][h] = ok ? cscale * cp[row] : 0.0;
+                }
+            }
+    }
+    (void)RUN;
 
     // per-thread fragment base offsets inside a stage
     const int aoff = (Cfg::WM == 64) ? (wm0 + 8 * g) : (wm0 + 2 * g);
@@ -312,6 +358,11 @@ __global__ void __launch_bounds__(Cfg::THREADS, 1) gemm_dmma_kernel(const __grid
     for (int c = 0; c < nChunks; c++) {
         const int s = c % STAGES;
         mbar_wait(&full[s], (c / STAGES) & 1);
+        // Release the PREVIOUS stage only now.  An arrive issued straight after the last LDS of a
+        // chunk can overtake that load (the arrive does not wait for the LDS scoreboard) and let
+        // the producer's bulk copy overwrite the stage under it.  Behind the spin-wait above, every
+        // DMMA of chunk c-1 -- and therefore every LDS feeding it -- has been issued and completed.
+        if (c > 0 && lane == 0) mbar_arrive(&empty[(c - 1) % STAGES]);
         const double* pA = sA + (size_t)s * Cfg::A_STAGE + aoff;
         const double* pB = sB + (size_t)s * Cfg::B_STAGE + boff;
 #pragma unroll
@@ -342,14 +393,25 @@ __global__ void __launch_bounds__(Cfg::THREADS, 1) gemm_dmma_kernel(const __grid
 #pragma unroll
                 for (int j = 0; j < NF; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[s]);
     }
 
     // ================================ epilogue ================================
-    // thread holds, for fragment (i,j): rows wm0+frag_row(g,i); columns wn0+frag_col(2t,j) and
-    // wn0+frag_col(2t+1,j)   (the C fragment's column index plays the role of B's g)
-    const double alpha = d.alpha, beta = d.beta;
+    if (vec) {
+#pragma unroll
+        for (int j = 0; j < NF; j++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                double* cp = w.C + (size_t)(wn0 + frag_col(2 * t + h, j)) * w.ldc + wm0;
+#pragma unroll
+                for (int i = 0; i < MF; i += 2) {
+                    double2 x;
+                    x.x = alpha * acc[i][j][h];
+                    x.y = alpha * acc[i + 1][j][h];
+                    *reinterpret_cast<double2*>(cp + frag_row<Cfg::WM>(g, i)) = x;
+                }
+            }
+        return;
+    }
 #pragma unroll
     for (int j = 0; j < NF; j++) {
 #pragma unroll
@@ -364,16 +426,16 @@ __global__ void __launch_bounds__(Cfg::THREADS, 1) gemm_dmma_kernel(const __grid
                 if (row >= w.M) continue;
                 if (w.lower == 1 && (w.gi0 + row < gj)) continue;
                 if (w.lower == 2 && (w.gi0 + row > gj)) continue;
-                double v = alpha * acc[i][j][h];
-                if (beta != 0.0) v += beta * cp[row];
-                cp[row] = v;
+                cp[row] = alpha * acc[i][j][h];
             }
         }
     }
 }
 
 // host side (gemm_dmma.cu)
-int gemm_launch(const GemmDesc& d, int nItems, bool smallCfg, cudaStream_t stream);
+int gemm_launch(const GemmDesc& d, int nItems, int cfg, cudaStream_t stream);
+int gemm_pick_cfg(long long bigItems);
+void gemm_cfg_dims(int cfg, int* bm, int* bn);
 int gemm_init_attributes();
 
 }  // namespace dpb

@@ -57,12 +57,15 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
         }
         if (tiles == 0) continue;
         const int bptBig = (C.nb + 127) / 128;
-        const bool small = tiles * bptBig * bptBig < 120;
-        d.bpt = small ? (C.nb + 63) / 64 : bptBig;
+        const int cfg = gemm_pick_cfg(tiles * bptBig * bptBig);
+        int bm, bn;
+        gemm_cfg_dims(cfg, &bm, &bn);
+        d.bptM = (C.nb + bm - 1) / bm;
+        d.bptN = (C.nb + bn - 1) / bn;
         long long items = 0;
         for (int c = 0; c < ncols; c++) {
             d.itemStart[c] = (int)items;
-            items += (long long)(rowEnd - d.rowFirst[c]) * d.bpt * d.bpt;
+            items += (long long)(rowEnd - d.rowFirst[c]) * d.bptM * d.bptN;
         }
         d.itemStart[ncols] = (int)items;
         ctx->launches++;
@@ -72,7 +75,7 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
             cudaEventCreate(&pe1);
             cudaEventRecord(pe0, s);
         }
-        int rc = gemm_launch(d, (int)items, small, s);
+        int rc = gemm_launch(d, (int)items, cfg, s);
         if (ctx->profile) {
             cudaEventRecord(pe1, s);
             // algorithmic flops of this launch: 2 nb^2 K per GEMM tile, nb (nb+1) K per SYRK tile

@@ -30,15 +30,16 @@ int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, doub
     d.fast = (!aK && !bK && (K % 16 == 0) && (lda % 2 == 0) && (ldb % 2 == 0) && aligned16(A) &&
               aligned16(B) && (sA % 2 == 0) && (sB % 2 == 0))
                  ? 1 : 0;
-    // tile configuration: the 128x128 CTA tile only when it still fills the machine
+    // tile configuration: the large CTA tiles only when they still fill the machine
     const long long bigItems = (long long)((M + 127) / 128) * ((N + 127) / 128) * batch;
-    const bool small = bigItems < 120;
-    const int bm = small ? 64 : 128;
+    const int cfg = gemm_pick_cfg(bigItems);
+    int bm, bn;
+    gemm_cfg_dims(cfg, &bm, &bn);
     d.gridM = (M + bm - 1) / bm;
-    d.gridN = (N + bm - 1) / bm;
+    d.gridN = (N + bn - 1) / bn;
     const long long items = (long long)d.gridM * d.gridN * batch;
     ctx->launches++;
-    return gemm_launch(d, (int)items, small, s);
+    return gemm_launch(d, (int)items, cfg, s);
 }
 
 int ensure_winv(parsec_context_s* ctx, int nb) {
