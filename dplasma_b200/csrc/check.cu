@@ -97,8 +97,9 @@ double dplasma_dlange(parsec_context_t* parsec, dplasma_enum_t ntype, const pars
 int check_dpotrf(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec_tiled_matrix_t* A,
                  parsec_tiled_matrix_t* A0) {
     if (!parsec) return 1;
-    if (A->super.nodes > 1) {
-        fprintf(stderr, "check_dpotrf: multi-process check not available yet\n");
+    const bool multi = A->super.nodes > 1;
+    if (multi && uplo != dplasmaLower) {
+        fprintf(stderr, "check_dpotrf: dplasmaUpper on a process grid is not available yet\n");
         return 1;
     }
     cudaSetDevice(parsec->device);
@@ -135,7 +136,8 @@ int check_dpotrf(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec
         }
         if (!rc) rc = launch_transpose_grid(parsec, s, dA);
     }
-    for (int k = 0; !rc && k < dA.nt; k++) {
+    if (!rc && multi) rc = check_update_multi(parsec, dA, R);
+    for (int k = 0; !rc && !multi && k < dA.nt; k++) {
         const int tk = dA.rowsOfTile(k), below = dA.nt - k - 1;
         // D = tril(L(k,k)) with the strict upper part zeroed (dplasma_zlacpy(uplo), src/dplasma_zcheck.c:90)
         rc = launch_copy_tril(parsec, s, dA.tile(k, k), dA.mb, diagCopy, dA.mb, tk, dplasmaLower, 0);

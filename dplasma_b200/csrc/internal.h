@@ -129,6 +129,8 @@ int group_start(parsec_context_s* ctx);
 int group_end(parsec_context_s* ctx);
 int ensure_grid_comms(parsec_context_s* ctx, int P, int Q);
 void comm_destroy(parsec_context_s* ctx);
+// potrf_dist.cu
+int check_update_multi(parsec_context_s* ctx, const DevMatrix& L, const DevMatrix& R);
 // potrf.cu
 int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp);
 int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,

@@ -128,6 +128,13 @@ void parsec_matrix_block_cyclic_lapack_init(parsec_matrix_block_cyclic_t *dc, in
                                             int m, int n, int P, int Q, int kp, int kq, int ip,
                                             int jq, int mloc, int nloc);
 void parsec_tiled_matrix_destroy(parsec_tiled_matrix_t *dc);
+/* The per-step communication plan of the calling rank for tile column k (rows >= gmFirst):
+ * which local tile rows / columns take part in the row and column panel broadcasts and, per
+ * local column, the broadcast root (a grid row) and the root's local row index.  This is the
+ * explicit form of the ranges in the JDF flows src/zpotrf_L.jdf:112,213-215 that PaRSEC turns
+ * into messages.  Host arithmetic only.  out[6] = {kq, kp, il0, nrows, jl0, ncols}. */
+int dplasma_b200_panel_plan(const parsec_tiled_matrix_t *A, int k, int gmFirst, int *out, int *colRoot,
+                            int *colSrcIl);
 /* rank owning global tile (m,n): the data collection's rank_of (src/zpotrf_L.jdf:105) */
 int dplasma_b200_rank_of(const parsec_tiled_matrix_t *A, int m, int n);
 

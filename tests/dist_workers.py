@@ -1,0 +1,166 @@
+"""Worker functions for the multi-process tests (spawned with torch.multiprocessing)."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def _init(rank, world, port, backend):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group(backend, rank=rank, world_size=world)
+    return dist
+
+
+def gloo_cholesky_worker(rank, world, port, P, Q, N, nb, q):
+    """CPU: distributed right-looking tiled Cholesky with the ORACLE's tile kernels, driven by the
+    library's own per-step communication plan (dplasma_b200_panel_plan) over gloo broadcasts."""
+    import torch
+    import dplasma_b200 as dp
+    from oracle.oracle import Oracle, Lower, NoTrans, Trans, ConjTrans, NonUnit, Right
+    from tests.util import full_to_local, local_to_full
+    dist = _init(rank, world, port, "gloo")
+    try:
+        lib, orc = dp.load(), Oracle()
+        prow, pcol = rank // Q, rank % Q
+        row_groups = [dist.new_group([r * Q + c for c in range(Q)]) for r in range(P)]
+        col_groups = [dist.new_group([r * Q + c for r in range(P)]) for c in range(Q)]
+        A0 = orc.plgsy(float(N), Lower, N, nb, 3872)
+        s = dp.capi.BlockCyclicStruct()
+        lib.parsec_matrix_block_cyclic_init(C.byref(s), dp.MATRIX_DOUBLE, dp.MATRIX_TILE, rank, nb, nb, N, N, 0, 0, N, N, P, Q, 1, 1, 0, 0)
+        lmt, lnt, mt = s.nb_elem_r, s.nb_elem_c, s.super.mt
+        flat = full_to_local(A0, nb, nb, P, Q, rank)
+        tiles = flat.reshape(lnt, lmt, nb, nb) if flat.size else np.zeros((lnt, lmt, nb, nb))
+
+        def tile(il, jl):  # column-major nb x nb view
+            return tiles[jl, il].reshape((nb, nb)).T  # stored flat column-major -> Fortran view
+
+        def tdim(g):
+            return N - g * nb if g == mt - 1 else nb
+        info = 0
+        for k in range(mt):
+            out = (C.c_int * 6)()
+            cr, cs = (C.c_int * max(lnt, 1))(), (C.c_int * max(lnt, 1))()
+            lib.dplasma_b200_panel_plan(C.byref(s), k, k + 1, out, cr, cs)
+            kq, kp, il0, nrows, jl0, ncols = list(out)
+            assert kq == k % Q and kp == k % P
+            tk = tdim(k)
+            jlk = k // Q
+            if pcol == kq:
+                Lkk = torch.zeros(nb, nb, dtype=torch.float64)
+                if prow == kp:
+                    T = np.asfortranarray(tile(k // P, jlk)[:tk, :tk])
+                    ii = orc.potrf_tile(Lower, T)
+                    if ii and not info:
+                        info = k * nb + ii
+                    tile(k // P, jlk)[:tk, :tk] = T
+                    Lkk = torch.from_numpy(np.ascontiguousarray(tile(k // P, jlk)))
+                dist.broadcast(Lkk, src=kp * Q + pcol, group=col_groups[pcol])
+                Lk = np.asfortranarray(Lkk.numpy()[:tk, :tk])
+                for il in range(il0, il0 + nrows):
+                    gm = il * P + prow
+                    B = np.asfortranarray(tile(il, jlk)[:tdim(gm), :tk])
+                    orc.trsm_tile(Right, Lower, ConjTrans, NonUnit, 1.0, Lk, B)
+                    tile(il, jlk)[:tdim(gm), :tk] = B
+            if k + 1 >= mt:
+                break
+            # (2) row broadcast of the slab [il0, il0+nrows)
+            slab = torch.zeros(max(nrows, 0), nb, nb, dtype=torch.float64)
+            if pcol == kq and nrows > 0:
+                slab = torch.from_numpy(np.stack([np.ascontiguousarray(tile(il, jlk)) for il in range(il0, il0 + nrows)]))
+            if nrows > 0:
+                dist.broadcast(slab, src=prow * Q + kq, group=row_groups[prow])
+            rowp = {il0 + i: slab[i].numpy() for i in range(nrows)}
+            # (3) column broadcasts, root alternating with n % P
+            colp = {}
+            for c in range(ncols):
+                jl = jl0 + c
+                t = torch.zeros(nb, nb, dtype=torch.float64)
+                if cr[c] == prow:
+                    t = torch.from_numpy(np.ascontiguousarray(rowp[cs[c]]))
+                dist.broadcast(t, src=cr[c] * Q + pcol, group=col_groups[pcol])
+                colp[jl] = t.numpy()
+            # trailing update on my tiles
+            for jl in range(jl0, jl0 + ncols):
+                gn = jl * Q + pcol
+                for il in range(il0, il0 + nrows):
+                    gm = il * P + prow
+                    if gm < gn:
+                        continue
+                    Am = np.asfortranarray(rowp[il][:tdim(gm), :nb])
+                    Cmn = np.asfortranarray(tile(il, jl)[:tdim(gm), :tdim(gn)])
+                    if gm == gn:
+                        orc.herk_tile(Lower, NoTrans, -1.0, Am, 1.0, Cmn)
+                    else:
+                        Bn = np.asfortranarray(colp[jl][:tdim(gn), :nb])
+                        orc.gemm_tile(NoTrans, ConjTrans, -1.0, Am, Bn, 1.0, Cmn)
+                    tile(il, jl)[:tdim(gm), :tdim(gn)] = Cmn
+        # compare my tiles with the single-process oracle
+        want = A0.copy(order="F")
+        winfo = orc.potrf(Lower, want, nb)
+        got = local_to_full(tiles.reshape(-1), N, N, nb, nb, P, Q, rank)
+        mask = np.zeros((N, N), dtype=bool)
+        for jl in range(lnt):
+            for il in range(lmt):
+                gm, gn = il * P + prow, jl * Q + pcol
+                if gm >= gn:
+                    mask[gm * nb:gm * nb + tdim(gm), gn * nb:gn * nb + tdim(gn)] = True
+        mask &= np.tril(np.ones((N, N), dtype=bool))
+        err = float(np.abs(got - want)[mask].max()) if mask.any() else 0.0
+        infos = [None] * world
+        dist.all_gather_object(infos, info)
+        q.put((rank, err, max(infos), winfo))
+    finally:
+        dist.destroy_process_group()
+
+
+def nccl_potrf_worker(rank, world, port, P, Q, N, nb, q, check_values):
+    """GPU: dplasma_dpotrf on a P x Q grid, one process per GPU, through the C ABI."""
+    import torch
+    import dplasma_b200 as dp
+    from tests.util import full_to_local
+    torch.cuda.set_device(rank)
+    dist = _init(rank, world, port, "nccl")
+    try:
+        lib = dp.load()
+        ctx = dp.Context(lib)
+        ids = [ctx.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.comm_init(ids[0], rank, world)
+        dA = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, where=1)   # descriptor first, buffer from torch
+        tA = torch.zeros(max(dA.elems, 1), dtype=torch.float64, device="cuda")
+        dA.s.mat = tA.data_ptr()
+        dA0 = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, where="device")
+        assert lib.dplasma_dplgsy(ctx.ptr, float(N), dp.Lower, dA.ref, 3872) == 0
+        assert lib.dplasma_dplgsy(ctx.ptr, float(N), dp.Lower, dA0.ref, 3872) == 0
+        info = lib.dplasma_dpotrf(ctx.ptr, dp.Lower, dA.ref)
+        t = lib.dplasma_b200_last_elapsed(ctx.ptr)
+        bad = lib.check_dpotrf(ctx.ptr, 0, dp.Lower, dA.ref, dA0.ref)
+        res = lib.dplasma_b200_last_check_result(ctx.ptr)
+        err = -1.0
+        if check_values:
+            from oracle.oracle import Oracle
+            orc = Oracle()
+            want = orc.plgsy(float(N), dp.Lower, N, nb, 3872)
+            assert orc.potrf(dp.Lower, want, nb) == 0
+            wl = full_to_local(np.tril(want), nb, nb, P, Q, rank)
+            from tests.util import local_to_full
+            torch.cuda.synchronize()
+            g = tA.cpu().numpy()[:dA.elems]
+            # compare only the lower-triangular entries (tiles above the diagonal are never touched)
+            gl = full_to_local(np.tril(local_to_full(g, N, N, nb, nb, P, Q, rank)), nb, nb, P, Q, rank)
+            err = float(np.abs(gl - wl).max() / np.abs(want).max())
+        # not positive definite: info must come back as the MAX over ranks of the global index
+        assert lib.dplasma_dplgsy(ctx.ptr, 0.0, dp.Lower, dA.ref, 3872) == 0
+        info_bad = lib.dplasma_dpotrf(ctx.ptr, dp.Lower, dA.ref)
+        q.put((rank, info, bad, res, err, t, info_bad))
+        dA0.free()
+        ctx.close()
+    finally:
+        dist.destroy_process_group()
