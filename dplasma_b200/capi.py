@@ -109,6 +109,7 @@ class Lib:
         proto("parsec_init_wrapper_", None, [])
         proto("parsec_fini_wrapper_", None, [])
         proto("dplasma_b200_blacs_gridinit", None, [i] * 5)
+        proto("dplasma_b200_wrapper_set_context", None, [vp])
         proto("dplasma_b200_dmma_peak_tflops", d, [i, i, C.POINTER(d)])
         proto("dplasma_b200_flops_dpotrf", d, [d])
         proto("dplasma_b200_flops_dpotrs", d, [d, d])

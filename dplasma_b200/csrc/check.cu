@@ -98,10 +98,6 @@ int check_dpotrf(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec
                  parsec_tiled_matrix_t* A0) {
     if (!parsec) return 1;
     const bool multi = A->super.nodes > 1;
-    if (multi && uplo != dplasmaLower) {
-        fprintf(stderr, "check_dpotrf: dplasmaUpper on a process grid is not available yet\n");
-        return 1;
-    }
     cudaSetDevice(parsec->device);
     cudaStream_t s = parsec->sPanel;
     DevMatrix dA, dA0, R;
@@ -121,7 +117,22 @@ int check_dpotrf(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec
         if (!rc && cudaMalloc(&diagCopy, (size_t)R.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
         if (!rc && cudaMemcpyAsync(R.base, dA0.base, elems * sizeof(double), cudaMemcpyDeviceToDevice, s) != cudaSuccess) rc = -201;
     }
-    if (!rc && uplo == dplasmaUpper) {
+    if (!rc && uplo == dplasmaUpper && multi) {
+        // grid: bring both the factor and A0 to lower form through the distributed transpose
+        DevMatrix Lt, Rt;
+        rc = ensure_grid_comms(parsec, dA.P, dA.Q);
+        if (!rc) rc = alloc_like(dA, &Lt);
+        if (!rc) rc = alloc_like(dA, &Rt);
+        if (!rc) rc = dist_transpose_tri(parsec, s, dA, dplasmaUpper, Lt);
+        if (!rc) rc = dist_transpose_tri(parsec, s, R, dplasmaUpper, Rt);
+        if (!rc) {
+            stage_free(&dA);
+            stage_free(&R);
+            dA = Lt;
+            R = Rt;
+        }
+    }
+    if (!rc && uplo == dplasmaUpper && !multi) {
         // run the lower algorithm on the transposed grids
         rc = launch_transpose_grid(parsec, s, R);
         if (!rc && !dA.owned) {
@@ -180,10 +191,7 @@ int check_dpotrf(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec
 int check_daxmb(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec_tiled_matrix_t* A,
                 parsec_tiled_matrix_t* b, parsec_tiled_matrix_t* x) {
     if (!parsec) return 1;
-    if (A->super.nodes > 1) {
-        fprintf(stderr, "check_daxmb: multi-process check not available yet\n");
-        return 1;
-    }
+    const bool multi = A->super.nodes > 1;
     cudaSetDevice(parsec->device);
     cudaStream_t s = parsec->sPanel;
     DevMatrix dA, dB, dX;
@@ -199,24 +207,33 @@ int check_daxmb(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec_
     if (!rc) rc = inf_norm(parsec, dX, false, 0, &Xnorm);
     if (!rc && cudaMalloc(&diagCopy, (size_t)dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
     // b <- b - A x with A symmetric, stored in uplo (dplasma_zhemm(Left, uplo, -1, A, x, 1, b), :199)
-    for (int m = 0; !rc && m < dA.mt; m++) {
-        const int tm = dA.rowsOfTile(m);
-        for (int n = 0; !rc && n < dA.nt; n++) {
-            const int tn = dA.colsOfTile(n);
-            const double* Amn;
-            bool aK;
-            if (m == n) {
-                rc = launch_copy_tril(parsec, s, dA.tile(m, m), dA.mb, diagCopy, dA.mb, tm, uplo, 1);
-                Amn = diagCopy;
-                aK = false;
-            } else {
-                const bool stored = (uplo == dplasmaLower) ? (m > n) : (m < n);
-                Amn = stored ? dA.tile(m, n) : dA.tile(n, m);
-                aK = !stored;
+    if (!rc && multi) rc = symm_residual_multi(parsec, s, uplo, dA, dX, dB);
+    // single process: per tile column n of A, one batched launch for the stored tiles (m,n), one
+    // for the mirrored tiles (n,m)^T and one for the symmetrised diagonal tile, per RHS tile column
+    for (int n = 0; !rc && !multi && n < dA.nt; n++) {
+        const int tn = dA.colsOfTile(n);
+        rc = launch_copy_tril(parsec, s, dA.tile(n, n), dA.mb, diagCopy, dA.mb, tn, uplo, 1);
+        for (int c = 0; !rc && c < dB.nt; c++) {
+            const int nc = dB.colsOfTile(c);
+            const double* Xn = dX.tile(n, c);
+            // diagonal tile
+            rc = gemm_single(parsec, s, tn, nc, tn, -1.0, diagCopy, dA.mb, false, Xn, dX.mb, true, 1.0, dB.tile(n, c), dB.mb, 0);
+            // rows below n: A(m,n) stored (Lower) or A(n,m)^T (Upper)
+            const int below = dA.mt - n - 1;
+            if (!rc && below > 0) {
+                const bool st = (uplo == dplasmaLower);
+                rc = gemm_single(parsec, s, dA.mb, nc, tn, -1.0, st ? dA.tile(n + 1, n) : dA.tile(n, n + 1), dA.mb, !st, Xn,
+                                 dX.mb, true, 1.0, dB.tile(n + 1, c), dB.mb, 0, below,
+                                 st ? dA.tileElems : (long long)dA.lmt * dA.tileElems, 0, dB.tileElems,
+                                 dA.rowsOfTile(dA.mt - 1));
             }
-            for (int c = 0; !rc && c < dB.nt; c++)
-                rc = gemm_single(parsec, s, tm, dB.colsOfTile(c), tn, -1.0, Amn, dA.mb, aK, dX.tile(n, c), dX.mb, true,
-                                 1.0, dB.tile(m, c), dB.mb, 0);
+            // rows above n: A(m,n) stored (Upper) or A(n,m)^T (Lower)
+            if (!rc && n > 0) {
+                const bool st = (uplo == dplasmaUpper);
+                rc = gemm_single(parsec, s, dA.mb, nc, tn, -1.0, st ? dA.tile(0, n) : dA.tile(n, 0), dA.mb, !st, Xn, dX.mb,
+                                 true, 1.0, dB.tile(0, c), dB.mb, 0, n, st ? dA.tileElems : (long long)dA.lmt * dA.tileElems,
+                                 0, dB.tileElems, dA.mb);
+            }
         }
     }
     if (!rc) rc = inf_norm(parsec, dB, false, 0, &Rnorm);

@@ -21,6 +21,8 @@ struct NcclApi {
     int (*CommDestroy)(nccl_comm_t) = nullptr;
     int (*Broadcast)(const void*, void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, nccl_comm_t, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
@@ -38,7 +40,7 @@ static NcclApi* load_nccl() {
     }
 #define LOAD(name) *(void**)(&api.name) = dlsym(h, "nccl" #name); if (!api.name) { fprintf(stderr, "dplasma_b200: nccl" #name " missing\n"); return nullptr; }
     LOAD(GetUniqueId) LOAD(CommInitRank) LOAD(CommSplit) LOAD(CommDestroy) LOAD(Broadcast) LOAD(AllReduce)
-    LOAD(GroupStart) LOAD(GroupEnd) LOAD(GetErrorString)
+    LOAD(GroupStart) LOAD(GroupEnd) LOAD(GetErrorString) LOAD(Send) LOAD(Recv)
 #undef LOAD
     api.h = h;
     return &api;
@@ -66,6 +68,16 @@ int sum_allreduce(parsec_context_s* ctx, double* dbuf, size_t n, cudaStream_t s)
 int bcast(parsec_context_s* ctx, void* comm, const double* send, double* recv, size_t count, int root, cudaStream_t s) {
     int rc = ctx->nccl->Broadcast(send, recv, count, NCCL_DOUBLE, root, comm, s);
     if (rc) { fprintf(stderr, "dplasma_b200: ncclBroadcast failed: %s\n", ctx->nccl->GetErrorString(rc)); return -301; }
+    return 0;
+}
+int p2p_send(parsec_context_s* ctx, const double* buf, size_t count, int peer, cudaStream_t s) {
+    int rc = ctx->nccl->Send(buf, count, NCCL_DOUBLE, peer, ctx->commWorld, s);
+    if (rc) { fprintf(stderr, "dplasma_b200: ncclSend failed: %s\n", ctx->nccl->GetErrorString(rc)); return -305; }
+    return 0;
+}
+int p2p_recv(parsec_context_s* ctx, double* buf, size_t count, int peer, cudaStream_t s) {
+    int rc = ctx->nccl->Recv(buf, count, NCCL_DOUBLE, peer, ctx->commWorld, s);
+    if (rc) { fprintf(stderr, "dplasma_b200: ncclRecv failed: %s\n", ctx->nccl->GetErrorString(rc)); return -306; }
     return 0;
 }
 int group_start(parsec_context_s* ctx) { return ctx->nccl->GroupStart(); }

@@ -7,12 +7,18 @@ namespace dpb {
 
 int gemm_init_attributes() {
     cudaError_t e;
-    e = cudaFuncSetAttribute(gemm_dmma_kernel<CfgBig>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgBig::SMEM);
+#define DPB_ATTR(CFG, AK, BK)                                                                     \
+    e = cudaFuncSetAttribute(gemm_dmma_kernel<CFG, AK, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                             (int)CFG::smem(AK, BK));                                                    \
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(gemm_dmma_kernel<CfgWide>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgWide::SMEM);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(gemm_dmma_kernel<CfgSmall>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgSmall::SMEM);
-    return (int)e;
+    DPB_ATTR(CfgBig, false, false)
+    DPB_ATTR(CfgWide, false, false)
+    DPB_ATTR(CfgSmall, false, false)
+    DPB_ATTR(CfgSmall, true, false)
+    DPB_ATTR(CfgSmall, false, true)
+    DPB_ATTR(CfgSmall, true, true)
+#undef DPB_ATTR
+    return 0;
 }
 
 void gemm_cfg_dims(int cfg, int* bm, int* bn) {
@@ -44,12 +50,20 @@ int gemm_pick_cfg(long long bigItems) {
 
 int gemm_launch(const GemmDesc& d, int nItems, int cfg, cudaStream_t stream) {
     if (nItems <= 0) return 0;
-    if (cfg == CFG_SMALL)
-        gemm_dmma_kernel<CfgSmall><<<nItems, CfgSmall::THREADS, CfgSmall::SMEM, stream>>>(d);
+    // operands stored K-major (transposed forms) exist for the 64x64 tile only
+    if (d.a_kmajor || d.b_kmajor) {
+        if (d.a_kmajor && d.b_kmajor)
+            gemm_dmma_kernel<CfgSmall, true, true><<<nItems, CfgSmall::THREADS, CfgSmall::smem(true, true), stream>>>(d);
+        else if (d.a_kmajor)
+            gemm_dmma_kernel<CfgSmall, true, false><<<nItems, CfgSmall::THREADS, CfgSmall::smem(true, false), stream>>>(d);
+        else
+            gemm_dmma_kernel<CfgSmall, false, true><<<nItems, CfgSmall::THREADS, CfgSmall::smem(false, true), stream>>>(d);
+    } else if (cfg == CFG_SMALL)
+        gemm_dmma_kernel<CfgSmall, false, false><<<nItems, CfgSmall::THREADS, CfgSmall::SMEM, stream>>>(d);
     else if (cfg == CFG_WIDE)
-        gemm_dmma_kernel<CfgWide><<<nItems, CfgWide::THREADS, CfgWide::SMEM, stream>>>(d);
+        gemm_dmma_kernel<CfgWide, false, false><<<nItems, CfgWide::THREADS, CfgWide::SMEM, stream>>>(d);
     else
-        gemm_dmma_kernel<CfgBig><<<nItems, CfgBig::THREADS, CfgBig::SMEM, stream>>>(d);
+        gemm_dmma_kernel<CfgBig, false, false><<<nItems, CfgBig::THREADS, CfgBig::SMEM, stream>>>(d);
     return (int)cudaGetLastError();
 }
 

@@ -133,8 +133,15 @@ struct GemmCfg {
     // the paired 2+2 layout needs stride = 4 (mod 16).
     static constexpr int LDA_S = (WM == 64) ? BM + 2 : BM + 4;
     static constexpr int LDB_S = BN + 4;
-    static constexpr int A_STAGE = BK * LDA_S, B_STAGE = BK * LDB_S;  // doubles
-    static constexpr size_t SMEM = (size_t)STAGES * (A_STAGE + B_STAGE) * 8 + 2 * STAGES * 8 + 16;
+    // K-major operands are staged as [row][LDK]: one 128 B bulk copy per operand row, natural
+    // fragment rows (8f + g), LDS.64 conflict-free for LDK = 4 (mod 16)
+    static constexpr int LDK = BK + 4;
+    __host__ __device__ static constexpr int a_stage(bool ak) { return ak ? BM * LDK : BK * LDA_S; }  // doubles
+    __host__ __device__ static constexpr int b_stage(bool bk) { return bk ? BN * LDK : BK * LDB_S; }
+    __host__ __device__ static constexpr size_t smem(bool ak, bool bk) {
+        return (size_t)STAGES * (a_stage(ak) + b_stage(bk)) * 8 + 2 * STAGES * 8 + 16;
+    }
+    static constexpr size_t SMEM = smem(false, false);
 };
 using CfgBig = GemmCfg<128, 128, 64, 4, 1>;   // 8 consumer warps, 64x32 warp tiles, 134 KB smem, 1 CTA/SM
 using CfgWide = GemmCfg<128, 64, 64, 4, 2>;   // 4 consumer warps, 64x32 warp tiles, 101 KB smem, 2 CTAs/SM
@@ -221,14 +228,15 @@ __device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
 // ---------------------------------------------------------------------------------------
 // The kernel
 // ---------------------------------------------------------------------------------------
-template <class Cfg>
+template <class Cfg, bool AK, bool BKM>
 __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(const __grid_constant__ GemmDesc d) {
     constexpr int BM = Cfg::BM, BN = Cfg::BN, BK = Cfg::BK, STAGES = Cfg::STAGES;
-    constexpr int LDA_S = Cfg::LDA_S, LDB_S = Cfg::LDB_S, MF = Cfg::MF, NF = Cfg::NF;
+    constexpr int LDA_S = Cfg::LDA_S, LDB_S = Cfg::LDB_S, MF = Cfg::MF, NF = Cfg::NF, LDK = Cfg::LDK;
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int A_STAGE = Cfg::a_stage(AK), B_STAGE = Cfg::b_stage(BKM);
     double* sA = reinterpret_cast<double*>(smem_raw);
-    double* sB = sA + (size_t)STAGES * Cfg::A_STAGE;
-    uint64_t* full = reinterpret_cast<uint64_t*>(sB + (size_t)STAGES * Cfg::B_STAGE);
+    double* sB = sA + (size_t)STAGES * A_STAGE;
+    uint64_t* full = reinterpret_cast<uint64_t*>(sB + (size_t)STAGES * B_STAGE);
     uint64_t* empty = full + STAGES;
 
     const BlockWork w = decode_work<Cfg>(d, blockIdx.x);
@@ -248,30 +256,36 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
 
     if (warp == Cfg::CONSUMER_WARPS) {
         // ============================ producer warp ============================
-        const bool fast = d.fast && !d.a_kmajor && !d.b_kmajor && !(w.M & 1) && !(w.N & 1);
+        // bulk (TMA) producer needs 16 B alignment: host-checked strides/pointers, K % 16 == 0, and an
+        // even row count for M-major operands (their rows are copied as one contiguous run)
+        const bool fast = d.fast && (AK || !(w.M & 1)) && (BKM || !(w.N & 1));
+        const int nA = AK ? w.M : BK, nB = BKM ? w.N : BK;  // bulk copies per stage
         for (int c = 0; c < nChunks; c++) {
             const int s = c % STAGES;
             const uint32_t ph = (c / STAGES) & 1;
             if (c >= STAGES) mbar_wait(&empty[s], ph ^ 1);
-            double* dA = sA + (size_t)s * Cfg::A_STAGE;
-            double* dB = sB + (size_t)s * Cfg::B_STAGE;
+            double* dA = sA + (size_t)s * A_STAGE;
+            double* dB = sB + (size_t)s * B_STAGE;
             const int kk0 = c * BK;
             const int kt = kk0 / d.kTile, kin = kk0 - kt * d.kTile;
             if (fast) {
                 // K % 16 == 0 and kTile % 16 == 0 are guaranteed by the host in fast mode.
                 if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)((w.M + w.N) * BK * 8));
                 __syncwarp();
-                // one k-row per lane: lanes 0-15 -> A rows, 16-31 -> B rows
-                if (lane < 16) {
-                    const double* src = w.A + (size_t)kt * d.aKTileStride + (size_t)(kin + lane) * w.lda;
-                    bulk_g2s(dA + lane * LDA_S, src, (uint32_t)w.M * 8, &full[s]);
-                } else {
-                    const int r = lane - 16;
-                    const double* src = w.B + (size_t)kt * d.bKTileStride + (size_t)(kin + r) * w.ldb;
-                    bulk_g2s(dB + r * LDB_S, src, (uint32_t)w.N * 8, &full[s]);
+                const double* Ab = w.A + (size_t)kt * d.aKTileStride;
+                const double* Bb = w.B + (size_t)kt * d.bKTileStride;
+                for (int q = lane; q < nA + nB; q += 32) {
+                    if (q < nA) {
+                        if (AK) bulk_g2s(dA + q * LDK, Ab + kin + (size_t)q * w.lda, BK * 8, &full[s]);
+                        else bulk_g2s(dA + q * LDA_S, Ab + (size_t)(kin + q) * w.lda, (uint32_t)w.M * 8, &full[s]);
+                    } else {
+                        const int r = q - nA;
+                        if (BKM) bulk_g2s(dB + r * LDK, Bb + kin + (size_t)r * w.ldb, BK * 8, &full[s]);
+                        else bulk_g2s(dB + r * LDB_S, Bb + (size_t)(kin + r) * w.ldb, (uint32_t)w.N * 8, &full[s]);
+                    }
                 }
             } else {
-                // generic producer: element loads, zero fill, optional transpose (K-major operand)
+                // generic producer: element loads with zero fill (odd sizes, unaligned operands)
                 for (int r = 0; r < BK; r++) {
                     const int kk = kk0 + r;
                     const bool kin_range = kk < d.K;
@@ -279,16 +293,16 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
                     for (int i = lane; i < BM; i += 32) {
                         double v = 0.0;
                         if (kin_range && i < w.M)
-                            v = d.a_kmajor ? w.A[(size_t)kt2 * d.aKTileStride + kin2 + (size_t)i * w.lda]
-                                           : w.A[(size_t)kt2 * d.aKTileStride + (size_t)kin2 * w.lda + i];
-                        dA[r * LDA_S + i] = v;
+                            v = AK ? w.A[(size_t)kt2 * d.aKTileStride + kin2 + (size_t)i * w.lda]
+                                   : w.A[(size_t)kt2 * d.aKTileStride + (size_t)kin2 * w.lda + i];
+                        dA[AK ? i * LDK + r : r * LDA_S + i] = v;
                     }
                     for (int j = lane; j < BN; j += 32) {
                         double v = 0.0;
                         if (kin_range && j < w.N)
-                            v = d.b_kmajor ? w.B[(size_t)kt2 * d.bKTileStride + kin2 + (size_t)j * w.ldb]
-                                           : w.B[(size_t)kt2 * d.bKTileStride + (size_t)kin2 * w.ldb + j];
-                        dB[r * LDB_S + j] = v;
+                            v = BKM ? w.B[(size_t)kt2 * d.bKTileStride + kin2 + (size_t)j * w.ldb]
+                                    : w.B[(size_t)kt2 * d.bKTileStride + (size_t)kin2 * w.ldb + j];
+                        dB[BKM ? j * LDK + r : r * LDB_S + j] = v;
                     }
                 }
                 __syncwarp();
@@ -310,8 +324,11 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
     const double alpha = d.alpha, beta = d.beta;
     const double cscale = (beta == 0.0) ? 0.0 : beta / alpha;
     constexpr int RUN = (Cfg::WM == 64) ? 8 : 2;  // contiguous rows a thread owns per fragment group
-    const bool vec = (w.M == BM) && (w.N == BN) && (w.lower == 0) && ((w.ldc & 1) == 0) &&
+    const bool vec = !AK && (w.M == BM) && (w.N == BN) && (w.lower == 0) && ((w.ldc & 1) == 0) &&
                      ((reinterpret_cast<uintptr_t>(w.C) & 15) == 0);
+    // fragment -> tile coordinates (K-major operands use the natural 8f+g fragment rows)
+    auto crow = [&](int i) { return wm0 + (AK ? 8 * i + g : frag_row<Cfg::WM>(g, i)); };
+    auto ccol = [&](int c, int j) { return wn0 + (BKM ? 8 * j + c : frag_col(c, j)); };
     double acc[MF][NF][2];
     if (cscale == 0.0) {
 #pragma unroll
@@ -323,7 +340,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
         for (int j = 0; j < NF; j++)
 #pragma unroll
             for (int h = 0; h < 2; h++) {
-                const double* cp = w.C + (size_t)(wn0 + frag_col(2 * t + h, j)) * w.ldc + wm0;
+                const double* cp = w.C + (size_t)ccol(2 * t + h, j) * w.ldc + wm0;
 #pragma unroll
                 for (int i = 0; i < MF; i += 2) {
                     const double2 x = *reinterpret_cast<const double2*>(cp + frag_row<Cfg::WM>(g, i));
@@ -336,12 +353,12 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
         for (int j = 0; j < NF; j++)
 #pragma unroll
             for (int h = 0; h < 2; h++) {
-                const int col = wn0 + frag_col(2 * t + h, j);
+                const int col = ccol(2 * t + h, j);
                 const double* cp = w.C + (size_t)col * w.ldc;
                 const int gj = w.gj0 + col;
 #pragma unroll
                 for (int i = 0; i < MF; i++) {
-                    const int row = wm0 + frag_row<Cfg::WM>(g, i);
+                    const int row = crow(i);
                     bool ok = (col < w.N) && (row < w.M);
                     if (w.lower == 1 && (w.gi0 + row < gj)) ok = false;
                     if (w.lower == 2 && (w.gi0 + row > gj)) ok = false;
@@ -352,8 +369,8 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
     (void)RUN;
 
     // per-thread fragment base offsets inside a stage
-    const int aoff = (Cfg::WM == 64) ? (wm0 + 8 * g) : (wm0 + 2 * g);
-    const int boff = wn0 + 2 * g;
+    const int aoff = AK ? (wm0 + g) * LDK + t : ((Cfg::WM == 64) ? (wm0 + 8 * g) : (wm0 + 2 * g));
+    const int boff = BKM ? (wn0 + g) * LDK + t : wn0 + 2 * g;
 
     for (int c = 0; c < nChunks; c++) {
         const int s = c % STAGES;
@@ -363,14 +380,17 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
         // the producer's bulk copy overwrite the stage under it.  Behind the spin-wait above, every
         // DMMA of chunk c-1 -- and therefore every LDS feeding it -- has been issued and completed.
         if (c > 0 && lane == 0) mbar_arrive(&empty[(c - 1) % STAGES]);
-        const double* pA = sA + (size_t)s * Cfg::A_STAGE + aoff;
-        const double* pB = sB + (size_t)s * Cfg::B_STAGE + boff;
+        const double* pA = sA + (size_t)s * A_STAGE + aoff;
+        const double* pB = sB + (size_t)s * B_STAGE + boff;
 #pragma unroll
         for (int ks = 0; ks < BK / 4; ks++) {
             double a[MF], b[NF];
-            const double* ra = pA + (ks * 4 + t) * LDA_S;
-            const double* rb = pB + (ks * 4 + t) * LDB_S;
-            if (Cfg::WM == 64) {
+            const double* ra = AK ? pA + ks * 4 : pA + (ks * 4 + t) * LDA_S;
+            const double* rb = BKM ? pB + ks * 4 : pB + (ks * 4 + t) * LDB_S;
+            if (AK) {
+#pragma unroll
+                for (int v = 0; v < MF; v++) a[v] = ra[v * 8 * LDK];
+            } else if (Cfg::WM == 64) {
 #pragma unroll
                 for (int v = 0; v < 4; v++) {
                     double2 x = *reinterpret_cast<const double2*>(ra + 2 * v);
@@ -383,10 +403,15 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
                     a[2 * v] = x.x; a[2 * v + 1] = x.y;
                 }
             }
+            if (BKM) {
 #pragma unroll
-            for (int v = 0; v < NF / 2; v++) {
-                double2 x = *reinterpret_cast<const double2*>(rb + 16 * v);
-                b[2 * v] = x.x; b[2 * v + 1] = x.y;
+                for (int v = 0; v < NF; v++) b[v] = rb[v * 8 * LDK];
+            } else {
+#pragma unroll
+                for (int v = 0; v < NF / 2; v++) {
+                    double2 x = *reinterpret_cast<const double2*>(rb + 16 * v);
+                    b[2 * v] = x.x; b[2 * v + 1] = x.y;
+                }
             }
 #pragma unroll
             for (int i = 0; i < MF; i++)
@@ -401,7 +426,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
         for (int j = 0; j < NF; j++)
 #pragma unroll
             for (int h = 0; h < 2; h++) {
-                double* cp = w.C + (size_t)(wn0 + frag_col(2 * t + h, j)) * w.ldc + wm0;
+                double* cp = w.C + (size_t)ccol(2 * t + h, j) * w.ldc + wm0;
 #pragma unroll
                 for (int i = 0; i < MF; i += 2) {
                     double2 x;
@@ -416,13 +441,13 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
     for (int j = 0; j < NF; j++) {
 #pragma unroll
         for (int h = 0; h < 2; h++) {
-            const int col = wn0 + frag_col(2 * t + h, j);
+            const int col = ccol(2 * t + h, j);
             if (col >= w.N) continue;
             double* cp = w.C + (size_t)col * w.ldc;
             const int gj = w.gj0 + col;
 #pragma unroll
             for (int i = 0; i < MF; i++) {
-                const int row = wm0 + frag_row<Cfg::WM>(g, i);
+                const int row = crow(i);
                 if (row >= w.M) continue;
                 if (w.lower == 1 && (w.gi0 + row < gj)) continue;
                 if (w.lower == 2 && (w.gi0 + row > gj)) continue;

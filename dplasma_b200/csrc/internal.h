@@ -100,6 +100,10 @@ int launch_copy_tril(parsec_context_s* ctx, cudaStream_t s, const double* src, i
 int launch_fill(parsec_context_s* ctx, cudaStream_t s, double* p, long long n, double v);
 int launch_trtri_leaf(parsec_context_s* ctx, cudaStream_t s, const double* A, int lda, int n, int uplo, int unit,
                       double* winv);
+int launch_trtri_blocks(parsec_context_s* ctx, cudaStream_t s, const double* T, int ldt, int n, int uplo, int unit,
+                        double* winv);
+int trsm_left_rec_entry(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int n, int ncols, double alpha,
+                        const double* T, int ldt, const double* winv, double* B, int ldb);
 int launch_transpose_grid(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A);
 int launch_transpose_upper_into(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst,
                                 int ldd, int n);
@@ -125,11 +129,19 @@ void stage_free(DevMatrix* dm);
 // comm.cu
 int sum_allreduce(parsec_context_s* ctx, double* dbuf, size_t n, cudaStream_t s);
 int bcast(parsec_context_s* ctx, void* comm, const double* send, double* recv, size_t count, int root, cudaStream_t s);
+int p2p_send(parsec_context_s* ctx, const double* buf, size_t count, int peer, cudaStream_t s);
+int p2p_recv(parsec_context_s* ctx, double* buf, size_t count, int peer, cudaStream_t s);
 int group_start(parsec_context_s* ctx);
 int group_end(parsec_context_s* ctx);
 int ensure_grid_comms(parsec_context_s* ctx, int P, int Q);
 void comm_destroy(parsec_context_s* ctx);
 // potrf_dist.cu
+int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T, int uplo, const DevMatrix& Tt);
+int alloc_like(const DevMatrix& A, DevMatrix* out);
+int trsm_left_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, int diag, double alpha,
+                    const DevMatrix& A, const DevMatrix& B);
+int symm_residual_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, const DevMatrix& A, const DevMatrix& X,
+                        const DevMatrix& B);
 int check_update_multi(parsec_context_s* ctx, const DevMatrix& L, const DevMatrix& R);
 // potrf.cu
 int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp);

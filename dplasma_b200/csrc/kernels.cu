@@ -126,6 +126,46 @@ __global__ void __launch_bounds__(256) trtri_leaf_kernel(const double* __restric
     }
 }
 
+// all IB x IB diagonal blocks of an n x n triangular tile in one launch (one CTA per block)
+__global__ void __launch_bounds__(256) trtri_blocks_kernel(const double* __restrict__ T, int ldt, int n, int uplo,
+                                                           int unit, double* __restrict__ winv) {
+    extern __shared__ double leaf_smem[];
+    double(*S)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem);
+    double(*X)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem + IB * LEAF_LD);
+    const int j0 = blockIdx.x * IB, nn = min(IB, n - j0), tid = threadIdx.x;
+    const double* A = T + j0 + (size_t)j0 * ldt;
+    double* W = winv + (size_t)blockIdx.x * IB * IB;
+    for (int e = tid; e < IB * IB; e += 256) {
+        int i = e % IB, j = e / IB;
+        double v = (i == j) ? 1.0 : 0.0;
+        if (i < nn && j < nn && i >= j) {
+            if (i == j && unit) v = 1.0;
+            else v = (uplo == dplasmaLower) ? A[i + (size_t)j * ldt] : A[j + (size_t)i * ldt];
+        }
+        S[i][j] = v;
+        X[i][j] = 0.0;
+    }
+    __syncthreads();
+    invert_lower_64(S, X, tid);
+    for (int e = tid; e < IB * IB; e += 256) {
+        int i = e % IB, j = e / IB;
+        W[e] = (i >= j) ? X[i][j] : 0.0;
+    }
+}
+int launch_trtri_blocks(parsec_context_s* ctx, cudaStream_t s, const double* T, int ldt, int n, int uplo, int unit,
+                        double* winv) {
+    if (n <= 0) return 0;
+    static bool attr = false;
+    const int smem = 2 * IB * LEAF_LD * (int)sizeof(double);
+    if (!attr) {
+        DPB_CUDA(cudaFuncSetAttribute(trtri_blocks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr = true;
+    }
+    trtri_blocks_kernel<<<(n + IB - 1) / IB, 256, smem, s>>>(T, ldt, n, uplo, unit, winv);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
 int launch_trtri_leaf(parsec_context_s* ctx, cudaStream_t s, const double* A, int lda, int n, int uplo, int unit,
                       double* winv) {
     static bool attr = false;

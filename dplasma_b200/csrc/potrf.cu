@@ -159,8 +159,23 @@ int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp) {
     // DAG is the transpose of its lower counterpart, so the factorization runs as the lower
     // schedule on the transposed tile grid and is transposed back (two HBM-bound passes).
     if (A.P * A.Q != 1) {
-        fprintf(stderr, "dplasma_b200: dplasmaUpper on a process grid is not available yet\n");
-        return -2;
+        // grid: factor the distributed transpose as a lower problem, transpose the factor back
+        if (A.P * A.Q != ctx->nranks) return -303;
+        int rc = ensure_grid_comms(ctx, A.P, A.Q);
+        DevMatrix W;
+        if (!rc) rc = alloc_like(A, &W);
+        if (!rc) rc = dist_transpose_tri(ctx, ctx->sPanel, A, dplasmaUpper, W);
+        if (!rc) {
+            parsec_taskpool_s low = *tp;
+            low.uplo = dplasmaLower;
+            low.dA = W;
+            low.dA.owned = false;
+            rc = potrf_multi(ctx, &low);
+        }
+        if (!rc) rc = dist_transpose_tri(ctx, ctx->sPanel, W, dplasmaLower, A);
+        cudaStreamSynchronize(ctx->sPanel);
+        stage_free(&W);
+        return rc;
     }
     int rc = launch_transpose_grid(ctx, ctx->sPanel, A);
     if (!rc) rc = potrf_lower_1gpu(ctx, A);

@@ -258,6 +258,221 @@ int check_update_multi(parsec_context_s* ctx, const DevMatrix& L, const DevMatri
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------
+// Distributed transpose of a triangle:  Tt(n,m) = T(m,n)^T for every stored tile (m,n) of T.
+// Tile (m,n) lives on rank (m%P)*Q + n%Q, its image on rank (n%P)*Q + m%Q: point-to-point
+// NCCL send/recv, one group per global tile column, then a local transposing copy.
+// Used where the reference's DAGs read the triangular factor "the other way round"
+// (ztrsm_LLT.jdf:132-137, zpotrf_U.jdf, zhemm in the axmb check).
+// ---------------------------------------------------------------------------------------
+int alloc_like(const DevMatrix& A, DevMatrix* out) {
+    *out = A;
+    out->base = nullptr;
+    out->owned = true;
+    size_t elems = (size_t)A.lmt * A.lnt * A.tileElems;
+    if (elems == 0) elems = 1;
+    DPB_CUDA(cudaMalloc(&out->base, elems * sizeof(double)));
+    return 0;
+}
+
+int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T, int uplo, const DevMatrix& Tt) {
+    if (T.mb != T.nb || T.mt != T.nt) return -320;
+    const size_t te = (size_t)T.tileElems;
+    const int me = T.prow * T.Q + T.pcol;
+    double* tmp = nullptr;
+    const int maxRecv = T.mt / std::min(T.P, T.Q) + 2;
+    DPB_CUDA(cudaMalloc(&tmp, (size_t)maxRecv * te * sizeof(double)));
+    std::vector<int> recvM;
+    int rc = 0;
+    for (int n = 0; n < T.nt && !rc; n++) {
+        const int m0 = (uplo == dplasmaLower) ? n : 0, m1 = (uplo == dplasmaLower) ? T.mt : n + 1;
+        recvM.clear();
+        bool grouped = false;
+        for (int m = m0; m < m1 && !rc; m++) {
+            const int src = (m % T.P) * T.Q + (n % T.Q), dst = (n % T.P) * T.Q + (m % T.Q);
+            if (src == me && dst == me) {
+                // both ends local: transpose straight into place (full nb x nb buffers, ragged edges included)
+                rc = launch_transpose(ctx, s, T.tile(m / T.P, n / T.Q), T.mb, Tt.tile(n / T.P, m / T.Q), T.mb, T.mb, T.nb);
+                continue;
+            }
+            if (src != me && dst != me) continue;
+            if (!grouped) { group_start(ctx); grouped = true; }
+            if (src == me) rc = p2p_send(ctx, T.tile(m / T.P, n / T.Q), te, dst, s);
+            else {
+                rc = p2p_recv(ctx, tmp + recvM.size() * te, te, src, s);
+                recvM.push_back(m);
+            }
+        }
+        if (grouped && group_end(ctx)) rc = -321;
+        for (size_t i = 0; i < recvM.size() && !rc; i++) {
+            const int m = recvM[i];
+            rc = launch_transpose(ctx, s, tmp + i * te, T.mb, Tt.tile(n / T.P, m / T.Q), T.mb, T.mb, T.nb);
+        }
+    }
+    cudaStreamSynchronize(s);
+    cudaFree(tmp);
+    return rc;
+}
+
+// ---------------------------------------------------------------------------------------
+// Right-looking tiled triangular solve on the grid, "column panel" form: at step k the tiles of
+// tile column k of the triangular matrix Tm (rows still to be updated, plus the diagonal tile)
+// travel along the grid rows, the freshly solved RHS tile row k travels down the grid columns:
+//   forward  (Tm lower): B(k) = Tm(k,k)^-1 B(k); B(m) -= Tm(m,k) B(k), m > k   (ztrsm_LLN.jdf)
+//   backward (Tm upper): B(k) = Tm(k,k)^-1 B(k); B(m) -= Tm(m,k) B(k), m < k   (ztrsm_LUN.jdf)
+// The transposed variants (LLT / LUT) run on a distributed transpose of the factor.
+// ---------------------------------------------------------------------------------------
+static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower, int diag, double alpha,
+                              const DevMatrix& Tm, const DevMatrix& B) {
+    int rc = ensure_grid_comms(ctx, Tm.P, Tm.Q);
+    if (!rc) rc = ensure_winv(ctx, Tm.nb);
+    if (!rc) rc = ensure_panel_bufs(ctx, Tm);
+    if (rc) return rc;
+    const size_t te = (size_t)Tm.tileElems, teB = (size_t)B.tileElems;
+    const int mt = Tm.mt;
+    const int rowEnd = std::min(Tm.firstLocalRowGE(Tm.mt), Tm.lmt);
+    const int colEndB = std::min(B.firstLocalColGE(B.nt), B.lnt);
+    double* xrow = nullptr;  // solved tile row k of the RHS, one tile per local RHS tile column
+    DPB_CUDA(cudaMalloc(&xrow, (size_t)std::max(colEndB, 1) * teB * sizeof(double)));
+    PanelBufs pb = panel_bufs(ctx, Tm, 0);
+    for (int kk = 0; kk < mt && !rc; kk++) {
+        const int k = lower ? kk : mt - 1 - kk;
+        const int kp = k % Tm.P, kq = k % Tm.Q, jlk = k / Tm.Q;
+        const int tk = Tm.rowsOfTile(k);
+        const double lalpha = (kk == 0) ? alpha : 1.0;
+        // local tile rows that take part: the diagonal tile's row and the rows still to update
+        const int ilA = lower ? std::min(Tm.firstLocalRowGE(k), rowEnd) : 0;
+        const int ilB = lower ? rowEnd : std::min(Tm.firstLocalRowGE(k + 1), rowEnd);
+        const int cnt = ilB - ilA;
+        // (a) tile column k of Tm along the grid rows
+        const double* rowPtr = pb.row;
+        if (Tm.Q == 1) rowPtr = Tm.tile(0, jlk);
+        else if (cnt > 0) {
+            const bool owner = (Tm.pcol == kq);
+            double* buf = owner ? Tm.tile(ilA, jlk) : pb.row + (size_t)ilA * te;
+            if (owner) rowPtr = Tm.tile(0, jlk);
+            rc = bcast(ctx, ctx->commRow, buf, buf, (size_t)cnt * te, kq, s);
+            if (rc) break;
+        }
+        // (b) solve the RHS tiles of tile row k (ranks of grid row kp, each for its own RHS columns)
+        const int ilk = k / Tm.P;
+        if (Tm.prow == kp) {
+            const double* Tkk = rowPtr + (size_t)ilk * te;
+            double* winv = ctx->wInv;
+            rc = launch_trtri_blocks(ctx, s, Tkk, Tm.mb, tk, lower ? dplasmaLower : dplasmaUpper, diag == dplasmaUnit, winv);
+            for (int jl = 0; jl < colEndB && !rc; jl++)
+                rc = trsm_left_rec_entry(ctx, s, lower ? dplasmaLower : dplasmaUpper, false, tk,
+                                         B.colsOfTile(jl * B.Q + B.pcol), lalpha, Tkk, Tm.mb, winv, B.tile(ilk, jl), B.mb);
+            if (rc) break;
+        }
+        // (c) solved tile row k down the grid columns
+        const double* xPtr = xrow;
+        long long xStride = (long long)teB;
+        if (Tm.P == 1) { xPtr = B.tile(ilk, 0); xStride = (long long)B.lmt * teB; }
+        else if (colEndB > 0) {
+            group_start(ctx);
+            for (int jl = 0; jl < colEndB && !rc; jl++)
+                rc = bcast(ctx, ctx->commCol, B.tile(std::min(ilk, std::max(B.lmt - 1, 0)), jl), xrow + (size_t)jl * teB, teB, kp, s);
+            if (group_end(ctx)) rc = -313;
+            if (rc) break;
+        }
+        // (d) update my remaining RHS tile rows
+        const int u0 = lower ? std::min(Tm.firstLocalRowGE(k + 1), rowEnd) : 0;
+        const int u1 = lower ? rowEnd : std::min(Tm.firstLocalRowGE(k), rowEnd);
+        if (u1 > u0) {
+            const int lastGm = (u1 - 1) * Tm.P + Tm.prow;
+            for (int jl = 0; jl < colEndB && !rc; jl++)
+                rc = gemm_single(ctx, s, B.mb, B.colsOfTile(jl * B.Q + B.pcol), tk, -1.0, rowPtr + (size_t)u0 * te, Tm.mb,
+                                 false, xPtr + (size_t)jl * xStride, B.mb, true, lalpha, B.tile(u0, jl), B.mb, 0, u1 - u0,
+                                 (long long)te, 0, (long long)teB, B.rowsOfTile(lastGm));
+        }
+    }
+    cudaStreamSynchronize(s);
+    cudaFree(xrow);
+    return rc;
+}
+
+int trsm_left_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, int diag, double alpha,
+                    const DevMatrix& A, const DevMatrix& B) {
+    if (A.P != B.P || A.Q != B.Q || A.mb != B.mb) {
+        fprintf(stderr, "dplasma_dtrsm: A and B must share the process grid and the row tiling\n");
+        return -102;
+    }
+    if (A.P * A.Q != ctx->nranks) return -303;
+    int rc = ensure_grid_comms(ctx, A.P, A.Q);
+    if (rc) return rc;
+    if (trans == dplasmaNoTrans) return solve_panels_multi(ctx, s, uplo == dplasmaLower, diag, alpha, A, B);
+    // op(A) = A^T: solve with the transposed factor, which is triangular the other way round
+    DevMatrix At;
+    rc = alloc_like(A, &At);
+    if (!rc) rc = dist_transpose_tri(ctx, s, A, uplo, At);
+    if (!rc) rc = solve_panels_multi(ctx, s, uplo != dplasmaLower, diag, alpha, At, B);
+    cudaStreamSynchronize(s);
+    stage_free(&At);
+    return rc;
+}
+
+// B <- B - A X with A symmetric, stored in `uplo`, everything distributed on the grid
+// (dplasma_zhemm(Left, uplo, -1, A, X, 1, B), src/dplasma_zcheck.c:199).
+int symm_residual_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, const DevMatrix& A, const DevMatrix& X,
+                        const DevMatrix& B) {
+    if (A.P * A.Q != ctx->nranks) return -303;
+    int rc = ensure_grid_comms(ctx, A.P, A.Q);
+    if (!rc) rc = ensure_panel_bufs(ctx, A);
+    if (rc) return rc;
+    DevMatrix At;
+    rc = alloc_like(A, &At);
+    if (!rc) rc = dist_transpose_tri(ctx, s, A, uplo, At);
+    const size_t te = (size_t)A.tileElems, teB = (size_t)B.tileElems;
+    const int rowEnd = std::min(A.firstLocalRowGE(A.mt), A.lmt);
+    const int colEndB = std::min(B.firstLocalColGE(B.nt), B.lnt);
+    double* xrow = nullptr;
+    if (!rc && cudaMalloc(&xrow, (size_t)std::max(colEndB, 1) * teB * sizeof(double)) != cudaSuccess) rc = -200;
+    PanelBufs pb = panel_bufs(ctx, A, 0);
+    for (int n = 0; n < A.nt && !rc; n++) {
+        const int np = n % A.P, nq = n % A.Q, jln = n / A.Q;
+        const int tn = A.colsOfTile(n);
+        // the full tile column n of the symmetric matrix, staged on the ranks of grid column nq
+        if (A.pcol == nq) {
+            // stored part comes from A, the mirrored part from the transposed copy
+            const int split = std::min(A.firstLocalRowGE(n), rowEnd);  // local rows [0,split) have gm < n
+            const DevMatrix& lowSrc = (uplo == dplasmaLower) ? At : A;   // rows above the diagonal tile
+            const DevMatrix& highSrc = (uplo == dplasmaLower) ? A : At;  // rows from the diagonal tile down
+            if (split > 0)
+                DPB_CUDA(cudaMemcpyAsync(pb.row, lowSrc.tile(0, jln), (size_t)split * te * sizeof(double),
+                                         cudaMemcpyDeviceToDevice, s));
+            if (rowEnd > split)
+                DPB_CUDA(cudaMemcpyAsync(pb.row + (size_t)split * te, highSrc.tile(split, jln),
+                                         (size_t)(rowEnd - split) * te * sizeof(double), cudaMemcpyDeviceToDevice, s));
+            if (A.prow == np)  // diagonal tile: mirror its stored triangle
+                rc = launch_copy_tril(ctx, s, A.tile(n / A.P, jln), A.mb, pb.row + (size_t)(n / A.P) * te, A.mb, tn, uplo, 1);
+        }
+        if (!rc && A.Q > 1 && rowEnd > 0) rc = bcast(ctx, ctx->commRow, pb.row, pb.row, (size_t)rowEnd * te, nq, s);
+        if (rc) break;
+        const int iln = n / A.P;
+        const double* xPtr = xrow;
+        long long xStride = (long long)teB;
+        if (A.P == 1) { xPtr = X.tile(iln, 0); xStride = (long long)X.lmt * teB; }
+        else if (colEndB > 0) {
+            group_start(ctx);
+            for (int jl = 0; jl < colEndB && !rc; jl++)
+                rc = bcast(ctx, ctx->commCol, X.tile(std::min(iln, std::max(X.lmt - 1, 0)), jl), xrow + (size_t)jl * teB, teB, np, s);
+            if (group_end(ctx)) rc = -313;
+        }
+        if (rowEnd > 0) {
+            const int lastGm = (rowEnd - 1) * A.P + A.prow;
+            for (int jl = 0; jl < colEndB && !rc; jl++)
+                rc = gemm_single(ctx, s, B.mb, B.colsOfTile(jl * B.Q + B.pcol), tn, -1.0, pb.row, A.mb, false,
+                                 xPtr + (size_t)jl * xStride, B.mb, true, 1.0, B.tile(0, jl), B.mb, 0, rowEnd, (long long)te,
+                                 0, (long long)teB, B.rowsOfTile(lastGm));
+        }
+    }
+    cudaStreamSynchronize(s);
+    if (xrow) cudaFree(xrow);
+    stage_free(&At);
+    return rc;
+}
+
 }  // namespace dpb
 
 // Host-only view of the plan, for tests of the multi-rank logic without GPUs.

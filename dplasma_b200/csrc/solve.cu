@@ -21,13 +21,11 @@ static inline int split_of(int n) {
 // inverse of a lower block, see trtri_leaf_kernel)
 static int invert_diag_blocks(parsec_context_s* ctx, cudaStream_t s, int uplo, int diag, int n, const double* T,
                               int ldt, double* winv) {
-    for (int j0 = 0; j0 < n; j0 += IB) {
-        int rc = launch_trtri_leaf(ctx, s, T + j0 + (size_t)j0 * ldt, ldt, std::min(IB, n - j0), uplo,
-                                   diag == dplasmaUnit, winv + (size_t)(j0 / IB) * IB * IB);
-        if (rc) return rc;
-    }
-    return 0;
+    return launch_trtri_blocks(ctx, s, T, ldt, n, uplo, diag == dplasmaUnit, winv);
 }
+
+int trsm_left_rec_entry(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int n, int ncols, double alpha,
+                        const double* T, int ldt, const double* winv, double* B, int ldb);
 
 // B(r0:r0+n, :) <- alpha * op(T(r0:r0+n, r0:r0+n))^-1 * B(r0:r0+n, :)      (B is m x ncols, Left side)
 // lowerEff: op(T) is lower triangular  (Lower/NoTrans or Upper/Trans)
@@ -76,6 +74,11 @@ int trsm_left(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, int di
     return trsm_left_rec(ctx, s, uplo, trans != dplasmaNoTrans, 0, m, n, alpha, T, ldt, winv, B, ldb);
 }
 
+int trsm_left_rec_entry(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int n, int ncols, double alpha,
+                        const double* T, int ldt, const double* winv, double* B, int ldb) {
+    return trsm_left_rec(ctx, s, uplo, trans, 0, n, ncols, alpha, T, ldt, winv, B, ldb);
+}
+
 // dplasma_ztrsm, Left side, on staged matrices (single process).
 static int trsm_left_tiled(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, int diag, double alpha,
                            const DevMatrix& A, const DevMatrix& B) {
@@ -96,15 +99,16 @@ static int trsm_left_tiled(parsec_context_s* ctx, cudaStream_t s, int uplo, int 
             rc = trsm_left_rec(ctx, s, uplo, tr, 0, tk, B.colsOfTile(n), lalpha, Akk, A.mb, winv, B.tile(k, n), B.mb);
             if (rc) return rc;
         }
+        // B(m,:) = lalpha B(m,:) - op(A)(m,k) B(k,:) for all remaining m (src/ztrsm_LLN.jdf:131-135,
+        // ztrsm_LLT.jdf:132-137): one launch per RHS tile column, batched over the tile rows m
         const int lo = forward ? k + 1 : 0, hi = forward ? mt : k;
-        for (int m = lo; m < hi; m++) {
-            const int tm = B.rowsOfTile(m);
-            // B(m,:) = lalpha B(m,:) - op(A)(m,k) B(k,:)   (src/ztrsm_LLN.jdf:131-135, ztrsm_LLT.jdf:132-137)
-            const bool stored_mk = (uplo == dplasmaLower) ? (m > k) : (m < k);  // is A(m,k) in the stored triangle?
-            const double* Amk = stored_mk ? A.tile(m, k) : A.tile(k, m);
+        if (hi > lo) {
+            const bool stored_mk = (uplo == dplasmaLower) ? forward : !forward;  // is A(m,k) in the stored triangle?
+            const double* A0 = stored_mk ? A.tile(lo, k) : A.tile(k, lo);
+            const long long sA = stored_mk ? A.tileElems : (long long)A.lmt * A.tileElems;
             for (int n = 0; n < ntr; n++) {
-                rc = gemm_single(ctx, s, tm, B.colsOfTile(n), tk, -1.0, Amk, A.mb, !stored_mk, B.tile(k, n), B.mb,
-                                 true, lalpha, B.tile(m, n), B.mb, 0);
+                rc = gemm_single(ctx, s, B.mb, B.colsOfTile(n), tk, -1.0, A0, A.mb, !stored_mk, B.tile(k, n), B.mb, true,
+                                 lalpha, B.tile(lo, n), B.mb, 0, hi - lo, sA, 0, B.tileElems, B.rowsOfTile(hi - 1));
                 if (rc) return rc;
             }
         }
@@ -130,15 +134,12 @@ int dplasma_dtrsm(parsec_context_t* parsec, dplasma_enum_t side, dplasma_enum_t 
         fprintf(stderr, "dplasma_dtrsm: side Right is outside the Cholesky path and not built here\n");
         return -1;
     }
-    if (A->super.nodes > 1) {
-        fprintf(stderr, "dplasma_dtrsm: multi-process solve not available yet\n");
-        return -101;
-    }
     cudaSetDevice(parsec->device);
     DevMatrix dA, dB;
     int rc = stage_in(parsec, A, &dA, true, uplo);
     if (!rc) rc = stage_in(parsec, B, &dB, true, dplasmaUpperLower);
-    if (!rc) rc = trsm_left_tiled(parsec, parsec->sPanel, uplo, trans, diag, alpha, dA, dB);
+    if (!rc) rc = (A->super.nodes > 1) ? trsm_left_multi(parsec, parsec->sPanel, uplo, trans, diag, alpha, dA, dB)
+                                       : trsm_left_tiled(parsec, parsec->sPanel, uplo, trans, diag, alpha, dA, dB);
     if (!rc) rc = stage_out(parsec, B, &dB, dplasmaUpperLower);
     cudaError_t e = cudaStreamSynchronize(parsec->sPanel);
     stage_free(&dA);
@@ -154,20 +155,20 @@ int dplasma_dpotrs(parsec_context_t* parsec, dplasma_enum_t uplo, const parsec_t
         return -1;
     }
     if (!parsec) return -100;
-    if (A->super.nodes > 1) return -101;
     cudaSetDevice(parsec->device);
     DevMatrix dA, dB;
     int rc = stage_in(parsec, A, &dA, true, uplo);
     if (!rc) rc = stage_in(parsec, B, &dB, true, dplasmaUpperLower);
     cudaStream_t s = parsec->sPanel;
+    const bool multi = A->super.nodes > 1;
+    auto solve = [&](int tr) {
+        return multi ? trsm_left_multi(parsec, s, uplo, tr, dplasmaNonUnit, 1.0, dA, dB)
+                     : trsm_left_tiled(parsec, s, uplo, tr, dplasmaNonUnit, 1.0, dA, dB);
+    };
     if (!rc) {
-        if (uplo == dplasmaUpper) {
-            rc = trsm_left_tiled(parsec, s, uplo, dplasmaTrans, dplasmaNonUnit, 1.0, dA, dB);
-            if (!rc) rc = trsm_left_tiled(parsec, s, uplo, dplasmaNoTrans, dplasmaNonUnit, 1.0, dA, dB);
-        } else {
-            rc = trsm_left_tiled(parsec, s, uplo, dplasmaNoTrans, dplasmaNonUnit, 1.0, dA, dB);
-            if (!rc) rc = trsm_left_tiled(parsec, s, uplo, dplasmaTrans, dplasmaNonUnit, 1.0, dA, dB);
-        }
+        // src/zpotrs_wrapper.c:78-98: Upper: U^T then U ; Lower: L then L^T
+        rc = solve(uplo == dplasmaUpper ? dplasmaTrans : dplasmaNoTrans);
+        if (!rc) rc = solve(uplo == dplasmaUpper ? dplasmaNoTrans : dplasmaTrans);
     }
     if (!rc) rc = stage_out(parsec, B, &dB, dplasmaUpperLower);
     cudaError_t e = cudaStreamSynchronize(s);

@@ -27,12 +27,12 @@ int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, doub
     d.lower = lower; d.rowOff = d.colOff = 0;
     d.batch = batch; d.batchStrideA = sA; d.batchStrideB = sB; d.batchStrideC = sC;
     d.lastBatchM = lastBatchM;
-    d.fast = (!aK && !bK && (K % 16 == 0) && (lda % 2 == 0) && (ldb % 2 == 0) && aligned16(A) &&
-              aligned16(B) && (sA % 2 == 0) && (sB % 2 == 0))
+    d.fast = ((K % 16 == 0) && (lda % 2 == 0) && (ldb % 2 == 0) && aligned16(A) && aligned16(B) &&
+              (sA % 2 == 0) && (sB % 2 == 0))
                  ? 1 : 0;
     // tile configuration: the large CTA tiles only when they still fill the machine
     const long long bigItems = (long long)((M + 127) / 128) * ((N + 127) / 128) * batch;
-    const int cfg = gemm_pick_cfg(bigItems);
+    const int cfg = (aK || bK) ? CFG_SMALL : gemm_pick_cfg(bigItems);
     int bm, bn;
     gemm_cfg_dims(cfg, &bm, &bn);
     d.gridM = (M + bm - 1) / bm;

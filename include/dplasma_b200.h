@@ -232,6 +232,10 @@ void parsec_fini_wrapper_(void);
 /* The reference obtains the process grid from BLACS (Cblacs_gridinfo, common.h:298-301);
  * there is no BLACS here, so the grid of a context number is registered explicitly. */
 void dplasma_b200_blacs_gridinit(int ictxt, int nprow, int npcol, int myrow, int mycol);
+/* The reference's wrapper initialises PaRSEC lazily on the BLACS communicator
+ * (dplasma_wrapper_parsec_init.c:72-96); here an application that already owns a context with
+ * its inter-GPU communicators lends it to the wrapper. */
+void dplasma_b200_wrapper_set_context(parsec_context_t *ctx);
 
 /* src/flops.h:86-87,92-93,282 */
 double dplasma_b200_flops_dpotrf(double n);

@@ -164,3 +164,99 @@ def nccl_potrf_worker(rank, world, port, P, Q, N, nb, q, check_values):
         ctx.close()
     finally:
         dist.destroy_process_group()
+
+
+def nccl_posv_worker(rank, world, port, P, Q, N, nb, K, nbr, uplo_name, q, check_values):
+    """GPU: dplasma_dposv (+ check_dpotrf / check_daxmb) on a P x Q grid, either triangle."""
+    import torch
+    import dplasma_b200 as dp
+    from tests.util import full_to_local, local_to_full
+    torch.cuda.set_device(rank)
+    dist = _init(rank, world, port, "nccl")
+    try:
+        lib = dp.load()
+        ctx = dp.Context(lib)
+        ids = [ctx.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.comm_init(ids[0], rank, world)
+        uplo = dp.Lower if uplo_name == "L" else dp.Upper
+
+        def dev_desc(M_, N_, mb_, nb_):
+            d = dp.BlockCyclic(lib, M_, N_, mb_, nb_, P, Q, rank, where=1)
+            t = torch.zeros(max(d.elems, 1), dtype=torch.float64, device="cuda")
+            d.s.mat = t.data_ptr()
+            return d, t
+        dA, tA = dev_desc(N, N, nb, nb)
+        dA0, tA0 = dev_desc(N, N, nb, nb)
+        dB, tB = dev_desc(N, K, nb, nbr)
+        dX, tX = dev_desc(N, K, nb, nbr)
+        assert lib.dplasma_dplgsy(ctx.ptr, float(N), uplo, dA.ref, 3872) == 0
+        assert lib.dplasma_dplgsy(ctx.ptr, float(N), uplo, dA0.ref, 3872) == 0
+        assert lib.dplasma_dplrnt(ctx.ptr, 0, dB.ref, 2354) == 0
+        assert lib.dplasma_dplrnt(ctx.ptr, 0, dX.ref, 2354) == 0
+        info = lib.dplasma_dposv(ctx.ptr, uplo, dA.ref, dX.ref)
+        bad_f = lib.check_dpotrf(ctx.ptr, 0, uplo, dA.ref, dA0.ref)
+        res_f = lib.dplasma_b200_last_check_result(ctx.ptr)
+        bad_s = lib.check_daxmb(ctx.ptr, 0, uplo, dA0.ref, dB.ref, dX.ref)
+        res_s = lib.dplasma_b200_last_check_result(ctx.ptr)
+        errF = errX = -1.0
+        if check_values:
+            from oracle.oracle import Oracle
+            orc = Oracle()
+            A0 = orc.plgsy(float(N), uplo, N, nb, 3872)
+            Bm = orc.plrnt(N, K, nb, nbr, 2354)
+            F, Xw = A0.copy(order="F"), Bm.copy(order="F")
+            assert orc.posv(uplo, F, Xw, nb, nbr) == 0
+            torch.cuda.synchronize()
+            tri = np.tril if uplo == dp.Lower else np.triu
+            gotF = local_to_full(tA.cpu().numpy()[:dA.elems], N, N, nb, nb, P, Q, rank)
+            wl = full_to_local(tri(F), nb, nb, P, Q, rank)
+            gl = full_to_local(tri(gotF), nb, nb, P, Q, rank)
+            errF = float(np.abs(gl - wl).max() / np.abs(F).max())
+            gx = tX.cpu().numpy()[:dX.elems]
+            wx = full_to_local(Xw, nb, nbr, P, Q, rank)
+            errX = float(np.abs(gx - wx).max() / np.abs(Xw).max()) if gx.size else 0.0
+        q.put((rank, info, bad_f, res_f, bad_s, res_s, errF, errX))
+        ctx.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def nccl_pdpotrf_worker(rank, world, port, P, Q, N, nb, uplo_name, q):
+    """GPU: the ScaLAPACK-compatible pdpotrf_ on a P x Q grid: each rank passes its own
+    column-major local array (LLD = local rows) and the 9-int array descriptor, like
+    tools/cscalapack/pdpotrf.c:94."""
+    import torch
+    import dplasma_b200 as dp
+    from tests.util import lapack_local
+    torch.cuda.set_device(rank)
+    dist = _init(rank, world, port, "nccl")
+    try:
+        lib = dp.load()
+        ctx = dp.Context(lib)
+        ids = [ctx.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.comm_init(ids[0], rank, world)
+        lib.dplasma_b200_wrapper_set_context(C.c_void_p(ctx.ptr))
+        from oracle.oracle import Oracle
+        orc = Oracle()
+        uplo = dp.Lower if uplo_name == "L" else dp.Upper
+        A0 = orc.plgsy(float(N), dp.UpperLower, N, nb, 3872)
+        loc, ri, ci = lapack_local(A0, nb, nb, P, Q, rank)
+        lld = max(1, loc.shape[0])
+        lib.dplasma_b200_blacs_gridinit(7, P, Q, rank // Q, rank % Q)
+        desc = (C.c_int * 9)(1, 7, N, N, nb, nb, 0, 0, lld)
+        n, one, info = C.c_int(N), C.c_int(1), C.c_int(-7)
+        lib.pdpotrf_(uplo_name.encode(), C.byref(n), loc.ctypes.data_as(C.c_void_p), C.byref(one), C.byref(one), desc, C.byref(info))
+        want = A0.copy(order="F")
+        assert orc.potrf(uplo, want, nb) == 0
+        tri = np.tril if uplo == dp.Lower else np.triu
+        mask = tri(np.ones((N, N), dtype=bool))[np.ix_(ri, ci)]
+        err = float(np.abs(loc - want[np.ix_(ri, ci)])[mask].max() / np.abs(want).max()) if mask.any() else 0.0
+        # the other triangle of the caller's array is left alone
+        untouched = bool(np.array_equal(loc[~mask], A0[np.ix_(ri, ci)][~mask]))
+        q.put((rank, info.value, err, untouched))
+        lib.dplasma_b200_wrapper_set_context(None)
+        ctx.close()
+    finally:
+        dist.destroy_process_group()

@@ -50,3 +50,66 @@ def test_dpotrf_grid_large_residual(P, Q, N, nb):
     res = run_grid(P, Q, N, nb, False)
     for rank, info, bad, resid, err, t, info_bad in res:
         assert info == 0 and bad == 0 and 0.0 <= resid < 60.0, (rank, info, bad, resid)
+
+
+def run_posv(P, Q, N, nb, K, nbr, uplo, check_values):
+    import torch
+    import torch.multiprocessing as mp
+    from tests.dist_workers import nccl_posv_worker
+    world = P * Q
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=nccl_posv_worker, args=(r, world, port, P, Q, N, nb, K, nbr, uplo, q, check_values)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=900) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    return res
+
+
+@pytest.mark.parametrize("P,Q", [(1, 2), (2, 1), (2, 2), (2, 4)])
+@pytest.mark.parametrize("uplo", ["L", "U"])
+def test_dposv_grid_matches_oracle(P, Q, uplo):
+    """dposv on a grid, both triangles; ragged sizes like the reference's mpi ctest (-N 457 -t 19 -K 367)"""
+    res = run_posv(P, Q, 1000, 128, 367, 96, uplo, True)
+    for rank, info, bad_f, res_f, bad_s, res_s, errF, errX in res:
+        assert info == 0 and bad_f == 0 and bad_s == 0, (rank, info, bad_f, res_f, bad_s, res_s)
+        assert 0 <= res_f < 60 and 0 <= res_s < 60
+        assert errF < 1e-11 and errX < 1e-10, (rank, errF, errX)
+
+
+@pytest.mark.parametrize("P,Q,N,nb,K,nbr", [(1, 2, 16384, 1024, 1024, 512), (2, 4, 65536, 1024, 1024, 256)])
+def test_dposv_grid_large_residual(P, Q, N, nb, K, nbr):
+    """BASELINE configs[3]: dposv N=65536 NRHS=1024 on 8 GPUs (P=2, Q=4) through the reference's two checks"""
+    res = run_posv(P, Q, N, nb, K, nbr, "L", False)
+    for rank, info, bad_f, res_f, bad_s, res_s, errF, errX in res:
+        assert info == 0 and bad_f == 0 and bad_s == 0, (rank, info, bad_f, res_f, bad_s, res_s)
+        assert 0 <= res_f < 60 and 0 <= res_s < 60
+
+
+@pytest.mark.parametrize("P,Q", [(1, 2), (2, 2), (2, 4)])
+@pytest.mark.parametrize("uplo", ["L", "U"])
+def test_pdpotrf_grid(P, Q, uplo):
+    import torch
+    import torch.multiprocessing as mp
+    from tests.dist_workers import nccl_pdpotrf_worker
+    world = P * Q
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=nccl_pdpotrf_worker, args=(r, world, port, P, Q, 1100, 128, uplo, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for rank, info, err, untouched in res:
+        assert info == 0 and err < 1e-11 and untouched, (rank, info, err, untouched)
