@@ -37,6 +37,9 @@ struct GemmDesc {
     double alpha, beta;  // C = beta*C + alpha*A*B^T
     int K;               // contraction length
     int fast;            // 1: 16B-aligned bulk-copy producer; 0: element-wise producer
+    int preload;         // 1: accumulators start as (beta/alpha)*C (hides the C read; sums into |C|-sized
+                         //    accumulators, so only for tiles whose entries are of the size of the products);
+                         // 0: BLAS order: product accumulated on its own, C = beta*C + alpha*acc in the epilogue
     int a_kmajor, b_kmajor;  // 0: operand stored M-major (NT form); 1: stored K-major
     // K may span several tiles of a tile-row: element (i,kk) of A is at
     //   A + (kk / kTile)*aKTileStride + (kk % kTile)*lda + i      (M-major)
@@ -322,7 +325,10 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
     // thread holds, for fragment (i,j): rows wm0+frag_row(g,i); columns wn0+frag_col(2t,j) and
     // wn0+frag_col(2t+1,j)   (the C fragment's column index plays the role of B's g)
     const double alpha = d.alpha, beta = d.beta;
-    const double cscale = (beta == 0.0) ? 0.0 : beta / alpha;
+    // diagonal (SYRK) tiles carry the large diagonal entries of the matrix: never preload those
+    const bool pre = d.preload && (w.lower == 0);
+    const double cscale = (beta == 0.0 || !pre) ? 0.0 : beta / alpha;
+    const double ebeta = pre ? 0.0 : beta;  // what the epilogue still has to add
     constexpr int RUN = (Cfg::WM == 64) ? 8 : 2;  // contiguous rows a thread owns per fragment group
     const bool vec = !AK && (w.M == BM) && (w.N == BN) && (w.lower == 0) && ((w.ldc & 1) == 0) &&
                      ((reinterpret_cast<uintptr_t>(w.C) & 15) == 0);
@@ -432,6 +438,11 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
                     double2 x;
                     x.x = alpha * acc[i][j][h];
                     x.y = alpha * acc[i + 1][j][h];
+                    if (ebeta != 0.0) {
+                        const double2 c0 = *reinterpret_cast<const double2*>(cp + frag_row<Cfg::WM>(g, i));
+                        x.x += ebeta * c0.x;
+                        x.y += ebeta * c0.y;
+                    }
                     *reinterpret_cast<double2*>(cp + frag_row<Cfg::WM>(g, i)) = x;
                 }
             }
@@ -451,7 +462,9 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
                 if (row >= w.M) continue;
                 if (w.lower == 1 && (w.gi0 + row < gj)) continue;
                 if (w.lower == 2 && (w.gi0 + row > gj)) continue;
-                cp[row] = alpha * acc[i][j][h];
+                double v = alpha * acc[i][j][h];
+                if (ebeta != 0.0) v += ebeta * cp[row];
+                cp[row] = v;
             }
         }
     }

@@ -65,7 +65,7 @@ struct parsec_context_s {
     std::vector<cudaEvent_t> evPool;
     int* dInfo = nullptr;       // device int
     int* hInfo = nullptr;       // pinned host int
-    double* wInv = nullptr;     // inverted diagonal blocks, 2 slots of (maxNB/IB)*IB*IB doubles
+    double* wInv = nullptr;     // 2 slots, each: inverted diagonal blocks + factored diagonal blocks (2*(maxNB/IB)*IB*IB doubles)
     size_t wInvSlot = 0;
     double* wNorm = nullptr;    // row-sum scratch for norms
     size_t wNormLen = 0;
@@ -80,6 +80,7 @@ struct parsec_context_s {
     void* commRow = nullptr;
     void* commCol = nullptr;
     int gridP = 0, gridQ = 0;
+    int gemmPreload = 1;  // internal products preload C into the accumulators; the tile seam API does not
     // optional per-kernel profile of the trailing-update launches (bench.py roofline leg)
     int profile = 0;
     std::vector<cudaEvent_t> profEv;   // pairs (start, stop)
@@ -90,6 +91,9 @@ namespace dpb {
 // kernels.cu
 int launch_potrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
                       int* dInfo, int infoBase);
+int launch_potrf_colblock(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, int j0, double* winv,
+                          double* wdiag, int* dInfo, int infoBase);
+int launch_potrf_diag_writeback(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, const double* wdiag);
 int launch_generate(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int kind /*0 plgsy,1 plrnt*/,
                     double bump, int uplo, unsigned long long seed);
 int launch_rowsum_sym(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int uplo, double* rowsum);
@@ -115,6 +119,9 @@ int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, doub
                 int lower, int batch = 1, long long sA = 0, long long sB = 0, long long sC = 0,
                 int lastBatchM = -1);
 int potrf_tile_lower(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
+                     int* dInfo, int infoBase);
+// fused variant: winv must be followed by a second region of the same size (see ensure_winv)
+int potrf_tile_fused(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
                      int* dInfo, int infoBase);
 int trsm_panel_lower(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, int n, const double* winv,
                      double* B, int ldb, int M, int batch, long long strideB, int lastBatchM);

@@ -40,6 +40,136 @@ __device__ __forceinline__ void invert_lower_64(double (*S)[IB + 1], double (*X)
     }
 }
 
+// In-place lower Cholesky of the n x n (n <= IB) leading block of S (shared memory), 256 threads.
+// Right-looking, unblocked.  report: write info for the first non-positive pivot.
+__device__ __forceinline__ void leaf_cholesky_64(double (*S)[IB + 1], int n, int tid, int* failed, int* dInfo,
+                                                 int infoBase, bool report) {
+    for (int j = 0; j < n; j++) {
+        const double d = S[j][j];
+        if (report && tid == 0 && !(d > 0.0) && !*failed) {
+            *failed = 1;
+            if (*dInfo == 0) *dInfo = infoBase + j + 1;
+        }
+        const double s = sqrt(d), inv = 1.0 / s;
+        __syncthreads();
+        if (tid < IB) {
+            if (tid == j) S[j][j] = s;
+            else if (tid > j && tid < n) S[tid][j] *= inv;
+        }
+        __syncthreads();
+        const int i = tid & (IB - 1);
+        const double lij = S[i][j];
+        for (int c = j + 1 + (tid >> 6); c < n; c += 4)
+            if (i >= c && i < n) S[i][c] -= lij * S[c][j];
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Fast 64x64 leaf: 2x2 blocks of 32, the sequential parts (32x32 Cholesky, 32x32 triangular
+// inverse) done by ONE warp in registers with shuffles -- no block-wide barrier per column.
+//   S (in/out): lower triangle of the block, identity beyond n.   X (out): inverse of L.
+// 256 threads.  info rule as leaf_cholesky_64.
+// ---------------------------------------------------------------------------------------
+// warp-level: lane r owns row r of the 32x32 block at S[o..o+32)[o..o+32)
+__device__ __forceinline__ void warp_chol32(double (*S)[IB + 1], double* invd, int o, int lane, int nvalid,
+                                            int* failed, int* dInfo, int infoBase, bool report) {
+    double a[32];
+#pragma unroll
+    for (int c = 0; c < 32; c++) a[c] = S[o + lane][o + c];
+#pragma unroll
+    for (int c = 0; c < 32; c++) {
+        const double d = __shfl_sync(0xffffffffu, a[c], c);
+        if (report && lane == 0 && c < nvalid && !(d > 0.0) && !*failed) {
+            *failed = 1;
+            if (*dInfo == 0) *dInfo = infoBase + o + c + 1;
+        }
+        const double s = sqrt(d), inv = 1.0 / s;
+        const double l = a[c] * inv;  // lanes > c: the column entry; lane c: overwritten below
+        if (lane == c) { a[c] = s; invd[o + c] = inv; }
+        else if (lane > c) a[c] = l;
+#pragma unroll
+        for (int c2 = c + 1; c2 < 32; c2++) {
+            const double lc2 = __shfl_sync(0xffffffffu, l, c2);
+            if (lane >= c2) a[c2] -= l * lc2;
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 32; c++)
+        if (c <= lane) S[o + lane][o + c] = a[c];
+}
+// warp-level: X block (o,o) = inverse of the lower-triangular S block (o,o); lane c owns column c
+__device__ __forceinline__ void warp_trinv32(double (*S)[IB + 1], double (*X)[IB + 1], const double* invd, int o,
+                                             int lane) {
+    double x[32];
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+        double sum = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+        for (int k = 0; k < i; k++) sum -= S[o + i][o + k] * x[k];  // x[k] == 0 for k < lane
+        x[i] = (i >= lane) ? sum * invd[o + i] : 0.0;
+    }
+#pragma unroll
+    for (int i = 0; i < 32; i++) X[o + i][o + lane] = x[i];
+}
+
+__device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB + 1], int n, int tid, int* failed,
+                                             int* dInfo, int infoBase, bool report) {
+    const int warp = tid >> 5, lane = tid & 31;
+    __shared__ double invd[IB];  // reciprocals of the diagonal of L
+    // 1. L11 = chol(A11)
+    if (warp == 0) warp_chol32(S, invd, 0, lane, min(n, 32), failed, dInfo, infoBase, report);
+    __syncthreads();
+    // 2. warp 0: X11 = inv(L11) ; warp 1: L21 = A21 L11^-T (one row per lane, forward substitution)
+    if (warp == 0) warp_trinv32(S, X, invd, 0, lane);
+    else if (warp == 1) {
+        double r[32];
+#pragma unroll
+        for (int c = 0; c < 32; c++) {
+            double sum = S[32 + lane][c];
+#pragma unroll
+            for (int k = 0; k < c; k++) sum -= r[k] * S[c][k];
+            r[c] = sum * invd[c];
+        }
+#pragma unroll
+        for (int c = 0; c < 32; c++) S[32 + lane][c] = r[c];
+    }
+    __syncthreads();
+    // 3. A22 -= L21 L21^T (lower part), all threads: 4 outputs each
+    for (int e = tid; e < 32 * 32; e += 256) {
+        const int i = e & 31, c = e >> 5;
+        if (i >= c) {
+            double sum = 0.0;
+#pragma unroll 8
+            for (int k = 0; k < 32; k++) sum += S[32 + i][k] * S[32 + c][k];
+            S[32 + i][32 + c] -= sum;
+        }
+    }
+    __syncthreads();
+    // 4. L22 = chol(A22)
+    if (warp == 0) warp_chol32(S, invd, 32, lane, max(0, min(n - 32, 32)), failed, dInfo, infoBase, report);
+    __syncthreads();
+    // 5. warp 0: X22 = inv(L22) ; the others: T = L21 X11 parked in X's upper-right block (transposed)
+    if (warp == 0) warp_trinv32(S, X, invd, 32, lane);
+    else {
+        for (int e = tid - 32; e < 32 * 32; e += 224) {
+            const int i = e & 31, c = e >> 5;
+            double t = 0.0;
+            for (int k = c; k < 32; k++) t += S[32 + i][k] * X[k][c];
+            X[c][32 + i] = t;
+        }
+    }
+    __syncthreads();
+    // 6. X21 = -X22 T
+    for (int e = tid; e < 32 * 32; e += 256) {
+        const int i = e & 31, c = e >> 5;
+        double x = 0.0;
+        for (int k = 0; k <= i; k++) x += X[32 + i][32 + k] * X[c][32 + k];
+        X[32 + i][c] = -x;
+    }
+    __syncthreads();
+}
+
 // ---------------------------------------------------------------------------------------
 // Leaf of the in-tile recursion: factor an n x n (n <= 64) diagonal block A = L L^T in
 // shared memory and invert L.  Replaces cusolverDnDpotrf on the innermost block
@@ -67,26 +197,7 @@ __global__ void __launch_bounds__(256) potrf_leaf_kernel(double* __restrict__ A,
     }
     if (tid == 0) failed = 0;
     __syncthreads();
-    // right-looking unblocked Cholesky
-    for (int j = 0; j < n; j++) {
-        const double d = S[j][j];
-        if (tid == 0 && !(d > 0.0) && !failed) {
-            failed = 1;
-            if (*dInfo == 0) *dInfo = infoBase + j + 1;
-        }
-        const double s = sqrt(d), inv = 1.0 / s;
-        __syncthreads();
-        if (tid < IB) {
-            if (tid == j) S[j][j] = s;
-            else if (tid > j && tid < n) S[tid][j] *= inv;
-        }
-        __syncthreads();
-        const int i = tid & (IB - 1);
-        const double lij = S[i][j];
-        for (int c = j + 1 + (tid >> 6); c < n; c += 4)
-            if (i >= c && i < n) S[i][c] -= lij * S[c][j];
-        __syncthreads();
-    }
+    leaf_cholesky_64(S, n, tid, &failed, dInfo, infoBase, true);
     // write the factor back (lower part only: the strict upper part of the tile is not ours)
     for (int e = tid; e < IB * IB; e += 256) {
         int i = e % IB, j = e / IB;
@@ -175,6 +286,182 @@ int launch_trtri_leaf(parsec_context_s* ctx, cudaStream_t s, const double* A, in
         attr = true;
     }
     trtri_leaf_kernel<<<1, 256, smem, s>>>(A, lda, n, uplo, unit, winv);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Fused left-looking column-block step of the diagonal-tile factorization (replaces
+// cusolverDnDpotrf on the tile, src/zpotrf_L.jdf:143, with nb/64 launches instead of a deep
+// recursion of tiny kernels).  For the 64-wide block column starting at j0, CTA b owns the
+// 64-row block i0 = j0 + 64 b and does, without any inter-CTA synchronisation:
+//   1. D = A(j0.., j0..) - A(j0.., 0:j0) A(j0.., 0:j0)^T      (every CTA, redundantly)
+//      R = A(i0.., j0..) - A(i0.., 0:j0) A(j0.., 0:j0)^T      (its own block; DMMA, K = j0)
+//   2. D = L L^T in shared memory, X = L^-1                    (every CTA, redundantly)
+//   3. A(i0.., j0..) = R X^T                                   (the panel solve of its block)
+// CTA 0 writes the inverse (for the panel TRSM), info, and the factored diagonal block -- the
+// latter to workspace (wdiag), not in place: the other CTAs of the launch still read the
+// original block.  Nothing reads a factored diagonal block before the tile is finished, so
+// one copy launch at the end puts them all in place.
+// ---------------------------------------------------------------------------------------
+constexpr int PC_KC = 32;            // contraction chunk
+constexpr int PC_LD = IB + 4;        // staged operand rows: conflict-free for the 2+2 fragment layout
+constexpr int PC_SMEM = (3 * IB * (IB + 1) + 2 * 2 * PC_KC * PC_LD) * (int)sizeof(double);
+
+__global__ void __launch_bounds__(256) potrf_colblock_kernel(double* __restrict__ A, int lda, int n, int j0,
+                                                             double* __restrict__ winv, double* __restrict__ wdiag,
+                                                             int* dInfo, int infoBase) {
+    extern __shared__ double pc_smem[];
+    double(*D)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(pc_smem);
+    double(*R)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(pc_smem + IB * LEAF_LD);
+    double(*X)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(pc_smem + 2 * IB * LEAF_LD);
+    double* stage = pc_smem + 3 * IB * LEAF_LD;  // [buf][op][PC_KC][PC_LD], op 0: rows of block j, 1: rows of block i
+    __shared__ int failed;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int i0 = j0 + blockIdx.x * IB;
+    const int nj = min(IB, n - j0), ni = min(IB, n - i0);
+    const bool isDiag = blockIdx.x == 0;
+    if (tid == 0) failed = 0;
+
+    // ---- 1. DMMA accumulation of the two 64x64 products over K = j0 ----
+    // warps 0-3: D quadrants, warps 4-7: R quadrants; 32x32 per warp
+    const int which = warp >> 2, q = warp & 3;
+    const int wm0 = (q & 1) * 32, wn0 = (q >> 1) * 32;
+    const int g = lane >> 2, t = lane & 3;
+    double acc[4][4][2];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+    const int nChunks = (j0 + PC_KC - 1) / PC_KC;
+    // 16-byte asynchronous copies when the tile allows it (even lda, 16 B aligned base, full row blocks)
+    const bool async16 = ((lda & 1) == 0) && ((reinterpret_cast<uintptr_t>(A) & 15) == 0) && (nj == IB) &&
+                         (isDiag || ni == IB);
+    auto load_chunk = [&](int c, int buf) {
+        double* dst = stage + (size_t)buf * 2 * PC_KC * PC_LD;
+        if (async16) {
+            // 2 operands x PC_KC k-columns x 32 pairs of rows
+            for (int e = tid; e < 2 * PC_KC * (IB / 2); e += 256) {
+                const int op = e / (PC_KC * (IB / 2)), r2 = e % (IB / 2), kk = (e / (IB / 2)) % PC_KC;
+                if (op && isDiag) continue;
+                const int k = c * PC_KC + kk;  // j0 is a multiple of 64: every chunk is full
+                const double* src = A + ((op ? i0 : j0) + 2 * r2) + (size_t)k * lda;
+                const uint32_t d32 = smem_u32(dst + (op * PC_KC + kk) * PC_LD + 2 * r2);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d32), "l"(src) : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        } else {
+            // predicated element loads (ragged edges read as zero)
+            for (int e = tid; e < 2 * PC_KC * IB; e += 256) {
+                const int op = e / (PC_KC * IB), r = e % IB, kk = (e / IB) % PC_KC;
+                const int k = c * PC_KC + kk, row = (op ? i0 : j0) + r;
+                double v = 0.0;
+                if (k < j0 && row < n && (op == 0 || !isDiag)) v = A[row + (size_t)k * lda];
+                dst[(op * PC_KC + kk) * PC_LD + r] = v;
+            }
+        }
+    };
+    if (nChunks > 0) load_chunk(0, 0);
+    for (int c = 0; c < nChunks; c++) {
+        const int buf = c & 1;
+        if (c + 1 < nChunks) load_chunk(c + 1, buf ^ 1);
+        if (async16) {
+            if (c + 1 < nChunks) asm volatile("cp.async.wait_group 1;" ::: "memory");
+            else asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();  // chunk c has landed for every thread
+        const double* sJ = stage + (size_t)buf * 2 * PC_KC * PC_LD;
+        const double* sI = sJ + PC_KC * PC_LD;
+        const double* sAop = which ? sI : sJ;
+        if (!(which && isDiag)) {
+#pragma unroll
+            for (int ks = 0; ks < PC_KC / 4; ks++) {
+                double a[4], b[4];
+                const double* ra = sAop + (ks * 4 + t) * PC_LD + wm0 + 2 * g;
+                const double* rb = sJ + (ks * 4 + t) * PC_LD + wn0 + 2 * g;
+#pragma unroll
+                for (int v = 0; v < 2; v++) {
+                    const double2 x = *reinterpret_cast<const double2*>(ra + 16 * v);
+                    a[2 * v] = x.x; a[2 * v + 1] = x.y;
+                    const double2 y = *reinterpret_cast<const double2*>(rb + 16 * v);
+                    b[2 * v] = y.x; b[2 * v + 1] = y.y;
+                }
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int j = 0; j < 4; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+            }
+        }
+        __syncthreads();  // everyone is done with buf before it is refilled (two iterations ahead)
+    }
+    // ---- D / R = A - acc into shared memory (identity padding beyond the ragged edge of D) ----
+    {
+        double(*Out)[LEAF_LD] = which ? R : D;
+        const int rbase = which ? i0 : j0, rlim = which ? ni : nj;
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const int col = wn0 + frag_col(2 * t + h, j);
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int row = wm0 + frag_row<32>(g, i);
+                    double v = (!which && row == col) ? 1.0 : 0.0;
+                    if (row < rlim && col < nj && !(which && isDiag)) {
+                        if (which || row >= col) v = A[rbase + row + (size_t)(j0 + col) * lda] - acc[i][j][h];
+                        else v = 0.0;
+                    }
+                    Out[row][col] = v;
+                }
+            }
+    }
+    for (int e = tid; e < IB * IB; e += 256) X[e % IB][e / IB] = 0.0;
+    __syncthreads();
+    // ---- 2. factor and invert the diagonal block (redundantly in every CTA: no inter-CTA sync) ----
+    leaf_fast_64(D, X, nj, tid, &failed, dInfo, infoBase + j0, isDiag);
+    // ---- 3. write back ----
+    if (isDiag) {
+        for (int e = tid; e < IB * IB; e += 256) {
+            const int i = e % IB, j = e / IB;
+            wdiag[e] = D[i][j];
+            winv[e] = (i >= j) ? X[i][j] : 0.0;
+        }
+    } else {
+        // A(i0.., j0..) = R X^T : out(r,c) = sum_{k<=c} R(r,k) X(c,k)
+        const int r = tid & (IB - 1);
+        for (int c = (tid >> 6); c < nj; c += 4) {
+            double sum = 0.0;
+            for (int k = 0; k <= c; k++) sum += R[r][k] * X[c][k];
+            if (r < ni) A[i0 + r + (size_t)(j0 + c) * lda] = sum;
+        }
+    }
+}
+
+// put the factored diagonal blocks (lower triangles) of an n x n tile in place
+__global__ void __launch_bounds__(256) potrf_diag_writeback_kernel(double* __restrict__ A, int lda, int n,
+                                                                   const double* __restrict__ wdiag) {
+    const int j0 = blockIdx.x * IB, nj = min(IB, n - j0);
+    const double* W = wdiag + (size_t)blockIdx.x * IB * IB;
+    for (int e = threadIdx.x; e < IB * IB; e += 256) {
+        const int i = e % IB, j = e / IB;
+        if (i < nj && j < nj && i >= j) A[j0 + i + (size_t)(j0 + j) * lda] = W[e];
+    }
+}
+int launch_potrf_diag_writeback(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, const double* wdiag) {
+    potrf_diag_writeback_kernel<<<(n + IB - 1) / IB, 256, 0, s>>>(A, lda, n, wdiag);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+int launch_potrf_colblock(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, int j0, double* winv,
+                          double* wdiag, int* dInfo, int infoBase) {
+    static bool attr = false;
+    if (!attr) {
+        DPB_CUDA(cudaFuncSetAttribute(potrf_colblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PC_SMEM));
+        attr = true;
+    }
+    const int nblk = (n - j0 + IB - 1) / IB;
+    potrf_colblock_kernel<<<nblk, 256, PC_SMEM, s>>>(A, lda, n, j0, winv, wdiag, dInfo, infoBase);
     ctx->launches++;
     return (int)cudaGetLastError();
 }

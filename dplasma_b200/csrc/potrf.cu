@@ -36,6 +36,7 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
         d.mode = GEMM_TRAILING;
         d.alpha = alpha; d.beta = 1.0; d.K = K;
         d.a_kmajor = d.b_kmajor = 0;
+        d.preload = 1;
         d.kTile = 1 << 30; d.aKTileStride = d.bKTileStride = 0;
         d.Cbase = C.base; d.rowPanel = rowPanel; d.colPanel = colPanel;
         d.rowPanelStride = rowStride; d.colPanelStride = colStride; d.tileElems = C.tileElems;
@@ -97,9 +98,41 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
     return 0;
 }
 
+// DPB_TRACE=1: timestamp the end of every phase of every step (debugging aid; adds event records)
+struct TraceRec { int k; int phase; cudaEvent_t ev; };
+static std::vector<TraceRec> g_trace;
+static cudaEvent_t g_trace0 = nullptr;
+static bool trace_on() {
+    static int on = -1;
+    if (on < 0) on = getenv("DPB_TRACE") ? 1 : 0;
+    return on == 1;
+}
+static void trace_mark(cudaStream_t s, int k, int phase) {
+    if (!trace_on()) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, s);
+    g_trace.push_back({k, phase, e});
+}
+void trace_dump() {
+    if (!trace_on() || !g_trace0) return;
+    static const char* names[] = {"potrf", "trsm", "lookahead", "bulk"};
+    for (auto& r : g_trace) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, g_trace0, r.ev);
+        fprintf(stderr, "TRACE k=%d %s end=%.3f ms\n", r.k, names[r.phase], ms);
+        cudaEventDestroy(r.ev);
+    }
+    g_trace.clear();
+}
+
 // ---- single-process schedule (P = Q = 1): panels are read in place from the matrix ----
 static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
     const int nt = A.nt, nb = A.nb;
+    if (trace_on()) {
+        if (!g_trace0) cudaEventCreate(&g_trace0);
+        cudaEventRecord(g_trace0, ctx->sPanel);
+    }
     int rc = ensure_winv(ctx, nb);
     if (rc) return rc;
     cudaStream_t sp = ctx->sPanel, su = ctx->sUpdate;
@@ -113,13 +146,15 @@ static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
         const int tk = A.rowsOfTile(k);
         double* winv = ctx->wInv + (size_t)(k & 1) * ctx->wInvSlot;
         double* Akk = A.tile(k, k);
-        rc = potrf_tile_lower(ctx, sp, Akk, A.mb, tk, winv, ctx->dInfo, k * nb);
+        rc = potrf_tile_fused(ctx, sp, Akk, A.mb, tk, winv, ctx->dInfo, k * nb);
         if (rc) return rc;
+        trace_mark(sp, k, 0);
         const int below = nt - k - 1;
         if (below <= 0) break;
         rc = trsm_panel_lower(ctx, sp, Akk, A.mb, tk, winv, A.tile(k + 1, k), A.mb, A.mb, below, A.tileElems,
                               A.rowsOfTile(nt - 1));
         if (rc) return rc;
+        trace_mark(sp, k, 1);
         cudaEvent_t evPanel = get_event(ctx, evi++);
         DPB_CUDA(cudaEventRecord(evPanel, sp));
         const double* panel = A.tile(0, k);  // tile (i,k) at panel + i*tileElems
@@ -127,11 +162,13 @@ static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
         if (evUpdPrev) DPB_CUDA(cudaStreamWaitEvent(sp, evUpdPrev, 0));
         rc = trailing_update(ctx, sp, A, panel, A.tileElems, panel, A.tileElems, k + 1, k + 2, -1.0, nb);
         if (rc) return rc;
+        trace_mark(sp, k, 2);
         // bulk: tile columns k+2.. on the update stream
         if (k + 2 < nt) {
             DPB_CUDA(cudaStreamWaitEvent(su, evPanel, 0));
             rc = trailing_update(ctx, su, A, panel, A.tileElems, panel, A.tileElems, k + 2, nt, -1.0, nb);
             if (rc) return rc;
+            trace_mark(su, k, 3);
             cudaEvent_t evUpd = get_event(ctx, evi++);
             DPB_CUDA(cudaEventRecord(evUpd, su));
             evUpdPrev = evUpd;
@@ -147,6 +184,7 @@ static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
 }
 
 int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp);  // potrf_dist.cu
+void trace_dump();
 
 int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp) {
     DevMatrix& A = tp->dA;
@@ -254,6 +292,7 @@ int parsec_context_wait(parsec_context_t* ctx) {
     DPB_CUDA(cudaStreamSynchronize(ctx->sUpdate));
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, ctx->evStart, ctx->evStop) == cudaSuccess) ctx->lastElapsed = ms * 1e-3;
+    dpb::trace_dump();
     for (parsec_taskpool_s* tp : ctx->queue) {
         if (tp->info && *tp->info == 0) *tp->info = *ctx->hInfo;  // rank-local until the wrapper reduces it
         stage_free(&tp->dA);

@@ -167,16 +167,14 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
         if (inCol) {
             double* winv = b.diag + te;
             if (A.prow == kp) {
+                // factor in place with the context workspace, then stage the inverses (and, when the
+                // tile has to travel, the tile itself) in the panel buffer
                 double* Akk = A.tile(k / A.P, jlk);
-                if (A.P == 1) {
-                    // no broadcast needed: factor in place, inverses straight into the buffer
-                    rc = potrf_tile_lower(ctx, sp, Akk, A.mb, tk, winv, ctx->dInfo, k * nb);
-                    if (rc) return rc;
-                } else {
-                    rc = potrf_tile_lower(ctx, sp, Akk, A.mb, tk, winv, ctx->dInfo, k * nb);
-                    if (rc) return rc;
+                rc = potrf_tile_fused(ctx, sp, Akk, A.mb, tk, ctx->wInv, ctx->dInfo, k * nb);
+                if (rc) return rc;
+                DPB_CUDA(cudaMemcpyAsync(winv, ctx->wInv, winvElems * sizeof(double), cudaMemcpyDeviceToDevice, sp));
+                if (A.P > 1)
                     DPB_CUDA(cudaMemcpyAsync(b.diag, Akk, te * sizeof(double), cudaMemcpyDeviceToDevice, sp));
-                }
             }
             const double* Lkk = b.diag;
             if (A.P == 1) Lkk = A.tile(k / A.P, jlk);

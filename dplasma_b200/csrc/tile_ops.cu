@@ -3,6 +3,7 @@
 // take the place of the reference's per-tile cuSOLVER / cuBLAS calls
 // (src/zpotrf_L.jdf:143,236-240,342-346,463-468).
 #include <cstdio>
+#include <cstdlib>
 #include "internal.h"
 
 namespace dpb {
@@ -16,6 +17,7 @@ int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, doub
                 int lda, bool aK, const double* B, int ldb, bool bK, double beta, double* C, int ldc,
                 int lower, int batch, long long sA, long long sB, long long sC, int lastBatchM) {
     if (M <= 0 || N <= 0 || batch <= 0) return 0;
+    if (alpha == 0.0) return -7;  // not used on this path
     if (lastBatchM < 0) lastBatchM = M;
     GemmDesc d;
     d.mode = GEMM_SINGLE;
@@ -25,6 +27,7 @@ int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, doub
     d.A = A; d.B = B; d.C = C;
     d.M = M; d.N = N; d.lda = lda; d.ldb = ldb; d.ldc = ldc;
     d.lower = lower; d.rowOff = d.colOff = 0;
+    d.preload = ctx->gemmPreload;
     d.batch = batch; d.batchStrideA = sA; d.batchStrideB = sB; d.batchStrideC = sC;
     d.lastBatchM = lastBatchM;
     d.fast = ((K % 16 == 0) && (lda % 2 == 0) && (ldb % 2 == 0) && aligned16(A) && aligned16(B) &&
@@ -43,7 +46,7 @@ int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, doub
 }
 
 int ensure_winv(parsec_context_s* ctx, int nb) {
-    const size_t slot = (size_t)((nb + IB - 1) / IB) * IB * IB;
+    const size_t slot = 2 * (size_t)((nb + IB - 1) / IB) * IB * IB;  // [inverses | factored diagonal blocks]
     if (ctx->wInv && ctx->wInvSlot >= slot) return 0;
     if (ctx->wInv) cudaFree(ctx->wInv);
     ctx->wInv = nullptr;
@@ -118,6 +121,26 @@ int potrf_tile_lower(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, 
     return potrf_rec(ctx, s, A, lda, winv, 0, n, dInfo, infoBase);
 }
 
+// Same result through the fused left-looking kernel: one launch per 64-wide block column plus
+// one write-back launch.  winv points at a slot of ensure_winv(): [inverses | factored blocks].
+int potrf_tile_fused(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv, int* dInfo,
+                     int infoBase) {
+    if (n <= 0) return 0;
+    static int mode = -1;  // DPB_POTRF_TILE=rec selects the recursive multi-launch variant
+    if (mode < 0) {
+        const char* e = getenv("DPB_POTRF_TILE");
+        mode = (e && e[0] == 'r') ? 1 : 0;
+    }
+    if (mode == 1) return potrf_rec(ctx, s, A, lda, winv, 0, n, dInfo, infoBase);
+    double* wdiag = winv + ctx->wInvSlot / 2;
+    for (int j0 = 0; j0 < n; j0 += IB) {
+        int rc = launch_potrf_colblock(ctx, s, A, lda, n, j0, winv + (size_t)(j0 / IB) * IB * IB,
+                                       wdiag + (size_t)(j0 / IB) * IB * IB, dInfo, infoBase);
+        if (rc) return rc;
+    }
+    return launch_potrf_diag_writeback(ctx, s, A, lda, n, wdiag);
+}
+
 }  // namespace dpb
 
 using namespace dpb;
@@ -134,12 +157,12 @@ int dplasma_b200_dpotrf_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t
     int rc = ensure_winv(ctx, n);
     if (rc) return rc;
     int* info = d_info ? d_info : ctx->dInfo + 2;
-    if (uplo == dplasmaLower) return potrf_tile_lower(ctx, s, A, lda, n, ctx->wInv, info, info_offset);
+    if (uplo == dplasmaLower) return potrf_tile_fused(ctx, s, A, lda, n, ctx->wInv, info, info_offset);
     // Upper: factor the transposed tile (U = L^T) in a scratch tile
     double* tmp = nullptr;
     DPB_CUDA(cudaMallocAsync(&tmp, (size_t)n * n * sizeof(double), s));
     rc = launch_transpose(ctx, s, A, lda, tmp, n, n, n);
-    if (!rc) rc = potrf_tile_lower(ctx, s, tmp, n, n, ctx->wInv, info, info_offset);
+    if (!rc) rc = potrf_tile_fused(ctx, s, tmp, n, n, ctx->wInv, info, info_offset);
     // only the upper triangle of A is ours to write: transpose the lower factor back into it
     if (!rc) rc = launch_transpose_upper_into(ctx, s, tmp, n, A, lda, n);
     cudaFreeAsync(tmp, s);
@@ -152,8 +175,10 @@ int dplasma_b200_dsyrk_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t 
     if (uplo != dplasmaLower && uplo != dplasmaUpper) return -3;
     cudaStream_t s = (cudaStream_t)stream;
     const bool aK = trans != dplasmaNoTrans;  // C = alpha A^T A + beta C : op(A)(i,kk) = A[kk + i*lda]
-    if (uplo == dplasmaLower) return gemm_single(ctx, s, n, n, k, alpha, A, lda, aK, A, lda, aK, beta, C, ldc, 1);
-    return gemm_single(ctx, s, n, n, k, alpha, A, lda, aK, A, lda, aK, beta, C, ldc, 2);
+    ctx->gemmPreload = 0;  // library-call semantics: product first, then beta*C
+    int rc = gemm_single(ctx, s, n, n, k, alpha, A, lda, aK, A, lda, aK, beta, C, ldc, uplo == dplasmaLower ? 1 : 2);
+    ctx->gemmPreload = 1;
+    return rc;
 }
 
 int dplasma_b200_dgemm_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t transA, dplasma_enum_t transB,
@@ -165,7 +190,10 @@ int dplasma_b200_dgemm_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t 
     // B'[j][kk] = op(B)[kk][j]: NoTrans -> B[kk + j*ldb] (K-major), Trans -> B[j + kk*ldb] (M-major).
     const bool aK = transA != dplasmaNoTrans;
     const bool bK = transB == dplasmaNoTrans;
-    return gemm_single(ctx, s, m, n, k, alpha, A, lda, aK, B, ldb, bK, beta, C, ldc, 0);
+    ctx->gemmPreload = getenv("DPB_GEMM_PRELOAD") ? 1 : 0;  // library-call semantics unless overridden (profiling)
+    int rc = gemm_single(ctx, s, m, n, k, alpha, A, lda, aK, B, ldb, bK, beta, C, ldc, 0);
+    ctx->gemmPreload = 1;
+    return rc;
 }
 
 }  // extern "C"
