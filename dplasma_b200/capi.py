@@ -93,6 +93,14 @@ class Lib:
         proto("dplasma_dplrnt", i, [vp, i, pBC, u64])
         proto("check_dpotrf", i, [vp, i, i, pBC, pBC])
         proto("check_daxmb", i, [vp, i, i, pBC, pBC, pBC])
+        proto("dplasma_zpotrf_New", vp, [i, pBC, C.POINTER(i)])
+        proto("dplasma_zpotrf_Destruct", None, [vp])
+        proto("dplasma_zpotrf_Destroy", None, [vp])
+        proto("dplasma_zpotrf", i, [vp, i, pBC])
+        proto("dplasma_zplghe", i, [vp, d, i, pBC, u64])
+        proto("dplasma_zplrnt", i, [vp, i, pBC, u64])
+        proto("check_zpotrf", i, [vp, i, i, pBC, pBC])
+        proto("dplasma_zlanhe", d, [vp, i, i, pBC])
         proto("dplasma_b200_last_check_result", d, [vp])
         proto("dplasma_dlansy", d, [vp, i, i, pBC])
         proto("dplasma_dlange", d, [vp, i, pBC])
@@ -170,10 +178,12 @@ class BlockCyclic:
     or an int address of caller memory."""
 
     def __init__(self, lib: Lib, M, N, mb, nb, P=1, Q=1, rank=0, kind="tile", uplo=UpperLower, where="host",
-                 lld=None):
+                 lld=None, cplx=False):
         self.lib = lib
         self.s = BlockCyclicStruct()
         self.kind = kind
+        self.cplx = cplx
+        MATRIX_DOUBLE = MATRIX_COMPLEX_DOUBLE if cplx else 4  # noqa: N806 (shadows the module constant on purpose)
         if kind == "tile":
             lib.parsec_matrix_block_cyclic_init(C.byref(self.s), MATRIX_DOUBLE, MATRIX_TILE, rank, mb, nb, M, N,
                                                 0, 0, M, N, P, Q, 1, 1, 0, 0)
@@ -193,6 +203,8 @@ class BlockCyclic:
         else:
             raise ValueError(kind)
         self.owned = None
+        if cplx:
+            self.elems *= 2  # counted in doubles
         nbytes = max(8, self.elems * 8)
         if where == "host":
             self.s.mat = lib.parsec_data_allocate(nbytes)

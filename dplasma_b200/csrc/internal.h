@@ -27,7 +27,8 @@ constexpr int IB = 64;  // leaf block of the in-tile recursion (diagonal blocks 
 struct DevMatrix {
     double* base = nullptr;
     int mb = 0, nb = 0;
-    long long tileElems = 0;
+    long long tileElems = 0;  // DOUBLES per tile (mb*nb*esz): all tile pointer arithmetic is in doubles
+    int esz = 1;              // doubles per element: 1 real, 2 complex (interleaved re,im)
     int lmt = 0, lnt = 0;  // local tile rows / cols
     int M = 0, N = 0;      // global size
     int mt = 0, nt = 0;    // global tile counts
@@ -80,6 +81,7 @@ struct parsec_context_s {
     void* commRow = nullptr;
     void* commCol = nullptr;
     int gridP = 0, gridQ = 0;
+    int cplx = 0;         // set by the drivers while they work on a complex (esz = 2) matrix
     int gemmPreload = 1;  // internal products preload C into the accumulators; the tile seam API does not
     // optional per-kernel profile of the trailing-update launches (bench.py roofline leg)
     int profile = 0;
@@ -91,6 +93,8 @@ namespace dpb {
 // kernels.cu
 int launch_potrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
                       int* dInfo, int infoBase);
+int launch_zpotrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv, int* dInfo,
+                       int infoBase);
 int launch_potrf_colblock(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, int j0, double* winv,
                           double* wdiag, int* dInfo, int infoBase);
 int launch_potrf_diag_writeback(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, const double* wdiag);
@@ -113,6 +117,9 @@ int launch_transpose_upper_into(parsec_context_s* ctx, cudaStream_t s, const dou
                                 int ldd, int n);
 int launch_transpose(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst, int ldd,
                      int m, int n);
+// zgemm_dmma.cu
+int zgemm_init_attributes();
+int zgemm_launch(const GemmDesc& d, int nItems, cudaStream_t stream);
 // tile_ops.cu
 int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, double alpha, const double* A,
                 int lda, bool aK, const double* B, int ldb, bool bK, double beta, double* C, int ldc,

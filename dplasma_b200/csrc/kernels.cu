@@ -466,6 +466,97 @@ int launch_potrf_colblock(parsec_context_s* ctx, cudaStream_t s, double* A, int 
     return (int)cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------
+// Complex leaf (zpotrf): A = L L^H on an n x n (n <= 64) interleaved-complex block in shared
+// memory, then X = L^-1.  Straightforward block-synchronous version (the real path has the
+// fast warp-register leaf; this one favours brevity).  winv: 64 x 64 complex, ld 64.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) zpotrf_leaf_kernel(double* __restrict__ A, int lda, int n,
+                                                          double* __restrict__ winv, int* dInfo, int infoBase) {
+    extern __shared__ double leaf_smem[];
+    double(*Sr)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem);
+    double(*Si)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem + IB * LEAF_LD);
+    double(*Xr)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem + 2 * IB * LEAF_LD);
+    double(*Xi)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem + 3 * IB * LEAF_LD);
+    __shared__ int failed;
+    const int tid = threadIdx.x;
+    for (int e = tid; e < IB * IB; e += 256) {
+        const int i = e % IB, j = e / IB;
+        double re = (i == j) ? 1.0 : 0.0, im = 0.0;
+        if (i < n && j < n && i >= j) {
+            re = A[2 * (i + (size_t)j * lda)];
+            im = (i == j) ? 0.0 : A[2 * (i + (size_t)j * lda) + 1];
+        }
+        Sr[i][j] = re; Si[i][j] = im;
+        Xr[i][j] = 0.0; Xi[i][j] = 0.0;
+    }
+    if (tid == 0) failed = 0;
+    __syncthreads();
+    for (int j = 0; j < n; j++) {
+        const double d = Sr[j][j];
+        if (tid == 0 && !(d > 0.0) && !failed) {
+            failed = 1;
+            if (*dInfo == 0) *dInfo = infoBase + j + 1;
+        }
+        const double s = sqrt(d), inv = 1.0 / s;
+        __syncthreads();
+        if (tid < IB) {
+            if (tid == j) { Sr[j][j] = s; Si[j][j] = 0.0; }
+            else if (tid > j && tid < n) { Sr[tid][j] *= inv; Si[tid][j] *= inv; }
+        }
+        __syncthreads();
+        const int i = tid & (IB - 1);
+        const double lr = Sr[i][j], li = Si[i][j];
+        for (int c = j + 1 + (tid >> 6); c < n; c += 4)
+            if (i >= c && i < n) {
+                const double cr = Sr[c][j], ci = Si[c][j];  // a_ic -= l_ij conj(l_cj)
+                Sr[i][c] -= lr * cr + li * ci;
+                Si[i][c] -= li * cr - lr * ci;
+            }
+        __syncthreads();
+    }
+    for (int e = tid; e < IB * IB; e += 256) {
+        const int i = e % IB, j = e / IB;
+        if (i < n && j < n && i >= j) {
+            A[2 * (i + (size_t)j * lda)] = Sr[i][j];
+            A[2 * (i + (size_t)j * lda) + 1] = Si[i][j];
+        }
+    }
+    // inverse by forward substitution, one column per thread
+    if (tid < IB) {
+        const int c = tid;
+        Xr[c][c] = 1.0 / Sr[c][c];
+        for (int i = c + 1; i < IB; i++) {
+            double sr = 0.0, si = 0.0;
+            for (int l = c; l < i; l++) {
+                sr += Sr[i][l] * Xr[l][c] - Si[i][l] * Xi[l][c];
+                si += Sr[i][l] * Xi[l][c] + Si[i][l] * Xr[l][c];
+            }
+            const double dinv = 1.0 / Sr[i][i];
+            Xr[i][c] = -sr * dinv;
+            Xi[i][c] = -si * dinv;
+        }
+    }
+    __syncthreads();
+    for (int e = tid; e < IB * IB; e += 256) {
+        const int i = e % IB, j = e / IB;
+        winv[2 * e] = (i >= j) ? Xr[i][j] : 0.0;
+        winv[2 * e + 1] = (i >= j) ? Xi[i][j] : 0.0;
+    }
+}
+int launch_zpotrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv, int* dInfo,
+                       int infoBase) {
+    static bool attr = false;
+    const int smem = 4 * IB * LEAF_LD * (int)sizeof(double);
+    if (!attr) {
+        DPB_CUDA(cudaFuncSetAttribute(zpotrf_leaf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr = true;
+    }
+    zpotrf_leaf_kernel<<<1, 256, smem, s>>>(A, lda, n, winv, dInfo, infoBase);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
 int launch_potrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
                       int* dInfo, int infoBase) {
     static bool attr = false;
@@ -538,9 +629,24 @@ __global__ void __launch_bounds__(256) generate_kernel(DevMatrix A, int kind, do
         unsigned long long idx;
         if (kind == 0) idx = (I >= J) ? I + J * (unsigned long long)A.M : J + I * (unsigned long long)A.M;
         else idx = I + J * (unsigned long long)A.M;
-        double v = rnd_value(rnd64_jump(idx, seed));
-        if (kind == 0 && I == J) v += bump;
-        T[i + (size_t)j * A.mb] = v;
+        if (A.esz == 1) {
+            double v = rnd_value(rnd64_jump(idx, seed));
+            if (kind == 0 && I == J) v += bump;
+            T[i + (size_t)j * A.mb] = v;
+        } else {
+            // two consecutive states per entry (NBELEM = 2); plghe: real diagonal, upper = conj of the
+            // mirrored entry (src/cores/core_zplghe.c:95-110,140-150)
+            unsigned long long ran = rnd64_jump(2ULL * idx, seed);
+            double re = rnd_value(ran);
+            ran = 6364136223846793005ULL * ran + 1ULL;
+            double im = rnd_value(ran);
+            if (kind == 0) {
+                if (I == J) { re += bump; im = 0.0; }
+                else if (I < J) im = -im;
+            }
+            T[2 * (i + (size_t)j * A.mb)] = re;
+            T[2 * (i + (size_t)j * A.mb) + 1] = im;
+        }
     }
 }
 
@@ -582,7 +688,12 @@ __global__ void __launch_bounds__(256) rowsum_kernel(DevMatrix A, int sym, int u
             if (sym) {
                 if (uplo == dplasmaLower ? (I < J) : (I > J)) continue;  // other triangle of a diagonal tile
             }
-            const double v = fabs(T[i + (size_t)j * A.mb]);
+            double v;
+            if (A.esz == 1) v = fabs(T[i + (size_t)j * A.mb]);
+            else {
+                const double re = T[2 * (i + (size_t)j * A.mb)], im = T[2 * (i + (size_t)j * A.mb) + 1];
+                v = (sym && I == J) ? fabs(re) : hypot(re, im);  // zlanhe takes |Re| on the diagonal
+            }
             atomicAdd(&rowsum[I], v);
             if (sym && I != J) colsum += v;
         }
@@ -655,9 +766,31 @@ __global__ void copy_tril_kernel(const double* __restrict__ src, int lds, double
         dst[i + (size_t)j * ldd] = v;
     }
 }
+// complex variant: triangle copy with the other triangle zeroed (symmetrize 0) or conj-mirrored (1)
+__global__ void zcopy_tril_kernel(const double* __restrict__ src, int lds, double* __restrict__ dst, int ldd, int n,
+                                  int uplo, int symmetrize) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < (long long)n * n;
+         e += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(e % n), j = (int)(e / n);
+        const bool stored = (uplo == dplasmaLower) ? (i >= j) : (i <= j);
+        double re = 0.0, im = 0.0;
+        if (stored) { re = src[2 * (i + (size_t)j * lds)]; im = (i == j) ? 0.0 : src[2 * (i + (size_t)j * lds) + 1]; }
+        else if (symmetrize == 2) continue;
+        else if (symmetrize) { re = src[2 * (j + (size_t)i * lds)]; im = -src[2 * (j + (size_t)i * lds) + 1]; }
+        dst[2 * (i + (size_t)j * ldd)] = re;
+        dst[2 * (i + (size_t)j * ldd) + 1] = im;
+    }
+}
 int launch_copy_tril(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst, int ldd,
                      int n, int uplo, int symmetrize) {
     if (n <= 0) return 0;
+    if (ctx->cplx) {
+        int zb = (int)(((long long)n * n + 255) / 256);
+        if (zb > 1184) zb = 1184;
+        zcopy_tril_kernel<<<zb, 256, 0, s>>>(src, lds, dst, ldd, n, uplo, symmetrize);
+        ctx->launches++;
+        return (int)cudaGetLastError();
+    }
     int blocks = (int)(((long long)n * n + 255) / 256);
     if (blocks > 1184) blocks = 1184;
     copy_tril_kernel<<<blocks, 256, 0, s>>>(src, lds, dst, ldd, n, uplo, symmetrize);

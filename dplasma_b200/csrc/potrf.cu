@@ -46,7 +46,8 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
         d.lastM = C.rowsOfTile(C.mt - 1); d.lastN = C.colsOfTile(C.nt - 1);
         d.mtGlobal = C.mt; d.ntGlobal = C.nt;
         d.rowEnd = rowEnd;
-        d.fast = ((C.nb % 2 == 0) && (K % 16 == 0) && ((reinterpret_cast<uintptr_t>(rowPanel) & 15) == 0) &&
+        if (ctx->cplx) d.fast = (K % 8 == 0) ? 1 : 0;
+        else d.fast = ((C.nb % 2 == 0) && (K % 16 == 0) && ((reinterpret_cast<uintptr_t>(rowPanel) & 15) == 0) &&
                   ((reinterpret_cast<uintptr_t>(colPanel) & 15) == 0) && (rowStride % 2 == 0) &&
                   (colStride % 2 == 0))
                      ? 1 : 0;
@@ -61,6 +62,7 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
         const int cfg = gemm_pick_cfg(tiles * bptBig * bptBig);
         int bm, bn;
         gemm_cfg_dims(cfg, &bm, &bn);
+        if (ctx->cplx) bm = bn = 64;
         d.bptM = (C.nb + bm - 1) / bm;
         d.bptN = (C.nb + bn - 1) / bn;
         long long items = 0;
@@ -76,7 +78,7 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
             cudaEventCreate(&pe1);
             cudaEventRecord(pe0, s);
         }
-        int rc = gemm_launch(d, (int)items, cfg, s);
+        int rc = ctx->cplx ? zgemm_launch(d, (int)items, s) : gemm_launch(d, (int)items, cfg, s);
         if (ctx->profile) {
             cudaEventRecord(pe1, s);
             // algorithmic flops of this launch: 2 nb^2 K per GEMM tile, nb (nb+1) K per SYRK tile
@@ -86,7 +88,7 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
                 for (int il = d.rowFirst[c]; il < rowEnd; il++) {
                     const int gm = il * C.P + C.prow;
                     const double tm = C.rowsOfTile(gm), tn = C.colsOfTile(gn);
-                    fl += (gm == gn) ? tm * (tm + 1.0) * K : 2.0 * tm * tn * K;
+                    fl += ((gm == gn) ? tm * (tm + 1.0) * K : 2.0 * tm * tn * K) * (ctx->cplx ? 4.0 : 1.0);
                 }
             }
             ctx->profEv.push_back(pe0);
@@ -189,9 +191,16 @@ void trace_dump();
 int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp) {
     DevMatrix& A = tp->dA;
     if (A.mb != A.nb) return -3;
+    ctx->cplx = (A.esz == 2);
     if (tp->uplo == dplasmaLower) {
-        if (A.P * A.Q == 1) return potrf_lower_1gpu(ctx, A);
-        return potrf_multi(ctx, tp);
+        const int rc = (A.P * A.Q == 1) ? potrf_lower_1gpu(ctx, A) : potrf_multi(ctx, tp);
+        ctx->cplx = 0;
+        return rc;
+    }
+    if (ctx->cplx) {
+        ctx->cplx = 0;
+        fprintf(stderr, "dplasma_b200: zpotrf with dplasmaUpper is not built yet (dplasmaLower is)\n");
+        return -2;
     }
     // dplasmaUpper (src/zpotrf_U.jdf): U(k,n) = L(n,k)^T and every tile operation of the upper
     // DAG is the transpose of its lower counterpart, so the factorization runs as the lower
@@ -345,6 +354,18 @@ int dplasma_b200_profile_read(parsec_context_t* ctx, double* seconds, double* fl
     if (launches) *launches = (int)n;
     if (best_tflops) *best_tflops = best;
     return 0;
+}
+
+// complex double: same driver, interleaved complex tiles (src/zpotrf_wrapper.c is the source all
+// four precisions are generated from)
+parsec_taskpool_t* dplasma_zpotrf_New(dplasma_enum_t uplo, parsec_tiled_matrix_t* A, int* info) {
+    return dplasma_dpotrf_New(uplo, A, info);
+}
+void dplasma_zpotrf_Destruct(parsec_taskpool_t* tp) { dplasma_dpotrf_Destruct(tp); }
+void dplasma_zpotrf_Destroy(parsec_taskpool_t* tp) { dplasma_dpotrf_Destruct(tp); }
+int dplasma_zpotrf(parsec_context_t* parsec, dplasma_enum_t uplo, parsec_tiled_matrix_t* A) {
+    if (A && A->mtype != PARSEC_MATRIX_COMPLEX_DOUBLE) return -3;
+    return dplasma_dpotrf(parsec, uplo, A);
 }
 
 int dplasma_dpotrf_rec(parsec_context_t* parsec, dplasma_enum_t uplo, parsec_tiled_matrix_t* A, int hmb) {

@@ -47,7 +47,7 @@ static void compute_panel_plan(const DevMatrix& A, int k, int gmFirst, PanelPlan
 }
 
 static int ensure_panel_bufs(parsec_context_s* ctx, const DevMatrix& A) {
-    const size_t diag = (size_t)A.tileElems + (size_t)((A.nb + IB - 1) / IB) * IB * IB;
+    const size_t diag = (size_t)A.tileElems + (size_t)((A.nb + IB - 1) / IB) * IB * IB * A.esz;
     const size_t need = (size_t)(A.lmt + A.lnt) * A.tileElems + diag;
     if (ctx->panelBuf[0] && ctx->panelBufElems >= need) return 0;
     for (int i = 0; i < 2; i++) {
@@ -149,7 +149,7 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
     cudaStream_t sp = ctx->sPanel, su = ctx->sUpdate;
     const int nt = A.nt, nb = A.nb;
     const size_t te = (size_t)A.tileElems;
-    const size_t winvElems = (size_t)((nb + IB - 1) / IB) * IB * IB;
+    const size_t winvElems = (size_t)((nb + IB - 1) / IB) * IB * IB * A.esz;
     cudaEvent_t ev0 = dist_event(ctx, 0);
     DPB_CUDA(cudaEventRecord(ev0, sp));
     DPB_CUDA(cudaStreamWaitEvent(su, ev0, 0));

@@ -31,7 +31,7 @@ parsec_context_t* parsec_init(int nb_cores, int* pargc, char** pargv[]) {
               cudaEventCreate(&ctx->evStart) == cudaSuccess && cudaEventCreate(&ctx->evStop) == cudaSuccess &&
               cudaMalloc(&ctx->dInfo, 64) == cudaSuccess &&
               cudaHostAlloc(&ctx->hInfo, 64, cudaHostAllocDefault) == cudaSuccess &&
-              gemm_init_attributes() == 0;
+              gemm_init_attributes() == 0 && zgemm_init_attributes() == 0;
     if (!ok) {
         fprintf(stderr, "dplasma_b200: context creation failed: %s\n", cudaGetErrorString(cudaGetLastError()));
         delete ctx;
@@ -188,10 +188,11 @@ static bool is_device_ptr(const void* p) {
 
 static int describe(const parsec_tiled_matrix_t* A, DevMatrix* dm) {
     const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
-    if (A->mtype != PARSEC_MATRIX_DOUBLE) return -1;
+    if (A->mtype != PARSEC_MATRIX_DOUBLE && A->mtype != PARSEC_MATRIX_COMPLEX_DOUBLE) return -1;
+    dm->esz = (A->mtype == PARSEC_MATRIX_COMPLEX_DOUBLE) ? 2 : 1;
     if (bc->grid.krows != 1 || bc->grid.kcols != 1) return -2;
     if (A->i != 0 || A->j != 0 || A->m != A->lm || A->n != A->ln) return -3;  // whole-matrix descriptors only
-    dm->mb = A->mb; dm->nb = A->nb; dm->tileElems = (long long)A->mb * A->nb;
+    dm->mb = A->mb; dm->nb = A->nb; dm->tileElems = (long long)A->mb * A->nb * dm->esz;
     dm->M = A->m; dm->N = A->n; dm->mt = A->mt; dm->nt = A->nt;
     dm->P = bc->grid.rows; dm->Q = bc->grid.cols;
     dm->prow = (bc->grid.rrank - bc->grid.ip + dm->P) % dm->P;
@@ -226,7 +227,7 @@ static int copy_layout(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, De
         }
     } else {
         // LAPACK storage: pitched copies, one per tile (src/dplasmajdf_lapack_dtt.h:161-178,238-255)
-        const size_t lld = (size_t)A->llm;
+        const size_t lld = (size_t)A->llm, eb = 8 * (size_t)dm->esz;
         for (int jl = 0; jl < dm->lnt; jl++) {
             const int gn = jl * dm->Q + dm->pcol;
             const int tn = dm->colsOfTile(gn);
@@ -236,12 +237,12 @@ static int copy_layout(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, De
                 if (part == dplasmaUpper && gm > gn) continue;
                 const int tm = dm->rowsOfTile(gm);
                 double* dev = dm->tile(il, jl);
-                double* usr = user + (size_t)il * dm->mb + (size_t)jl * dm->nb * lld;
+                double* usr = user + ((size_t)il * dm->mb + (size_t)jl * dm->nb * lld) * dm->esz;
                 if (dir == 0)
-                    DPB_CUDA(cudaMemcpy2DAsync(dev, (size_t)dm->mb * 8, usr, lld * 8, (size_t)tm * 8, tn,
+                    DPB_CUDA(cudaMemcpy2DAsync(dev, (size_t)dm->mb * eb, usr, lld * eb, (size_t)tm * eb, tn,
                                                cudaMemcpyDefault, s));
                 else
-                    DPB_CUDA(cudaMemcpy2DAsync(usr, lld * 8, dev, (size_t)dm->mb * 8, (size_t)tm * 8, tn,
+                    DPB_CUDA(cudaMemcpy2DAsync(usr, lld * eb, dev, (size_t)dm->mb * eb, (size_t)tm * eb, tn,
                                                cudaMemcpyDefault, s));
             }
         }

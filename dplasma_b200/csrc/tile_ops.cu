@@ -18,6 +18,25 @@ int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, doub
                 int lower, int batch, long long sA, long long sB, long long sC, int lastBatchM) {
     if (M <= 0 || N <= 0 || batch <= 0) return 0;
     if (alpha == 0.0) return -7;  // not used on this path
+    if (ctx->cplx) {
+        // complex double: interleaved tiles, C = beta C + alpha A B^H only (the forms zpotrf needs)
+        if (aK || bK || lower == 2) return -8;
+        GemmDesc z;
+        z.mode = GEMM_SINGLE;
+        z.alpha = alpha; z.beta = beta; z.K = K;
+        z.a_kmajor = z.b_kmajor = 0; z.preload = 0;
+        z.kTile = 1 << 30; z.aKTileStride = z.bKTileStride = 0;
+        z.A = A; z.B = B; z.C = C;
+        z.M = M; z.N = N; z.lda = lda; z.ldb = ldb; z.ldc = ldc;
+        z.lower = lower; z.rowOff = z.colOff = 0;
+        z.batch = batch; z.batchStrideA = sA; z.batchStrideB = sB; z.batchStrideC = sC;
+        z.lastBatchM = lastBatchM < 0 ? M : lastBatchM;
+        z.fast = ((K % 8 == 0) && aligned16(A) && aligned16(B) && (sA % 2 == 0) && (sB % 2 == 0)) ? 1 : 0;
+        z.gridM = (M + 63) / 64;
+        z.gridN = (N + 63) / 64;
+        ctx->launches++;
+        return zgemm_launch(z, z.gridM * z.gridN * batch, s);
+    }
     if (lastBatchM < 0) lastBatchM = M;
     GemmDesc d;
     d.mode = GEMM_SINGLE;
@@ -46,7 +65,8 @@ int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, doub
 }
 
 int ensure_winv(parsec_context_s* ctx, int nb) {
-    const size_t slot = 2 * (size_t)((nb + IB - 1) / IB) * IB * IB;  // [inverses | factored diagonal blocks]
+    // [inverses | factored diagonal blocks], sized for complex elements
+    const size_t slot = 2 * 2 * (size_t)((nb + IB - 1) / IB) * IB * IB;
     if (ctx->wInv && ctx->wInvSlot >= slot) return 0;
     if (ctx->wInv) cudaFree(ctx->wInv);
     ctx->wInv = nullptr;
@@ -73,17 +93,18 @@ static inline int split_of(int n) {
 // of its IB x IB diagonal blocks in winv (block b at winv + b*IB*IB, ld IB).
 static int trsm_rec(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, const double* winv, int j0,
                     int n, double* B, int ldb, int M, int batch, long long strideB, int lastBatchM) {
+    const size_t ez = ctx->cplx ? 2 : 1;  // doubles per element
     if (n <= IB) {
         // in place: every CTA owns whole rows and has consumed all of A before its epilogue
-        return gemm_single(ctx, s, M, n, n, 1.0, B + (size_t)j0 * ldb, ldb, false,
-                           winv + (size_t)(j0 / IB) * IB * IB, IB, false, 0.0, B + (size_t)j0 * ldb, ldb, 0,
+        return gemm_single(ctx, s, M, n, n, 1.0, B + ez * (size_t)j0 * ldb, ldb, false,
+                           winv + ez * (size_t)(j0 / IB) * IB * IB, IB, false, 0.0, B + ez * (size_t)j0 * ldb, ldb, 0,
                            batch, strideB, 0, strideB, lastBatchM);
     }
     const int n1 = split_of(n), n2 = n - n1;
     int rc = trsm_rec(ctx, s, L, ldl, winv, j0, n1, B, ldb, M, batch, strideB, lastBatchM);
     if (rc) return rc;
-    rc = gemm_single(ctx, s, M, n2, n1, -1.0, B + (size_t)j0 * ldb, ldb, false,
-                     L + (j0 + n1) + (size_t)j0 * ldl, ldl, false, 1.0, B + (size_t)(j0 + n1) * ldb, ldb, 0,
+    rc = gemm_single(ctx, s, M, n2, n1, -1.0, B + ez * (size_t)j0 * ldb, ldb, false,
+                     L + ez * ((j0 + n1) + (size_t)j0 * ldl), ldl, false, 1.0, B + ez * (size_t)(j0 + n1) * ldb, ldb, 0,
                      batch, strideB, 0, strideB, lastBatchM);
     if (rc) return rc;
     return trsm_rec(ctx, s, L, ldl, winv, j0 + n1, n2, B, ldb, M, batch, strideB, lastBatchM);
@@ -97,17 +118,22 @@ int trsm_panel_lower(parsec_context_s* ctx, cudaStream_t s, const double* L, int
 
 static int potrf_rec(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, double* winv, int j0, int n,
                      int* dInfo, int infoBase) {
-    double* Ajj = A + j0 + (size_t)j0 * lda;
-    if (n <= IB) return launch_potrf_leaf(ctx, s, Ajj, lda, n, winv + (size_t)(j0 / IB) * IB * IB, dInfo, infoBase + j0);
+    const size_t ez = ctx->cplx ? 2 : 1;
+    double* Ajj = A + ez * (j0 + (size_t)j0 * lda);
+    if (n <= IB) {
+        double* w = winv + ez * (size_t)(j0 / IB) * IB * IB;
+        return ctx->cplx ? launch_zpotrf_leaf(ctx, s, Ajj, lda, n, w, dInfo, infoBase + j0)
+                         : launch_potrf_leaf(ctx, s, Ajj, lda, n, w, dInfo, infoBase + j0);
+    }
     const int n1 = split_of(n), n2 = n - n1;
     int rc = potrf_rec(ctx, s, A, lda, winv, j0, n1, dInfo, infoBase);
     if (rc) return rc;
     // A21 <- A21 * L11^-T
-    double* A21 = A + (j0 + n1) + (size_t)j0 * lda;
-    rc = trsm_rec(ctx, s, Ajj, lda, winv + (size_t)(j0 / IB) * IB * IB, 0, n1, A21, lda, n2, 1, 0, n2);
+    double* A21 = A + ez * ((j0 + n1) + (size_t)j0 * lda);
+    rc = trsm_rec(ctx, s, Ajj, lda, winv + ez * (size_t)(j0 / IB) * IB * IB, 0, n1, A21, lda, n2, 1, 0, n2);
     if (rc) return rc;
     // A22 <- A22 - A21 A21^T (lower)
-    double* A22 = A + (j0 + n1) + (size_t)(j0 + n1) * lda;
+    double* A22 = A + ez * ((j0 + n1) + (size_t)(j0 + n1) * lda);
     rc = gemm_single(ctx, s, n2, n2, n1, -1.0, A21, lda, false, A21, lda, false, 1.0, A22, lda, 1);
     if (rc) return rc;
     return potrf_rec(ctx, s, A, lda, winv, j0 + n1, n2, dInfo, infoBase);
@@ -131,7 +157,8 @@ int potrf_tile_fused(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, 
         const char* e = getenv("DPB_POTRF_TILE");
         mode = (e && e[0] == 'r') ? 1 : 0;
     }
-    if (mode == 1) return potrf_rec(ctx, s, A, lda, winv, 0, n, dInfo, infoBase);
+    // the fused kernel is real-only; complex tiles take the recursive variant
+    if (mode == 1 || ctx->cplx) return potrf_rec(ctx, s, A, lda, winv, 0, n, dInfo, infoBase);
     double* wdiag = winv + ctx->wInvSlot / 2;
     for (int j0 = 0; j0 < n; j0 += IB) {
         int rc = launch_potrf_colblock(ctx, s, A, lda, n, j0, winv + (size_t)(j0 / IB) * IB * IB,

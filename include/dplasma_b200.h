@@ -171,6 +171,21 @@ int check_dpotrf(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec
 /* :279, src/dplasma_zcheck.c:180-225 (b is overwritten with b - A x like the reference) */
 int check_daxmb(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec_tiled_matrix_t *A,
                 parsec_tiled_matrix_t *b, parsec_tiled_matrix_t *x);
+/* ---- complex double (zpotrf, BASELINE configs[4]); A->mtype must be PARSEC_MATRIX_COMPLEX_DOUBLE,
+ *      tiles hold interleaved (re,im) dplasma_complex64_t.  dplasmaLower only in this build.
+ *      src/include/dplasma/dplasma_z.h:82,107,109,172,239,280 ---- */
+parsec_taskpool_t *dplasma_zpotrf_New(dplasma_enum_t uplo, parsec_tiled_matrix_t *A, int *info);
+void dplasma_zpotrf_Destruct(parsec_taskpool_t *tp);
+void dplasma_zpotrf_Destroy(parsec_taskpool_t *tp);
+int dplasma_zpotrf(parsec_context_t *parsec, dplasma_enum_t uplo, parsec_tiled_matrix_t *A);
+/* src/zplghe_wrapper.c -> src/cores/core_zplghe.c:72-154 (bit-exact) */
+int dplasma_zplghe(parsec_context_t *parsec, double bump, dplasma_enum_t uplo, parsec_tiled_matrix_t *A,
+                   unsigned long long int seed);
+int dplasma_zplrnt(parsec_context_t *parsec, int diagdom, parsec_tiled_matrix_t *A, unsigned long long int seed);
+int check_zpotrf(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec_tiled_matrix_t *A,
+                 parsec_tiled_matrix_t *A0);
+double dplasma_zlanhe(parsec_context_t *parsec, dplasma_enum_t ntype, dplasma_enum_t uplo,
+                      const parsec_tiled_matrix_t *A);
 /* the numbers the two checks print (src/dplasma_zcheck.c:105,203), for callers that want them */
 double dplasma_b200_last_check_result(parsec_context_t *parsec);
 /* dplasma_zlanhe / dplasma_zlange, InfNorm only (src/dplasma_zcheck.c:101-103,194-196) */

@@ -120,8 +120,8 @@ def gloo_cholesky_worker(rank, world, port, P, Q, N, nb, q):
         dist.destroy_process_group()
 
 
-def nccl_potrf_worker(rank, world, port, P, Q, N, nb, q, check_values):
-    """GPU: dplasma_dpotrf on a P x Q grid, one process per GPU, through the C ABI."""
+def nccl_potrf_worker(rank, world, port, P, Q, N, nb, q, check_values, cplx=False):
+    """GPU: dplasma_dpotrf (or zpotrf) on a P x Q grid, one process per GPU, through the C ABI."""
     import torch
     import dplasma_b200 as dp
     from tests.util import full_to_local
@@ -133,32 +133,38 @@ def nccl_potrf_worker(rank, world, port, P, Q, N, nb, q, check_values):
         ids = [ctx.unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         ctx.comm_init(ids[0], rank, world)
-        dA = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, where=1)   # descriptor first, buffer from torch
+        dA = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, where=1, cplx=cplx)   # descriptor first, buffer from torch
         tA = torch.zeros(max(dA.elems, 1), dtype=torch.float64, device="cuda")
         dA.s.mat = tA.data_ptr()
-        dA0 = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, where="device")
-        assert lib.dplasma_dplgsy(ctx.ptr, float(N), dp.Lower, dA.ref, 3872) == 0
-        assert lib.dplasma_dplgsy(ctx.ptr, float(N), dp.Lower, dA0.ref, 3872) == 0
-        info = lib.dplasma_dpotrf(ctx.ptr, dp.Lower, dA.ref)
+        dA0 = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, where="device", cplx=cplx)
+        gen = lib.dplasma_zplghe if cplx else lib.dplasma_dplgsy
+        fac = lib.dplasma_zpotrf if cplx else lib.dplasma_dpotrf
+        chk = lib.check_zpotrf if cplx else lib.check_dpotrf
+        assert gen(ctx.ptr, float(N), dp.Lower, dA.ref, 3872) == 0
+        assert gen(ctx.ptr, float(N), dp.Lower, dA0.ref, 3872) == 0
+        info = fac(ctx.ptr, dp.Lower, dA.ref)
         t = lib.dplasma_b200_last_elapsed(ctx.ptr)
-        bad = lib.check_dpotrf(ctx.ptr, 0, dp.Lower, dA.ref, dA0.ref)
+        bad = chk(ctx.ptr, 0, dp.Lower, dA.ref, dA0.ref)
         res = lib.dplasma_b200_last_check_result(ctx.ptr)
         err = -1.0
         if check_values:
             from oracle.oracle import Oracle
             orc = Oracle()
-            want = orc.plgsy(float(N), dp.Lower, N, nb, 3872)
-            assert orc.potrf(dp.Lower, want, nb) == 0
+            pch = "z" if cplx else "d"
+            want = orc.plgsy(float(N), dp.Lower, N, nb, 3872, pch)
+            assert orc.potrf(dp.Lower, want, nb, pch) == 0
             wl = full_to_local(np.tril(want), nb, nb, P, Q, rank)
             from tests.util import local_to_full
             torch.cuda.synchronize()
             g = tA.cpu().numpy()[:dA.elems]
+            if cplx:
+                g = g.view(np.complex128)
             # compare only the lower-triangular entries (tiles above the diagonal are never touched)
             gl = full_to_local(np.tril(local_to_full(g, N, N, nb, nb, P, Q, rank)), nb, nb, P, Q, rank)
             err = float(np.abs(gl - wl).max() / np.abs(want).max())
         # not positive definite: info must come back as the MAX over ranks of the global index
-        assert lib.dplasma_dplgsy(ctx.ptr, 0.0, dp.Lower, dA.ref, 3872) == 0
-        info_bad = lib.dplasma_dpotrf(ctx.ptr, dp.Lower, dA.ref)
+        assert gen(ctx.ptr, 0.0, dp.Lower, dA.ref, 3872) == 0
+        info_bad = fac(ctx.ptr, dp.Lower, dA.ref)
         q.put((rank, info, bad, res, err, t, info_bad))
         dA0.free()
         ctx.close()

@@ -15,7 +15,7 @@ def free_port():
     return p
 
 
-def run_grid(P, Q, N, nb, check_values):
+def run_grid(P, Q, N, nb, check_values, cplx=False):
     import torch
     import torch.multiprocessing as mp
     from tests.dist_workers import nccl_potrf_worker
@@ -25,7 +25,7 @@ def run_grid(P, Q, N, nb, check_values):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = free_port()
-    procs = [ctx.Process(target=nccl_potrf_worker, args=(r, world, port, P, Q, N, nb, q, check_values)) for r in range(world)]
+    procs = [ctx.Process(target=nccl_potrf_worker, args=(r, world, port, P, Q, N, nb, q, check_values, cplx)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=600) for _ in range(world)]
@@ -113,3 +113,19 @@ def test_pdpotrf_grid(P, Q, uplo):
         assert p.exitcode == 0
     for rank, info, err, untouched in res:
         assert info == 0 and err < 1e-11 and untouched, (rank, info, err, untouched)
+
+
+@pytest.mark.parametrize("P,Q", [(1, 2), (2, 2)])
+def test_zpotrf_grid_matches_oracle(P, Q):
+    res = run_grid(P, Q, 1000, 128, True, cplx=True)
+    for rank, info, bad, resid, err, t, info_bad in res:
+        assert info == 0 and bad == 0 and 0.0 <= resid < 60.0, (rank, info, bad, resid)
+        assert err < 1e-11, (rank, err)
+        assert info_bad == res[0][6] and info_bad > 0
+
+
+def test_zpotrf_baseline_config5_residual():
+    """BASELINE configs[4]: zpotrf complex double N=49152 NB=512 on 4 x B200 (P=2, Q=2)"""
+    res = run_grid(2, 2, 49152, 512, False, cplx=True)
+    for rank, info, bad, resid, err, t, info_bad in res:
+        assert info == 0 and bad == 0 and 0.0 <= resid < 60.0, (rank, info, bad, resid)

@@ -366,3 +366,81 @@ def test_baseline_configs_residual_on_gpu(ctx, N, nb):
     res = lib.dplasma_b200_last_check_result(ctx.ptr)
     assert 0.0 < res < 60.0
     dA.free(); dA0.free()
+
+
+# ------------------------------------------------------------------ complex double (zpotrf)
+def zmake_host(ctx, A, nb):
+    N = A.shape[0]
+    d = dp.BlockCyclic(ctx.lib, N, N, nb, nb, where="host", cplx=True)
+    d.host_array()[:d.elems] = full_to_local(A, nb, nb).view(np.float64)
+    return d
+
+
+def zread_host(d, N, nb):
+    return local_to_full(d.host_array()[:d.elems].view(np.complex128), N, N, nb, nb)
+
+
+@pytest.mark.parametrize("N,nb", [(378, 93), (512, 64)])
+@pytest.mark.parametrize("uplo", [Lower, Upper, UpperLower])
+def test_zplghe_zplrnt_bit_exact(ctx, oracle, golden, N, nb, uplo):
+    d = dp.BlockCyclic(ctx.lib, N, N, nb, nb, where="host", cplx=True)
+    d.host_array()[:] = 0.0
+    assert ctx.lib.dplasma_zplghe(ctx.ptr, float(N), uplo, d.ref, SEED_A) == 0
+    got = zread_host(d, N, nb)
+    assert np.array_equal(got, oracle.plgsy(float(N), uplo, N, nb, SEED_A, "z"))
+    if N == 378 and uplo == Lower:
+        assert np.array_equal(got.ravel(order="F")[::31], golden["z378_A0_L_s31"])
+    d.free()
+    b = dp.BlockCyclic(ctx.lib, N, 5, nb, 5, where="host", cplx=True)
+    assert ctx.lib.dplasma_zplrnt(ctx.ptr, 0, b.ref, SEED_B) == 0
+    gotb = local_to_full(b.host_array()[:b.elems].view(np.complex128), N, 5, nb, 5)
+    assert np.array_equal(gotb, oracle.plrnt(N, 5, nb, 5, SEED_B, "z"))
+    b.free()
+
+
+@pytest.mark.parametrize("N,nb", [(378, 93), (1024, 128), (2048, 512), (1700, 320)])
+def test_zpotrf_lower_vs_oracle(ctx, oracle, golden, N, nb):
+    """zpotrf (BASELINE configs[4] family): values against the oracle, the reference's residual test,
+    and the frozen output of the reference's CORE_z* kernels for the 378/93 ctest size"""
+    A0 = oracle.plgsy(float(N), Lower, N, nb, SEED_A, "z")
+    d = zmake_host(ctx, A0, nb)
+    assert ctx.lib.dplasma_zpotrf(ctx.ptr, Lower, d.ref) == 0
+    F = zread_host(d, N, nb)
+    want = A0.copy(order="F")
+    assert oracle.potrf(Lower, want, nb, "z") == 0
+    assert relerr(np.tril(F), np.tril(want)) < VTOL
+    assert np.array_equal(np.triu(F, 1), np.triu(A0, 1))
+    if N == 378:
+        assert relerr(F.ravel(order="F")[::31], golden["z378_F_L_s31"]) < VTOL
+    bad, res, _, _ = oracle.check_potrf(Lower, F, A0, "z")
+    assert bad == 0 and res < 60.0
+    # the GPU-side check agrees
+    dA0 = zmake_host(ctx, A0, nb)
+    assert ctx.lib.check_zpotrf(ctx.ptr, 0, Lower, d.ref, dA0.ref) == 0
+    assert 0.0 <= ctx.lib.dplasma_b200_last_check_result(ctx.ptr) < 60.0
+    assert ctx.lib.dplasma_zlanhe(ctx.ptr, dp.InfNorm, Lower, dA0.ref) == pytest.approx(oracle.lanhe_inf(Lower, A0, "z"), rel=1e-13)
+    d.free(); dA0.free()
+
+
+def test_zpotrf_info_and_unsupported(ctx, oracle):
+    N, nb = 200, 64
+    A = oracle.plgsy(200.0, Lower, N, nb, SEED_A, "z")
+    A[150, 150] = -1.0
+    d = zmake_host(ctx, A, nb)
+    assert ctx.lib.dplasma_zpotrf(ctx.ptr, Lower, d.ref) == 151
+    assert ctx.lib.dplasma_zpotrf(ctx.ptr, Upper, d.ref) < 0      # not built yet: fails loudly, no fallback
+    d.free()
+
+
+def test_zpotrf_device_resident_residual(ctx):
+    """complex factorization at a size with many tiles, generated and checked in HBM"""
+    lib = ctx.lib
+    N, nb = 8192, 512
+    dA = dp.BlockCyclic(lib, N, N, nb, nb, where="device", cplx=True)
+    dA0 = dp.BlockCyclic(lib, N, N, nb, nb, where="device", cplx=True)
+    assert lib.dplasma_zplghe(ctx.ptr, float(N), Lower, dA.ref, SEED_A) == 0
+    assert lib.dplasma_zplghe(ctx.ptr, float(N), Lower, dA0.ref, SEED_A) == 0
+    assert lib.dplasma_zpotrf(ctx.ptr, Lower, dA.ref) == 0
+    assert lib.check_zpotrf(ctx.ptr, 0, Lower, dA.ref, dA0.ref) == 0
+    assert 0.0 < lib.dplasma_b200_last_check_result(ctx.ptr) < 60.0
+    dA.free(); dA0.free()

@@ -23,20 +23,20 @@ def full_to_local(A, mb, nb, P=1, Q=1, rank=0, sym_uplo=None):
                 continue
             if sym_uplo == Upper and gm > gn:
                 continue
-            t = np.zeros((mb, nb), order="F")
+            t = np.zeros((mb, nb), dtype=A.dtype, order="F")
             blk = A[gm * mb:(gm + 1) * mb, gn * nb:(gn + 1) * nb]
             t[:blk.shape[0], :blk.shape[1]] = blk
             out.append(t.ravel(order="F"))
-    return np.concatenate(out) if out else np.zeros(0)
+    return np.concatenate(out) if out else np.zeros(0, dtype=A.dtype)
 
 
 def local_to_full(flat, M, N, mb, nb, P=1, Q=1, rank=0, sym_uplo=None, out=None):
-    """Scatter rank's local tile-storage array into the full matrix `out`."""
+    """Scatter rank's local tile-storage array into the full matrix `out` (dtype follows `flat`)."""
     mt, nt = -(-M // mb), -(-N // nb)
     prow, pcol = rank // Q, rank % Q
     rows, cols = local_tile_rows(mt, P, prow), local_tile_rows(nt, Q, pcol)
     if out is None:
-        out = np.zeros((M, N), order="F")
+        out = np.zeros((M, N), dtype=flat.dtype, order="F")
     k = 0
     for gn in cols:
         for gm in rows:
