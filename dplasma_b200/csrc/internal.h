@@ -93,6 +93,8 @@ namespace dpb {
 // kernels.cu
 int launch_potrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
                       int* dInfo, int infoBase);
+int launch_trsm_panel_fused(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, int n, const double* winv,
+                            double* B, int ldb, long long tileStride, int rowsPerTile, int lastTileRows, int ntiles);
 int launch_zpotrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv, int* dInfo,
                        int infoBase);
 int launch_potrf_colblock(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, int j0, double* winv,

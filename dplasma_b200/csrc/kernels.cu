@@ -71,6 +71,7 @@ __device__ __forceinline__ void leaf_cholesky_64(double (*S)[IB + 1], int n, int
 //   S (in/out): lower triangle of the block, identity beyond n.   X (out): inverse of L.
 // 256 threads.  info rule as leaf_cholesky_64.
 // ---------------------------------------------------------------------------------------
+__device__ long long g_leaf_clk[8];
 // warp-level: lane r owns row r of the 32x32 block at S[o..o+32)[o..o+32)
 __device__ __forceinline__ void warp_chol32(double (*S)[IB + 1], double* invd, int o, int lane, int nvalid,
                                             int* failed, int* dInfo, int infoBase, bool report) {
@@ -84,7 +85,12 @@ __device__ __forceinline__ void warp_chol32(double (*S)[IB + 1], double* invd, i
             *failed = 1;
             if (*dInfo == 0) *dInfo = infoBase + o + c + 1;
         }
-        const double s = sqrt(d), inv = 1.0 / s;
+        // sqrt and reciprocal from one rsqrt plus a Newton correction each (the IEEE sqrt + divide
+        // sequences cost ~600 cycles per column and sit on the critical path of the whole tile)
+        const double r0 = rsqrt(d);
+        double s = d * r0;
+        s = fma(0.5 * r0, fma(-s, s, d), s);
+        const double inv = fma(r0, fma(-s, r0, 1.0), r0);
         const double l = a[c] * inv;  // lanes > c: the column entry; lane c: overwritten below
         if (lane == c) { a[c] = s; invd[o + c] = inv; }
         else if (lane > c) a[c] = l;
@@ -120,6 +126,7 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
     // 1. L11 = chol(A11)
     if (warp == 0) warp_chol32(S, invd, 0, lane, min(n, 32), failed, dInfo, infoBase, report);
     __syncthreads();
+    if (tid == 0 && report) g_leaf_clk[0] = clock64();
     // 2. warp 0: X11 = inv(L11) ; warp 1: L21 = A21 L11^-T (one row per lane, forward substitution)
     if (warp == 0) warp_trinv32(S, X, invd, 0, lane);
     else if (warp == 1) {
@@ -135,6 +142,7 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
         for (int c = 0; c < 32; c++) S[32 + lane][c] = r[c];
     }
     __syncthreads();
+    if (tid == 0 && report) g_leaf_clk[1] = clock64();
     // 3. A22 -= L21 L21^T (lower part), all threads: 4 outputs each
     for (int e = tid; e < 32 * 32; e += 256) {
         const int i = e & 31, c = e >> 5;
@@ -146,9 +154,11 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
         }
     }
     __syncthreads();
+    if (tid == 0 && report) g_leaf_clk[2] = clock64();
     // 4. L22 = chol(A22)
     if (warp == 0) warp_chol32(S, invd, 32, lane, max(0, min(n - 32, 32)), failed, dInfo, infoBase, report);
     __syncthreads();
+    if (tid == 0 && report) g_leaf_clk[3] = clock64();
     // 5. warp 0: X22 = inv(L22) ; the others: T = L21 X11 parked in X's upper-right block (transposed)
     if (warp == 0) warp_trinv32(S, X, invd, 32, lane);
     else {
@@ -160,6 +170,7 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
         }
     }
     __syncthreads();
+    if (tid == 0 && report) g_leaf_clk[4] = clock64();
     // 6. X21 = -X22 T
     for (int e = tid; e < 32 * 32; e += 256) {
         const int i = e & 31, c = e >> 5;
@@ -306,22 +317,42 @@ int launch_trtri_leaf(parsec_context_s* ctx, cudaStream_t s, const double* A, in
 // ---------------------------------------------------------------------------------------
 constexpr int PC_KC = 32;            // contraction chunk
 constexpr int PC_LD = IB + 4;        // staged operand rows: conflict-free for the 2+2 fragment layout
-constexpr int PC_SMEM = (3 * IB * (IB + 1) + 2 * 2 * PC_KC * PC_LD) * (int)sizeof(double);
+constexpr int PC_SMEM = (2 * IB * (IB + 1) + IB * PC_LD + 2 * 2 * PC_KC * PC_LD) * (int)sizeof(double);
+
+// phase clocks of the last CTA of each launch (debugging aid, read with dplasma_b200_debug_read)
+__device__ long long g_dbg_clk[16 * 8];
+#define DBG_CLK(ph)                                                                      \
+    do {                                                                                 \
+        if (tid == 0 && blockIdx.x == gridDim.x - 1 && (j0 / IB) < 16) g_dbg_clk[(j0 / IB) * 8 + (ph)] = clock64(); \
+    } while (0)
 
 __global__ void __launch_bounds__(256) potrf_colblock_kernel(double* __restrict__ A, int lda, int n, int j0,
                                                              double* __restrict__ winv, double* __restrict__ wdiag,
                                                              int* dInfo, int infoBase) {
     extern __shared__ double pc_smem[];
     double(*D)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(pc_smem);
-    double(*R)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(pc_smem + IB * LEAF_LD);
-    double(*X)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(pc_smem + 2 * IB * LEAF_LD);
-    double* stage = pc_smem + 3 * IB * LEAF_LD;  // [buf][op][PC_KC][PC_LD], op 0: rows of block j, 1: rows of block i
+    double* Rk = pc_smem + IB * LEAF_LD;  // R transposed: [col][row], stride PC_LD (A operand of R X^T)
+    double(*X)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(pc_smem + IB * LEAF_LD + IB * PC_LD);
+    double* stage = pc_smem + 2 * IB * LEAF_LD + IB * PC_LD;  // [buf][op][PC_KC][PC_LD], op 0: rows of block j, 1: block i
     __shared__ int failed;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int i0 = j0 + blockIdx.x * IB;
     const int nj = min(IB, n - j0), ni = min(IB, n - i0);
     const bool isDiag = blockIdx.x == 0;
     if (tid == 0) failed = 0;
+    DBG_CLK(0);
+    // source blocks, coalesced: D = lower triangle of A(j0.., j0..) with identity padding, Rk = A(i0.., j0..)^T
+    for (int e = tid; e < IB * IB; e += 256) {
+        const int r = e % IB, c = e / IB;
+        double dv = (r == c) ? 1.0 : 0.0;
+        if (r < nj && c < nj) dv = (r >= c) ? A[j0 + r + (size_t)(j0 + c) * lda] : 0.0;
+        D[r][c] = dv;
+        double rv = 0.0;
+        if (!isDiag && r < ni && c < nj) rv = A[i0 + r + (size_t)(j0 + c) * lda];
+        Rk[c * PC_LD + r] = rv;
+        X[r][c] = 0.0;
+    }
+    __syncthreads();  // the fragment-wise "-= acc" below touches elements other threads loaded
 
     // ---- 1. DMMA accumulation of the two 64x64 products over K = j0 ----
     // warps 0-3: D quadrants, warps 4-7: R quadrants; 32x32 per warp
@@ -394,10 +425,9 @@ __global__ void __launch_bounds__(256) potrf_colblock_kernel(double* __restrict_
         }
         __syncthreads();  // everyone is done with buf before it is refilled (two iterations ahead)
     }
-    // ---- D / R = A - acc into shared memory (identity padding beyond the ragged edge of D) ----
-    {
-        double(*Out)[LEAF_LD] = which ? R : D;
-        const int rbase = which ? i0 : j0, rlim = which ? ni : nj;
+    DBG_CLK(1);
+    // ---- D / R -= acc, in place in shared memory (the source blocks were loaded coalesced up front) ----
+    if (!(which && isDiag)) {
 #pragma unroll
         for (int j = 0; j < 4; j++)
 #pragma unroll
@@ -406,19 +436,15 @@ __global__ void __launch_bounds__(256) potrf_colblock_kernel(double* __restrict_
 #pragma unroll
                 for (int i = 0; i < 4; i++) {
                     const int row = wm0 + frag_row<32>(g, i);
-                    double v = (!which && row == col) ? 1.0 : 0.0;
-                    if (row < rlim && col < nj && !(which && isDiag)) {
-                        if (which || row >= col) v = A[rbase + row + (size_t)(j0 + col) * lda] - acc[i][j][h];
-                        else v = 0.0;
-                    }
-                    Out[row][col] = v;
+                    if (which) Rk[col * PC_LD + row] -= acc[i][j][h];
+                    else if (row >= col && row < nj) D[row][col] -= acc[i][j][h];
                 }
             }
     }
-    for (int e = tid; e < IB * IB; e += 256) X[e % IB][e / IB] = 0.0;
     __syncthreads();
-    // ---- 2. factor and invert the diagonal block (redundantly in every CTA: no inter-CTA sync) ----
+    DBG_CLK(2);
     leaf_fast_64(D, X, nj, tid, &failed, dInfo, infoBase + j0, isDiag);
+    DBG_CLK(3);
     // ---- 3. write back ----
     if (isDiag) {
         for (int e = tid; e < IB * IB; e += 256) {
@@ -427,14 +453,55 @@ __global__ void __launch_bounds__(256) potrf_colblock_kernel(double* __restrict_
             winv[e] = (i >= j) ? X[i][j] : 0.0;
         }
     } else {
-        // A(i0.., j0..) = R X^T : out(r,c) = sum_{k<=c} R(r,k) X(c,k)
-        const int r = tid & (IB - 1);
-        for (int c = (tid >> 6); c < nj; c += 4) {
-            double sum = 0.0;
-            for (int k = 0; k <= c; k++) sum += R[r][k] * X[c][k];
-            if (r < ni) A[i0 + r + (size_t)(j0 + c) * lda] = sum;
+        // A(i0.., j0..) = R X^T : out(r,c) = sum_k Rk[k][r] Xk[k][c], Xk = X^T staged in the (free) operand buffers
+        double* Xk = stage;
+        for (int e = tid; e < IB * IB; e += 256) {
+            const int c = e % IB, k = e / IB;
+            Xk[k * PC_LD + c] = (c >= k) ? X[c][k] : 0.0;
         }
+        __syncthreads();
+        const int pm0 = (warp & 1) * 32, pn0 = (warp >> 1) * 16;  // 8 warps: 2 x 4, 32 x 16 each
+        double o[4][2][2];
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j < 2; j++) o[i][j][0] = o[i][j][1] = 0.0;
+#pragma unroll
+        for (int ks = 0; ks < IB / 4; ks++) {
+            double a[4], bb[2];
+            const double* ra = Rk + (ks * 4 + t) * PC_LD + pm0 + 2 * g;
+            const double2 y = *reinterpret_cast<const double2*>(Xk + (ks * 4 + t) * PC_LD + pn0 + 2 * g);
+            bb[0] = y.x; bb[1] = y.y;
+#pragma unroll
+            for (int v = 0; v < 2; v++) {
+                const double2 x = *reinterpret_cast<const double2*>(ra + 16 * v);
+                a[2 * v] = x.x; a[2 * v + 1] = x.y;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+                for (int j = 0; j < 2; j++) dmma884(o[i][j][0], o[i][j][1], a[i], bb[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 2; j++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const int col = pn0 + frag_col(2 * t + h, j);
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int row = pm0 + frag_row<32>(g, i);
+                    if (row < ni && col < nj) A[i0 + row + (size_t)(j0 + col) * lda] = o[i][j][h];
+                }
+            }
     }
+    DBG_CLK(4);
+}
+
+extern "C" int dplasma_b200_debug_read(long long* out, int n) {
+    return (int)cudaMemcpyFromSymbol(out, g_dbg_clk, sizeof(long long) * (n < 128 ? n : 128));
+}
+extern "C" int dplasma_b200_debug_read_leaf(long long* out) {
+    return (int)cudaMemcpyFromSymbol(out, g_leaf_clk, sizeof(long long) * 8);
 }
 
 // put the factored diagonal blocks (lower triangles) of an n x n tile in place
@@ -553,6 +620,166 @@ int launch_zpotrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda
         attr = true;
     }
     zpotrf_leaf_kernel<<<1, 256, smem, s>>>(A, lda, n, winv, dInfo, infoBase);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------
+// Fused panel solve  B <- B L^-T  for all tiles below the diagonal tile (cublasDtrsm Right /
+// Lower / Trans at src/zpotrf_L.jdf:236-240), ONE launch per step.  Rows are independent, so a
+// CTA owns a 64-row strip of one tile and walks the nb/64 block columns by itself:
+//     T   = B(strip, j) - sum_{l<j} X(strip, l) L(j, l)^T        (DMMA, K = 64 j)
+//     X_j = T inv(L_jj)^T                                         (DMMA, K = 64; inverse from the leaf)
+// X_j is written in place and read back (L2) as an operand of the later block columns.
+// ---------------------------------------------------------------------------------------
+constexpr int TP_SMEM = (2 * IB * PC_LD + 2 * 2 * PC_KC * PC_LD) * (int)sizeof(double);
+
+__global__ void __launch_bounds__(256) trsm_panel_fused_kernel(const double* __restrict__ L, int ldl, int n,
+                                                               const double* __restrict__ winv, double* B, int ldb,
+                                                               long long tileStride, int rowsPerTile, int lastTileRows,
+                                                               int ntiles) {
+    extern __shared__ double tp_smem[];
+    double* Tk = tp_smem;                 // [k][row], stride PC_LD : T transposed = A operand of the inverse product
+    double* Wk = Tk + IB * PC_LD;         // [k][col], stride PC_LD : inv(L_jj)^T as B operand
+    double* stage = Wk + IB * PC_LD;      // [buf][op][PC_KC][PC_LD]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int spt = (rowsPerTile + IB - 1) / IB;
+    const int b = blockIdx.x / spt, r0 = (blockIdx.x - b * spt) * IB;
+    const int rows = (b == ntiles - 1) ? lastTileRows : rowsPerTile;
+    const int nr = min(IB, rows - r0);
+    if (nr <= 0) return;
+    double* Bs = B + (size_t)b * tileStride + r0;
+    // 8 warps: 2 (rows) x 4 (cols), 32 x 16 each
+    const int wm0 = (warp & 1) * 32, wn0 = (warp >> 1) * 16;
+    const int g = lane >> 2, t = lane & 3;
+    const bool aligned = ((ldb & 1) == 0) && ((ldl & 1) == 0) && ((reinterpret_cast<uintptr_t>(B) & 15) == 0) &&
+                         ((reinterpret_cast<uintptr_t>(L) & 15) == 0) && ((tileStride & 1) == 0) && (nr == IB);
+    const int nblk = (n + IB - 1) / IB;
+    for (int jb = 0; jb < nblk; jb++) {
+        const int j0 = jb * IB, nj = min(IB, n - j0);
+        double acc[4][2][2];
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j < 2; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+        const int nChunks = j0 / PC_KC;  // j0 is a multiple of 64
+        const bool async16 = aligned && (nj == IB);
+        auto load_chunk = [&](int c, int buf) {
+            double* dst = stage + (size_t)buf * 2 * PC_KC * PC_LD;
+            if (async16) {
+                for (int e = tid; e < 2 * PC_KC * (IB / 2); e += 256) {
+                    const int op = e / (PC_KC * (IB / 2)), r2 = e % (IB / 2), kk = (e / (IB / 2)) % PC_KC;
+                    const int k = c * PC_KC + kk;
+                    const double* src = op ? L + (j0 + 2 * r2) + (size_t)k * ldl : Bs + 2 * r2 + (size_t)k * ldb;
+                    const uint32_t d32 = smem_u32(dst + (op * PC_KC + kk) * PC_LD + 2 * r2);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d32), "l"(src) : "memory");
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            } else {
+                for (int e = tid; e < 2 * PC_KC * IB; e += 256) {
+                    const int op = e / (PC_KC * IB), r = e % IB, kk = (e / IB) % PC_KC;
+                    const int k = c * PC_KC + kk;
+                    double v = 0.0;
+                    if (op == 0) { if (r < nr) v = __ldcg(Bs + r + (size_t)k * ldb); }
+                    else if (r < nj) v = L[(j0 + r) + (size_t)k * ldl];
+                    dst[(op * PC_KC + kk) * PC_LD + r] = v;
+                }
+            }
+        };
+        if (nChunks > 0) load_chunk(0, 0);
+        for (int c = 0; c < nChunks; c++) {
+            const int buf = c & 1;
+            if (c + 1 < nChunks) load_chunk(c + 1, buf ^ 1);
+            if (async16) {
+                if (c + 1 < nChunks) asm volatile("cp.async.wait_group 1;" ::: "memory");
+                else asm volatile("cp.async.wait_group 0;" ::: "memory");
+            }
+            __syncthreads();
+            const double* sX = stage + (size_t)buf * 2 * PC_KC * PC_LD;
+            const double* sL = sX + PC_KC * PC_LD;
+#pragma unroll
+            for (int ks = 0; ks < PC_KC / 4; ks++) {
+                double a[4], bb[2];
+                const double* ra = sX + (ks * 4 + t) * PC_LD + wm0 + 2 * g;
+                const double2 y = *reinterpret_cast<const double2*>(sL + (ks * 4 + t) * PC_LD + wn0 + 2 * g);
+                bb[0] = y.x; bb[1] = y.y;
+#pragma unroll
+                for (int v = 0; v < 2; v++) {
+                    const double2 x = *reinterpret_cast<const double2*>(ra + 16 * v);
+                    a[2 * v] = x.x; a[2 * v + 1] = x.y;
+                }
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int j = 0; j < 2; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], bb[j]);
+            }
+            __syncthreads();
+        }
+        // T = B(strip, j) - acc, stored transposed; W = inv(L_jj) as [k][col]
+#pragma unroll
+        for (int j = 0; j < 2; j++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const int col = wn0 + frag_col(2 * t + h, j);
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int row = wm0 + frag_row<32>(g, i);
+                    double v = 0.0;
+                    if (row < nr && col < nj) v = __ldcg(Bs + row + (size_t)(j0 + col) * ldb) - acc[i][j][h];
+                    Tk[col * PC_LD + row] = v;
+                }
+            }
+        const double* Wj = winv + (size_t)jb * IB * IB;
+        for (int e = tid; e < IB * IB; e += 256) Wk[(e / IB) * PC_LD + (e % IB)] = Wj[e];  // Wk[k][c] = W(c,k)
+        __syncthreads();
+        // X_j = T W^T : out(row, c) = sum_k Tk[k][row] Wk[k][c]
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+            for (int j = 0; j < 2; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+#pragma unroll
+        for (int ks = 0; ks < IB / 4; ks++) {
+            double a[4], bb[2];
+            const double* ra = Tk + (ks * 4 + t) * PC_LD + wm0 + 2 * g;
+            const double2 y = *reinterpret_cast<const double2*>(Wk + (ks * 4 + t) * PC_LD + wn0 + 2 * g);
+            bb[0] = y.x; bb[1] = y.y;
+#pragma unroll
+            for (int v = 0; v < 2; v++) {
+                const double2 x = *reinterpret_cast<const double2*>(ra + 16 * v);
+                a[2 * v] = x.x; a[2 * v + 1] = x.y;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+                for (int j = 0; j < 2; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], bb[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 2; j++)
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const int col = wn0 + frag_col(2 * t + h, j);
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int row = wm0 + frag_row<32>(g, i);
+                    if (row < nr && col < nj) Bs[row + (size_t)(j0 + col) * ldb] = acc[i][j][h];
+                }
+            }
+        __threadfence_block();
+        __syncthreads();  // X_j visible to the whole CTA before it is read back as an operand; Tk/Wk free
+    }
+}
+
+int launch_trsm_panel_fused(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, int n, const double* winv,
+                            double* B, int ldb, long long tileStride, int rowsPerTile, int lastTileRows, int ntiles) {
+    if (ntiles <= 0 || n <= 0) return 0;
+    static bool attr = false;
+    if (!attr) {
+        DPB_CUDA(cudaFuncSetAttribute(trsm_panel_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM));
+        attr = true;
+    }
+    const int spt = (rowsPerTile + IB - 1) / IB;
+    trsm_panel_fused_kernel<<<ntiles * spt, 256, TP_SMEM, s>>>(L, ldl, n, winv, B, ldb, tileStride, rowsPerTile,
+                                                                lastTileRows, ntiles);
     ctx->launches++;
     return (int)cudaGetLastError();
 }

@@ -113,6 +113,16 @@ static int trsm_rec(parsec_context_s* ctx, cudaStream_t s, const double* L, int 
 int trsm_panel_lower(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, int n, const double* winv,
                      double* B, int ldb, int M, int batch, long long strideB, int lastBatchM) {
     if (batch <= 0 || M <= 0) return 0;
+    static int mode = -1;  // DPB_TRSM=rec selects the recursive multi-launch variant
+    if (mode < 0) {
+        const char* e = getenv("DPB_TRSM");
+        mode = (e && e[0] == 'r') ? 1 : 0;
+    }
+    // Many tiles below the diagonal: the step is bound by the bulk update and the panel has slack, so
+    // the recursive form wins (its products run on the 3-CTA/SM GEMM engine at full rate).  Few tiles:
+    // the panel IS the critical path and the single-launch fused kernel wins on latency.
+    if (mode == 0 && !ctx->cplx && (long long)batch * M <= 20LL * 512)
+        return launch_trsm_panel_fused(ctx, s, L, ldl, n, winv, B, ldb, strideB, M, lastBatchM, batch);
     return trsm_rec(ctx, s, L, ldl, winv, 0, n, B, ldb, M, batch, strideB, lastBatchM);
 }
 
