@@ -81,6 +81,9 @@ struct parsec_context_s {
     void* commRow = nullptr;
     void* commCol = nullptr;
     int gridP = 0, gridQ = 0;
+    parsec_taskpool_s* curTp = nullptr;  // taskpool being enqueued (for early write-back of finished columns)
+    int earlyOut = 0;                    // columns of curTp already written back by the copy stream
+    std::vector<cudaEvent_t> evIn;       // per local tile column: its host-to-device copy has landed (pipelined stage-in)
     int cplx = 0;         // set by the drivers while they work on a complex (esz = 2) matrix
     int gemmPreload = 1;  // internal products preload C into the accumulators; the tile seam API does not
     // optional per-kernel profile of the trailing-update launches (bench.py roofline leg)
@@ -142,6 +145,9 @@ int ensure_wnorm(parsec_context_s* ctx, size_t n);
 int stage_in(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* out, bool copyData, int uploOnly);
 int stage_out(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int uploOnly);
 void stage_free(DevMatrix* dm);
+int stage_in_pipelined(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* out, int uploOnly);
+int stage_out_column(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, int uploOnly,
+                     cudaEvent_t ready);
 // comm.cu
 int sum_allreduce(parsec_context_s* ctx, double* dbuf, size_t n, cudaStream_t s);
 int bcast(parsec_context_s* ctx, void* comm, const double* send, double* recv, size_t count, int root, cudaStream_t s);
@@ -163,5 +169,5 @@ int check_update_multi(parsec_context_s* ctx, const DevMatrix& L, const DevMatri
 int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp);
 int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,
                     long long rowStride, const double* colPanel, long long colStride, int gnFirst,
-                    int gnEnd, double alpha, int K);
+                    int gnEnd, double alpha, int K, int kTile = 0, long long kTileStride = 0);
 }  // namespace dpb

@@ -72,6 +72,11 @@ __device__ __forceinline__ void leaf_cholesky_64(double (*S)[IB + 1], int n, int
 // 256 threads.  info rule as leaf_cholesky_64.
 // ---------------------------------------------------------------------------------------
 __device__ long long g_leaf_clk[8];
+#ifdef DPB_DEBUG_CLOCKS
+#define LEAF_CLK(i) do { if (tid == 0 && report) g_leaf_clk[i] = clock64(); } while (0)
+#else
+#define LEAF_CLK(i) do { } while (0)
+#endif
 // warp-level: lane r owns row r of the 32x32 block at S[o..o+32)[o..o+32)
 __device__ __forceinline__ void warp_chol32(double (*S)[IB + 1], double* invd, int o, int lane, int nvalid,
                                             int* failed, int* dInfo, int infoBase, bool report) {
@@ -126,7 +131,7 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
     // 1. L11 = chol(A11)
     if (warp == 0) warp_chol32(S, invd, 0, lane, min(n, 32), failed, dInfo, infoBase, report);
     __syncthreads();
-    if (tid == 0 && report) g_leaf_clk[0] = clock64();
+    LEAF_CLK(0);
     // 2. warp 0: X11 = inv(L11) ; warp 1: L21 = A21 L11^-T (one row per lane, forward substitution)
     if (warp == 0) warp_trinv32(S, X, invd, 0, lane);
     else if (warp == 1) {
@@ -142,7 +147,7 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
         for (int c = 0; c < 32; c++) S[32 + lane][c] = r[c];
     }
     __syncthreads();
-    if (tid == 0 && report) g_leaf_clk[1] = clock64();
+    LEAF_CLK(1);
     // 3. A22 -= L21 L21^T (lower part), all threads: 4 outputs each
     for (int e = tid; e < 32 * 32; e += 256) {
         const int i = e & 31, c = e >> 5;
@@ -154,11 +159,11 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
         }
     }
     __syncthreads();
-    if (tid == 0 && report) g_leaf_clk[2] = clock64();
+    LEAF_CLK(2);
     // 4. L22 = chol(A22)
     if (warp == 0) warp_chol32(S, invd, 32, lane, max(0, min(n - 32, 32)), failed, dInfo, infoBase, report);
     __syncthreads();
-    if (tid == 0 && report) g_leaf_clk[3] = clock64();
+    LEAF_CLK(3);
     // 5. warp 0: X22 = inv(L22) ; the others: T = L21 X11 parked in X's upper-right block (transposed)
     if (warp == 0) warp_trinv32(S, X, invd, 32, lane);
     else {
@@ -170,7 +175,7 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
         }
     }
     __syncthreads();
-    if (tid == 0 && report) g_leaf_clk[4] = clock64();
+    LEAF_CLK(4);
     // 6. X21 = -X22 T
     for (int e = tid; e < 32 * 32; e += 256) {
         const int i = e & 31, c = e >> 5;
@@ -319,12 +324,16 @@ constexpr int PC_KC = 32;            // contraction chunk
 constexpr int PC_LD = IB + 4;        // staged operand rows: conflict-free for the 2+2 fragment layout
 constexpr int PC_SMEM = (2 * IB * (IB + 1) + IB * PC_LD + 2 * 2 * PC_KC * PC_LD) * (int)sizeof(double);
 
-// phase clocks of the last CTA of each launch (debugging aid, read with dplasma_b200_debug_read)
+// phase clocks of the last CTA of each launch (build with -DDPB_DEBUG_CLOCKS; tools/tile_phases.py reads them)
 __device__ long long g_dbg_clk[16 * 8];
+#ifdef DPB_DEBUG_CLOCKS
 #define DBG_CLK(ph)                                                                      \
     do {                                                                                 \
         if (tid == 0 && blockIdx.x == gridDim.x - 1 && (j0 / IB) < 16) g_dbg_clk[(j0 / IB) * 8 + (ph)] = clock64(); \
     } while (0)
+#else
+#define DBG_CLK(ph) do { } while (0)
+#endif
 
 __global__ void __launch_bounds__(256) potrf_colblock_kernel(double* __restrict__ A, int lda, int n, int j0,
                                                              double* __restrict__ winv, double* __restrict__ wdiag,

@@ -27,7 +27,7 @@ static cudaEvent_t get_event(parsec_context_s* ctx, size_t idx) {
 // gnFirst <= gn < gnEnd and gm >= gn; diagonal tiles only in their lower part (SYRK).
 int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,
                     long long rowStride, const double* colPanel, long long colStride, int gnFirst, int gnEnd,
-                    double alpha, int K) {
+                    double alpha, int K, int kTile, long long kTileStride) {
     const int jl0 = C.firstLocalColGE(gnFirst), jl1 = std::min(C.firstLocalColGE(gnEnd), C.lnt);
     const int rowEnd = std::min(C.firstLocalRowGE(C.mt), C.lmt);
     for (int c0 = jl0; c0 < jl1; c0 += kMaxCols) {
@@ -38,6 +38,10 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
         d.a_kmajor = d.b_kmajor = 0;
         d.preload = 1;
         d.kTile = 1 << 30; d.aKTileStride = d.bKTileStride = 0;
+        if (kTile > 0) {  // the contraction runs over several tiles of a tile row (left-looking update)
+            d.kTile = kTile;
+            d.aKTileStride = d.bKTileStride = kTileStride;
+        }
         d.Cbase = C.base; d.rowPanel = rowPanel; d.colPanel = colPanel;
         d.rowPanelStride = rowStride; d.colPanelStride = colStride; d.tileElems = C.tileElems;
         d.tileLdT = C.lmt; d.nb = C.nb;
@@ -47,7 +51,7 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
         d.mtGlobal = C.mt; d.ntGlobal = C.nt;
         d.rowEnd = rowEnd;
         if (ctx->cplx) d.fast = (K % 8 == 0) ? 1 : 0;
-        else d.fast = ((C.nb % 2 == 0) && (K % 16 == 0) && ((reinterpret_cast<uintptr_t>(rowPanel) & 15) == 0) &&
+        else d.fast = ((C.nb % 2 == 0) && (K % 16 == 0) && (kTile % 16 == 0) && (kTileStride % 2 == 0) && ((reinterpret_cast<uintptr_t>(rowPanel) & 15) == 0) &&
                   ((reinterpret_cast<uintptr_t>(colPanel) & 15) == 0) && (rowStride % 2 == 0) &&
                   (colStride % 2 == 0))
                      ? 1 : 0;
@@ -144,7 +148,49 @@ static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
     DPB_CUDA(cudaStreamWaitEvent(su, ev0, 0));
     size_t evi = 1;
     cudaEvent_t evUpdPrev = nullptr;
-    for (int k = 0; k < nt; k++) {
+    int kStart = 0;
+    if (!ctx->evIn.empty() && (int)ctx->evIn.size() == nt && nt >= 8 && !ctx->cplx) {
+        // ---- pipelined stage-in: the host matrix is still arriving, tile column by tile column.
+        // Start LEFT-looking on the columns that are here (column j needs only columns <= j):
+        //   A(j.., j) -= A(j.., 0:j) A(j, 0:j)^T ; POTRF(j,j) ; TRSM(j+1.., j)
+        // then bring the rest of the matrix up to date in one grouped launch and go on right-looking.
+        const int cstar = nt / 4;
+        const long long kts = (long long)A.lmt * A.tileElems;
+        for (int j = 0; j < cstar; j++) {
+            DPB_CUDA(cudaStreamWaitEvent(sp, ctx->evIn[j], 0));
+            if (j > 0) {
+                rc = trailing_update(ctx, sp, A, A.tile(0, 0), A.tileElems, A.tile(0, 0), A.tileElems, j, j + 1, -1.0,
+                                     j * nb, nb, kts);
+                if (rc) return rc;
+            }
+            double* winv = ctx->wInv + (size_t)(j & 1) * ctx->wInvSlot;
+            rc = potrf_tile_fused(ctx, sp, A.tile(j, j), A.mb, nb, winv, ctx->dInfo, j * nb);
+            if (rc) return rc;
+            rc = trsm_panel_lower(ctx, sp, A.tile(j, j), A.mb, nb, winv, A.tile(j + 1, j), A.mb, A.mb, nt - j - 1,
+                                  A.tileElems, A.rowsOfTile(nt - 1));
+            if (rc) return rc;
+            cudaEvent_t evCol = get_event(ctx, evi++);
+            DPB_CUDA(cudaEventRecord(evCol, sp));
+            if (ctx->curTp && ctx->earlyOut >= 0) {
+                rc = stage_out_column(ctx, ctx->curTp->A, &ctx->curTp->dA, j, dplasmaLower, evCol);
+                if (rc) return rc;
+                ctx->earlyOut = j + 1;
+            }
+        }
+        DPB_CUDA(cudaStreamWaitEvent(sp, ctx->evIn[nt - 1], 0));  // copies are in order: everything has landed
+        rc = trailing_update(ctx, sp, A, A.tile(0, 0), A.tileElems, A.tile(0, 0), A.tileElems, cstar, nt, -1.0,
+                             cstar * nb, nb, kts);
+        if (rc) return rc;
+        cudaEvent_t evCatch = get_event(ctx, evi++);
+        DPB_CUDA(cudaEventRecord(evCatch, sp));
+        DPB_CUDA(cudaStreamWaitEvent(su, evCatch, 0));
+        kStart = cstar;
+    } else if (!ctx->evIn.empty()) {
+        // not eligible for the left-looking start: wait for the whole matrix
+        DPB_CUDA(cudaStreamWaitEvent(sp, ctx->evIn.back(), 0));
+        DPB_CUDA(cudaStreamWaitEvent(su, ctx->evIn.back(), 0));
+    }
+    for (int k = kStart; k < nt; k++) {
         const int tk = A.rowsOfTile(k);
         double* winv = ctx->wInv + (size_t)(k & 1) * ctx->wInvSlot;
         double* Akk = A.tile(k, k);
@@ -159,6 +205,12 @@ static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
         trace_mark(sp, k, 1);
         cudaEvent_t evPanel = get_event(ctx, evi++);
         DPB_CUDA(cudaEventRecord(evPanel, sp));
+        // tile column k is final: a staged (host) matrix gets it back now, underneath the remaining steps
+        if (ctx->curTp && ctx->earlyOut >= 0) {
+            rc = stage_out_column(ctx, ctx->curTp->A, &ctx->curTp->dA, k, dplasmaLower, evPanel);
+            if (rc) return rc;
+            ctx->earlyOut = k + 1;
+        }
         const double* panel = A.tile(0, k);  // tile (i,k) at panel + i*tileElems
         // look-ahead: tile column k+1 on the panel stream (after the previous bulk update wrote it)
         if (evUpdPrev) DPB_CUDA(cudaStreamWaitEvent(sp, evUpdPrev, 0));
@@ -275,19 +327,52 @@ int parsec_context_start(parsec_context_t* ctx) {
     if (!ctx) return -1;
     cudaSetDevice(ctx->device);
     DPB_CUDA(cudaMemsetAsync(ctx->dInfo, 0, sizeof(int), ctx->sPanel));
+    for (cudaEvent_t e : ctx->evIn) cudaEventDestroy(e);
+    ctx->evIn.clear();
     for (parsec_taskpool_s* tp : ctx->queue) {
         if (tp->kind != TP_POTRF) continue;
-        int rc = stage_in(ctx, tp->A, &tp->dA, true, tp->uplo);
+        // A single queued lower factorization of a host matrix in TILE storage, one process: pipeline the
+        // stage-in with a left-looking start.  Everything else: plain stage-in.
+        const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)tp->A;
+        cudaPointerAttributes at;
+        bool onDevice = cudaPointerGetAttributes(&at, bc->mat) == cudaSuccess &&
+                        (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged);
+        cudaGetLastError();
+        const bool pipe = ctx->queue.size() == 1 && tp->uplo == dplasmaLower && tp->A->super.nodes == 1 &&
+                          tp->A->storage == PARSEC_MATRIX_TILE && tp->A->mtype == PARSEC_MATRIX_DOUBLE && !onDevice &&
+                          tp->A->m % tp->A->mb == 0 && !getenv("DPB_NO_PIPELINE");
+        int rc = pipe ? stage_in_pipelined(ctx, tp->A, &tp->dA, tp->uplo) : stage_in(ctx, tp->A, &tp->dA, true, tp->uplo);
         if (rc) return rc;
         tp->staged = true;
     }
     DPB_CUDA(cudaEventRecord(ctx->evStart, ctx->sPanel));
-    for (parsec_taskpool_s* tp : ctx->queue) {
+    std::vector<int> early(ctx->queue.size(), 0);
+    for (size_t i = 0; i < ctx->queue.size(); i++) {
+        parsec_taskpool_s* tp = ctx->queue[i];
+        // early column write-back: single-process lower factorizations of staged matrices
+        const bool canEarly = tp->dA.owned && tp->uplo == dplasmaLower && tp->dA.P * tp->dA.Q == 1;
+        ctx->curTp = canEarly ? tp : nullptr;
+        ctx->earlyOut = canEarly ? 0 : -1;
         int rc = potrf_enqueue(ctx, tp);
+        early[i] = canEarly ? ctx->earlyOut : 0;
+        ctx->curTp = nullptr;
         if (rc) return rc;
     }
     DPB_CUDA(cudaEventRecord(ctx->evStop, ctx->sPanel));
-    for (parsec_taskpool_s* tp : ctx->queue) {
+    for (size_t i = 0; i < ctx->queue.size(); i++) {
+        parsec_taskpool_s* tp = ctx->queue[i];
+        if (early[i] > 0) {
+            // columns [0, early) already went out on the copy stream; the rest follow on the panel stream
+            for (int jl = early[i]; jl < tp->dA.lnt; jl++) {
+                cudaEvent_t e;
+                cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+                cudaEventRecord(e, ctx->sPanel);
+                int rc = stage_out_column(ctx, tp->A, &tp->dA, jl, tp->uplo, e);
+                cudaEventDestroy(e);
+                if (rc) return rc;
+            }
+            continue;
+        }
         int rc = stage_out(ctx, tp->A, &tp->dA, tp->uplo);
         if (rc) return rc;
     }
@@ -299,6 +384,7 @@ int parsec_context_wait(parsec_context_t* ctx) {
     if (!ctx) return -1;
     DPB_CUDA(cudaStreamSynchronize(ctx->sPanel));
     DPB_CUDA(cudaStreamSynchronize(ctx->sUpdate));
+    DPB_CUDA(cudaStreamSynchronize(ctx->sCopy));
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, ctx->evStart, ctx->evStop) == cudaSuccess) ctx->lastElapsed = ms * 1e-3;
     dpb::trace_dump();

@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include "internal.h"
 
 using namespace dpb;
@@ -47,6 +48,7 @@ int parsec_fini(parsec_context_t** pctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     comm_destroy(ctx);
+    for (cudaEvent_t e : ctx->evIn) cudaEventDestroy(e);
     for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
     if (ctx->wInv) cudaFree(ctx->wInv);
     if (ctx->wNorm) cudaFree(ctx->wNorm);
@@ -201,53 +203,70 @@ static int describe(const parsec_tiled_matrix_t* A, DevMatrix* dm) {
     return 0;
 }
 
-// Copies between the caller's layout and the regular device tile grid.  dir 0: in, 1: out.
-static int copy_layout(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int dir, int uploOnly) {
+// Copies one local tile column between the caller's layout and the regular device tile grid.
+// dir 0: in, 1: out.  Only the `part` triangle moves (dplasmaUpperLower: everything).
+static int copy_column(const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, int dir, int part, cudaStream_t s) {
     const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
     double* user = (double*)bc->mat;
-    cudaStream_t s = ctx->sPanel;
     const bool sym = bc->uplo != dplasmaUpperLower;
-    const int part = sym ? bc->uplo : uploOnly;  // which tiles move
+    const int gn = jl * dm->Q + dm->pcol;
+    int i0 = 0, i1 = dm->lmt;
+    if (part == dplasmaLower) i0 = dm->firstLocalRowGE(gn);
+    else if (part == dplasmaUpper) i1 = dm->firstLocalRowGE(gn + 1);
+    if (i1 > dm->lmt) i1 = dm->lmt;
+    if (i0 >= i1) return 0;
     if (A->storage == PARSEC_MATRIX_TILE) {
-        size_t packed = 0;  // running tile offset in a sym-packed array
-        for (int jl = 0; jl < dm->lnt; jl++) {
-            const int gn = jl * dm->Q + dm->pcol;
-            int i0 = 0, i1 = dm->lmt;
-            if (part == dplasmaLower) i0 = dm->firstLocalRowGE(gn);
-            else if (part == dplasmaUpper) i1 = dm->firstLocalRowGE(gn + 1);
-            if (i1 > dm->lmt) i1 = dm->lmt;
-            if (i0 >= i1) continue;
-            const size_t cnt = (size_t)(i1 - i0) * dm->tileElems;
-            double* dev = dm->tile(i0, jl);
-            double* usr = sym ? user + packed * dm->tileElems
-                              : user + ((size_t)i0 + (size_t)jl * dm->lmt) * dm->tileElems;
-            packed += (size_t)(i1 - i0);
-            if (dir == 0) DPB_CUDA(cudaMemcpyAsync(dev, usr, cnt * sizeof(double), cudaMemcpyDefault, s));
-            else DPB_CUDA(cudaMemcpyAsync(usr, dev, cnt * sizeof(double), cudaMemcpyDefault, s));
-        }
-    } else {
-        // LAPACK storage: pitched copies, one per tile (src/dplasmajdf_lapack_dtt.h:161-178,238-255)
-        const size_t lld = (size_t)A->llm, eb = 8 * (size_t)dm->esz;
-        for (int jl = 0; jl < dm->lnt; jl++) {
-            const int gn = jl * dm->Q + dm->pcol;
-            const int tn = dm->colsOfTile(gn);
-            for (int il = 0; il < dm->lmt; il++) {
-                const int gm = il * dm->P + dm->prow;
-                if (part == dplasmaLower && gm < gn) continue;
-                if (part == dplasmaUpper && gm > gn) continue;
-                const int tm = dm->rowsOfTile(gm);
-                double* dev = dm->tile(il, jl);
-                double* usr = user + ((size_t)il * dm->mb + (size_t)jl * dm->nb * lld) * dm->esz;
-                if (dir == 0)
-                    DPB_CUDA(cudaMemcpy2DAsync(dev, (size_t)dm->mb * eb, usr, lld * eb, (size_t)tm * eb, tn,
-                                               cudaMemcpyDefault, s));
-                else
-                    DPB_CUDA(cudaMemcpy2DAsync(usr, lld * eb, dev, (size_t)dm->mb * eb, (size_t)tm * eb, tn,
-                                               cudaMemcpyDefault, s));
+        size_t packed = 0;  // tile offset of this column in a sym-packed array
+        if (sym)
+            for (int j = 0; j < jl; j++) {
+                const int g = j * dm->Q + dm->pcol;
+                int a = 0, b = dm->lmt;
+                if (bc->uplo == dplasmaLower) a = dm->firstLocalRowGE(g);
+                else b = std::min(dm->firstLocalRowGE(g + 1), dm->lmt);
+                if (b > a) packed += (size_t)(b - a);
             }
-        }
+        const size_t cnt = (size_t)(i1 - i0) * dm->tileElems;
+        double* dev = dm->tile(i0, jl);
+        double* usr = sym ? user + packed * dm->tileElems : user + ((size_t)i0 + (size_t)jl * dm->lmt) * dm->tileElems;
+        if (dir == 0) DPB_CUDA(cudaMemcpyAsync(dev, usr, cnt * sizeof(double), cudaMemcpyDefault, s));
+        else DPB_CUDA(cudaMemcpyAsync(usr, dev, cnt * sizeof(double), cudaMemcpyDefault, s));
+        return 0;
+    }
+    // LAPACK storage: pitched copies, one per tile (src/dplasmajdf_lapack_dtt.h:161-178,238-255)
+    const size_t lld = (size_t)A->llm, eb = 8 * (size_t)dm->esz;
+    const int tn = dm->colsOfTile(gn);
+    for (int il = i0; il < i1; il++) {
+        const int gm = il * dm->P + dm->prow;
+        const int tm = dm->rowsOfTile(gm);
+        double* dev = dm->tile(il, jl);
+        double* usr = user + ((size_t)il * dm->mb + (size_t)jl * dm->nb * lld) * dm->esz;
+        if (dir == 0)
+            DPB_CUDA(cudaMemcpy2DAsync(dev, (size_t)dm->mb * eb, usr, lld * eb, (size_t)tm * eb, tn, cudaMemcpyDefault, s));
+        else
+            DPB_CUDA(cudaMemcpy2DAsync(usr, lld * eb, dev, (size_t)dm->mb * eb, (size_t)tm * eb, tn, cudaMemcpyDefault, s));
     }
     return 0;
+}
+
+static int copy_layout(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int dir, int uploOnly) {
+    const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
+    const bool sym = bc->uplo != dplasmaUpperLower;
+    const int part = sym ? bc->uplo : uploOnly;  // which tiles move
+    for (int jl = 0; jl < dm->lnt; jl++) {
+        int rc = copy_column(A, dm, jl, dir, part, ctx->sPanel);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+// Early write-back of one finished tile column on the copy stream (overlaps the rest of the factorization).
+int stage_out_column(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, int uploOnly,
+                     cudaEvent_t ready) {
+    if (!dm->owned) return 0;
+    const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
+    const int part = (bc->uplo != dplasmaUpperLower) ? bc->uplo : uploOnly;
+    DPB_CUDA(cudaStreamWaitEvent(ctx->sCopy, ready, 0));
+    return copy_column(A, dm, jl, 1, part, ctx->sCopy);
 }
 
 int stage_in(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, bool copyData, int uploOnly) {
@@ -269,6 +288,31 @@ int stage_in(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* d
     DPB_CUDA(cudaMalloc(&dm->base, elems * sizeof(double)));
     dm->owned = true;
     if (copyData) return copy_layout(ctx, A, dm, 0, uploOnly);
+    return 0;
+}
+
+// Stage-in that does not wait: tile columns travel left to right on the copy stream, one event each,
+// so that a left-looking start of the factorization can consume them as they arrive.
+int stage_in_pipelined(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int uploOnly) {
+    int rc = describe(A, dm);
+    if (rc) return -100 + rc;
+    const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
+    if (!bc->mat) return -110;
+    size_t elems = (size_t)dm->lmt * dm->lnt * dm->tileElems;
+    if (elems == 0) elems = 1;
+    DPB_CUDA(cudaMalloc(&dm->base, elems * sizeof(double)));
+    dm->owned = true;
+    const int part = (bc->uplo != dplasmaUpperLower) ? bc->uplo : uploOnly;
+    for (cudaEvent_t e : ctx->evIn) cudaEventDestroy(e);
+    ctx->evIn.clear();
+    for (int jl = 0; jl < dm->lnt; jl++) {
+        rc = copy_column(A, dm, jl, 0, part, ctx->sCopy);
+        if (rc) return rc;
+        cudaEvent_t e;
+        DPB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        DPB_CUDA(cudaEventRecord(e, ctx->sCopy));
+        ctx->evIn.push_back(e);
+    }
     return 0;
 }
 

@@ -227,6 +227,22 @@ def test_dpotrf_fast_path_vs_oracle(ctx, oracle, N, nb, uplo):
     d.free()
 
 
+@pytest.mark.parametrize("kind", ["tile", "sym"])
+def test_dpotrf_host_matrix_pipelined_stage_in(ctx, oracle, kind):
+    """host matrices with enough tile columns take the pipelined path: left-looking start while the
+    columns arrive, one catch-up update, right-looking rest, finished columns written back early"""
+    N, nb = 2048, 128   # 16 tile columns -> 4 of them factored left-looking
+    A0 = oracle.plgsy(float(N), Lower, N, nb, SEED_A)
+    d = make_host(ctx, A0, nb, nb, kind, Lower)
+    assert ctx.lib.dplasma_dpotrf(ctx.ptr, Lower, d.ref) == 0
+    F = read_host(d, N, N, nb, nb, kind, Lower, out=A0.copy(order="F") if kind == "sym" else None)
+    want = A0.copy(order="F")
+    assert oracle.potrf(Lower, want, nb) == 0
+    assert relerr(np.tril(F), np.tril(want)) < VTOL
+    assert np.array_equal(np.triu(F, 1), np.triu(A0, 1))
+    d.free()
+
+
 def test_dpotrf_new_start_wait_destruct_device_resident(ctx, oracle):
     """the 3-call pattern of tests/common.h:253-267 on a matrix that lives in HBM"""
     import torch
