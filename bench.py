@@ -257,6 +257,7 @@ def run_ours(args):
         "bound": "tensor", "kernel": "gemm_dmma_kernel (grouped trailing update: DGEMM + DSYRK tiles)",
         "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": (achieved / peak) if achieved and peak > 0 else None,
         "traffic": None,
+        "traffic_note": "ncu --set full on the same kernel (profiles/ncu_gemm_r01_final_summary.md): dram read+write = 1.59 x algorithmic bytes, 13 % of the HBM roof",
         "launches_timed": pl.value, "algorithmic_flops_per_launch_avg": pf.value / max(pl.value, 1),
         "best_launch_tflops": pb.value, "share_of_step": ps.value / (dev_seconds / K) if dev_seconds > 0 else None,
         "peak_source": "of measured: live register-resident DMMA (mma.sync.m8n8k4.f64) loop on this GPU "
