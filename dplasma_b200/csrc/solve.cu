@@ -138,6 +138,10 @@ int dplasma_dtrsm(parsec_context_t* parsec, dplasma_enum_t side, dplasma_enum_t 
     DevMatrix dA, dB;
     int rc = stage_in(parsec, A, &dA, true, uplo);
     if (!rc) rc = stage_in(parsec, B, &dB, true, dplasmaUpperLower);
+    if (!rc && alpha == 0.0) {
+        // BLAS semantics: alpha == 0 -> B = 0, A is not referenced
+        rc = launch_fill(parsec, parsec->sPanel, dB.base, (long long)dB.lmt * dB.lnt * dB.tileElems, 0.0);
+    } else
     if (!rc) rc = (A->super.nodes > 1) ? trsm_left_multi(parsec, parsec->sPanel, uplo, trans, diag, alpha, dA, dB)
                                        : trsm_left_tiled(parsec, parsec->sPanel, uplo, trans, diag, alpha, dA, dB);
     if (!rc) rc = stage_out(parsec, B, &dB, dplasmaUpperLower);

@@ -460,3 +460,63 @@ def test_zpotrf_device_resident_residual(ctx):
     assert lib.check_zpotrf(ctx.ptr, 0, Lower, dA.ref, dA0.ref) == 0
     assert 0.0 < lib.dplasma_b200_last_check_result(ctx.ptr) < 60.0
     dA.free(); dA0.free()
+
+
+# ------------------------------------------------------------------ edge cases and the C driver
+@pytest.mark.parametrize("N,nb", [(1, 64), (7, 64), (64, 64), (65, 64), (129, 128)])
+@pytest.mark.parametrize("uplo", [Lower, Upper])
+def test_dpotrf_tiny_and_single_tile(ctx, oracle, N, nb, uplo):
+    A0 = oracle.plgsy(float(N), uplo, N, nb, SEED_A)
+    d = make_host(ctx, A0, nb, nb)
+    assert ctx.lib.dplasma_dpotrf(ctx.ptr, uplo, d.ref) == 0
+    F = read_host(d, N, N, nb, nb)
+    want = A0.copy(order="F")
+    assert oracle.potrf(uplo, want, nb) == 0
+    tri = np.tril if uplo == Lower else np.triu
+    assert relerr(tri(F), tri(want)) < VTOL
+    B = oracle.plrnt(N, 1, nb, 1, SEED_B)            # one right-hand side
+    dB = make_host(ctx, B, nb, 1)
+    assert ctx.lib.dplasma_dpotrs(ctx.ptr, uplo, d.ref, dB.ref) == 0
+    X = read_host(dB, N, 1, nb, 1)
+    wx = B.copy(order="F")
+    oracle.potrs(uplo, want, wx, nb, 1)
+    assert relerr(X, wx) < 1e-10
+    d.free(); dB.free()
+
+
+def test_empty_matrix_and_alpha_zero(ctx, oracle):
+    lib = ctx.lib
+    d = dp.BlockCyclic(lib, 0, 0, 64, 64, where="host")
+    assert lib.dplasma_dpotrf(ctx.ptr, Lower, d.ref) == 0          # nothing to do, info = 0
+    d.free()
+    n, one, info = C.c_int(0), C.c_int(1), C.c_int(-7)              # pdpotrf_ with N == 0 returns at once (:148-150)
+    desc = (C.c_int * 9)(1, 0, 0, 0, 64, 64, 0, 0, 1)
+    lib.pdpotrf_(b"L", C.byref(n), None, C.byref(one), C.byref(one), desc, C.byref(info))
+    assert info.value == 0
+    # dtrsm with alpha = 0 zeroes B (BLAS semantics)
+    N, nb = 130, 64
+    T = oracle.plgsy(float(N), Lower, N, nb, SEED_A)
+    oracle.potrf(Lower, T, nb)
+    B = oracle.plrnt(N, 9, nb, 9, 5)
+    dT, dB = make_host(ctx, T, nb, nb), make_host(ctx, B, nb, 9)
+    assert lib.dplasma_dtrsm(ctx.ptr, Left, Lower, NoTrans, NonUnit, 0.0, dT.ref, dB.ref) == 0
+    assert not read_host(dB, N, 9, nb, 9).any()
+    dT.free(); dB.free()
+
+
+def test_c_driver_written_like_the_reference_test():
+    """tests/c/testing_dpotrf.c: plain C against include/dplasma_b200.h, the call sequence of
+    tests/testing_zpotrf.c; exit code 0 iff both of the reference's checks pass"""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "tests", "c", "testing_dpotrf")
+    subprocess.check_call(["gcc", "-std=c11", "-O2", "-I" + os.path.join(root, "include"),
+                           os.path.join(root, "tests", "c", "testing_dpotrf.c"), "-o", exe,
+                           "-L" + os.path.join(root, "dplasma_b200", "lib"), "-ldplasma_b200",
+                           "-Wl,-rpath," + os.path.join(root, "dplasma_b200", "lib")])
+    for args in (["3200", "320", "L"], ["1700", "320", "U"]):      # the reference's GPU ctest sizes (Testings.cmake:146-148)
+        out = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stdout + out.stderr
+        assert "Factorization is CORRECT" in out.stdout and "Solution is CORRECT" in out.stdout
+        assert "[****] TIME(s)" in out.stdout
