@@ -126,8 +126,8 @@ int check_dpotrf(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec
     const double eps = 0x1.0p-53;  // LAPACKE_dlamch_work('e'), src/dplasma_zcheck.c:77
     int rc = stage_in(parsec, A, &dA, true, uplo);
     if (!rc) rc = stage_in(parsec, A0, &dA0, true, uplo);
-    if (!rc && dA.esz == 2 && uplo != dplasmaLower) {
-        fprintf(stderr, "check_zpotrf: dplasmaUpper is not built yet\n");
+    if (!rc && dA.esz == 2 && uplo != dplasmaLower && multi) {
+        fprintf(stderr, "check_zpotrf: dplasmaUpper on a process grid is not built yet\n");
         rc = -2;
     }
     if (!rc) rc = inf_norm(parsec, dA0, true, uplo, &Anorm);

@@ -1107,13 +1107,37 @@ __global__ void __launch_bounds__(256) transpose_grid_kernel(DevMatrix A) {
         if (bi + tx < nb && bj + j < nb) Ta[(bi + tx) + (size_t)(bj + j) * ld] = tb[tx][j];
     }
 }
+// complex variant: tile (m,n) <-> tile (n,m)^H (conjugate transpose), interleaved (re,im)
+__global__ void __launch_bounds__(256) ztranspose_grid_kernel(DevMatrix A) {
+    __shared__ double2 ta[32][33], tb[32][33];
+    int pz = blockIdx.z, m = 0;
+    while ((m + 1) * (m + 2) / 2 <= pz) m++;
+    const int n = pz - m * (m + 1) / 2;
+    if (m >= A.mt || n >= A.nt) return;
+    const int bi = blockIdx.x * 32, bj = blockIdx.y * 32;
+    if (m == n && bi < bj) return;
+    double2* Ta = reinterpret_cast<double2*>(A.tile(m, n));
+    double2* Tb = reinterpret_cast<double2*>(A.tile(n, m));
+    const int ld = A.mb, nb = A.mb;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int j = ty; j < 32; j += 8) {
+        if (bi + tx < nb && bj + j < nb) ta[j][tx] = Ta[(bi + tx) + (size_t)(bj + j) * ld];
+        if (bj + tx < nb && bi + j < nb) tb[j][tx] = Tb[(bj + tx) + (size_t)(bi + j) * ld];
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        if (bj + tx < nb && bi + j < nb) { double2 v = ta[tx][j]; v.y = -v.y; Tb[(bj + tx) + (size_t)(bi + j) * ld] = v; }
+        if (bi + tx < nb && bj + j < nb) { double2 v = tb[tx][j]; v.y = -v.y; Ta[(bi + tx) + (size_t)(bj + j) * ld] = v; }
+    }
+}
 int launch_transpose_grid(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A) {
     if (A.P * A.Q != 1 || A.mb != A.nb || A.mt != A.nt) return -3;
     const int nblk = (A.mb + 31) / 32;
     const long long pairs = (long long)A.mt * (A.mt + 1) / 2;
     if (pairs > 65535) return -4;
     dim3 grid(nblk, nblk, (unsigned)pairs);
-    transpose_grid_kernel<<<grid, 256, 0, s>>>(A);
+    if (A.esz == 2) ztranspose_grid_kernel<<<grid, 256, 0, s>>>(A);
+    else transpose_grid_kernel<<<grid, 256, 0, s>>>(A);
     ctx->launches++;
     return (int)cudaGetLastError();
 }

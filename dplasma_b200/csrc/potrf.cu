@@ -249,9 +249,9 @@ int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp) {
         ctx->cplx = 0;
         return rc;
     }
-    if (ctx->cplx) {
+    if (ctx->cplx && A.P * A.Q != 1) {
         ctx->cplx = 0;
-        fprintf(stderr, "dplasma_b200: zpotrf with dplasmaUpper is not built yet (dplasmaLower is)\n");
+        fprintf(stderr, "dplasma_b200: zpotrf with dplasmaUpper on a process grid is not built yet\n");
         return -2;
     }
     // dplasmaUpper (src/zpotrf_U.jdf): U(k,n) = L(n,k)^T and every tile operation of the upper
@@ -276,9 +276,10 @@ int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp) {
         stage_free(&W);
         return rc;
     }
-    int rc = launch_transpose_grid(ctx, ctx->sPanel, A);
+    int rc = launch_transpose_grid(ctx, ctx->sPanel, A);  // conjugate transpose for complex tiles
     if (!rc) rc = potrf_lower_1gpu(ctx, A);
     if (!rc) rc = launch_transpose_grid(ctx, ctx->sPanel, A);
+    ctx->cplx = 0;
     return rc;
 }
 

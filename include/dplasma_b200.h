@@ -172,7 +172,7 @@ int check_dpotrf(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec
 int check_daxmb(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec_tiled_matrix_t *A,
                 parsec_tiled_matrix_t *b, parsec_tiled_matrix_t *x);
 /* ---- complex double (zpotrf, BASELINE configs[4]); A->mtype must be PARSEC_MATRIX_COMPLEX_DOUBLE,
- *      tiles hold interleaved (re,im) dplasma_complex64_t.  dplasmaLower only in this build.
+ *      tiles hold interleaved (re,im) dplasma_complex64_t.  Both triangles on one GPU, dplasmaLower on a grid.
  *      src/include/dplasma/dplasma_z.h:82,107,109,172,239,280 ---- */
 parsec_taskpool_t *dplasma_zpotrf_New(dplasma_enum_t uplo, parsec_tiled_matrix_t *A, int *info);
 void dplasma_zpotrf_Destruct(parsec_taskpool_t *tp);

@@ -438,14 +438,32 @@ def test_zpotrf_lower_vs_oracle(ctx, oracle, golden, N, nb):
     d.free(); dA0.free()
 
 
-def test_zpotrf_info_and_unsupported(ctx, oracle):
+def test_zpotrf_info(ctx, oracle):
     N, nb = 200, 64
     A = oracle.plgsy(200.0, Lower, N, nb, SEED_A, "z")
     A[150, 150] = -1.0
     d = zmake_host(ctx, A, nb)
     assert ctx.lib.dplasma_zpotrf(ctx.ptr, Lower, d.ref) == 151
-    assert ctx.lib.dplasma_zpotrf(ctx.ptr, Upper, d.ref) < 0      # not built yet: fails loudly, no fallback
     d.free()
+
+
+@pytest.mark.parametrize("N,nb", [(378, 93), (1024, 128)])
+def test_zpotrf_upper_vs_oracle(ctx, oracle, golden, N, nb):
+    """testing_zpotrf.c hard-codes dplasmaUpper (tests/testing_zpotrf.c:21): U^H U = A"""
+    A0 = oracle.plgsy(float(N), Upper, N, nb, SEED_A, "z")
+    d = zmake_host(ctx, A0, nb)
+    assert ctx.lib.dplasma_zpotrf(ctx.ptr, Upper, d.ref) == 0
+    F = zread_host(d, N, nb)
+    want = A0.copy(order="F")
+    assert oracle.potrf(Upper, want, nb, "z") == 0
+    assert relerr(np.triu(F), np.triu(want)) < VTOL
+    assert np.array_equal(np.tril(F, -1), np.tril(A0, -1))
+    if N == 378:
+        assert relerr(F.ravel(order="F")[::31], golden["z378_F_U_s31"]) < VTOL
+    dA0 = zmake_host(ctx, A0, nb)
+    assert ctx.lib.check_zpotrf(ctx.ptr, 0, Upper, d.ref, dA0.ref) == 0
+    assert 0.0 <= ctx.lib.dplasma_b200_last_check_result(ctx.ptr) < 60.0
+    d.free(); dA0.free()
 
 
 def test_zpotrf_device_resident_residual(ctx):
