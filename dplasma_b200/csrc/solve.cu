@@ -116,6 +116,94 @@ static int trsm_left_tiled(parsec_context_s* ctx, cudaStream_t s, int uplo, int 
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------
+// Right side:  B <- alpha * B * op(T)^-1  (src/ztrsm_RLN.jdf, ztrsm_RLT.jdf, ztrsm_RUN.jdf,
+// ztrsm_RUT.jdf; CORE_ztrsm(Right, ...) at :48 of each).  B is batched over tiles (all tile
+// rows of one tile column of B share the triangular tile).  Same inverse-block recursion as
+// the left side; which operand form (M-major / K-major) a block takes follows from where
+// op(T)(k,c) sits in memory.
+// ---------------------------------------------------------------------------------------
+static int trsm_right_rec(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int c0, int n, double alpha,
+                          const double* T, int ldt, const double* winv, double* B, int ldb, int M, int batch,
+                          long long strideB, int lastBatchM) {
+    const bool upperEff = (uplo == dplasmaUpper) != trans;  // op(T) upper triangular -> forward over the columns
+    if (n <= IB) {
+        // X = alpha * B inv(op(Tjj)); winv = inverse of the block's lower form
+        const bool leafK = (uplo == dplasmaLower) != trans;   // RLN, RUT: inv(op)[k][c] = W[k + c*IB]
+        double* Bc = B + (size_t)c0 * ldb;
+        return gemm_single(ctx, s, M, n, n, alpha, Bc, ldb, false, winv + (size_t)(c0 / IB) * IB * IB, IB, leafK, 0.0, Bc,
+                           ldb, 0, batch, strideB, 0, strideB, lastBatchM);
+    }
+    const int n1 = split_of(n), n2 = n - n1;
+    int rc;
+    if (upperEff) {
+        // X1 = a B1 inv(T11) ; B2 = a B2 - X1 opT(1,2) ; X2 = B2 inv(T22)
+        rc = trsm_right_rec(ctx, s, uplo, trans, c0, n1, alpha, T, ldt, winv, B, ldb, M, batch, strideB, lastBatchM);
+        if (rc) return rc;
+        // opT(1,2)[k][c]: Upper/NoTrans -> T[(c0+k) + (c0+n1+c) ldt] (K-major) ; Lower/Trans -> T[(c0+n1+c) + (c0+k) ldt] (M-major)
+        const double* T12 = trans ? T + (c0 + n1) + (size_t)c0 * ldt : T + c0 + (size_t)(c0 + n1) * ldt;
+        rc = gemm_single(ctx, s, M, n2, n1, -1.0, B + (size_t)c0 * ldb, ldb, false, T12, ldt, !trans, alpha,
+                         B + (size_t)(c0 + n1) * ldb, ldb, 0, batch, strideB, 0, strideB, lastBatchM);
+        if (rc) return rc;
+        return trsm_right_rec(ctx, s, uplo, trans, c0 + n1, n2, 1.0, T, ldt, winv, B, ldb, M, batch, strideB, lastBatchM);
+    }
+    // op(T) lower: X2 = a B2 inv(T22) ; B1 = a B1 - X2 opT(2,1) ; X1 = B1 inv(T11)
+    rc = trsm_right_rec(ctx, s, uplo, trans, c0 + n1, n2, alpha, T, ldt, winv, B, ldb, M, batch, strideB, lastBatchM);
+    if (rc) return rc;
+    // opT(2,1)[k][c]: Lower/NoTrans -> T[(c0+n1+k) + (c0+c) ldt] (K-major) ; Upper/Trans -> T[(c0+c) + (c0+n1+k) ldt] (M-major)
+    const double* T21 = trans ? T + c0 + (size_t)(c0 + n1) * ldt : T + (c0 + n1) + (size_t)c0 * ldt;
+    rc = gemm_single(ctx, s, M, n1, n2, -1.0, B + (size_t)(c0 + n1) * ldb, ldb, false, T21, ldt, !trans, alpha,
+                     B + (size_t)c0 * ldb, ldb, 0, batch, strideB, 0, strideB, lastBatchM);
+    if (rc) return rc;
+    return trsm_right_rec(ctx, s, uplo, trans, c0, n1, 1.0, T, ldt, winv, B, ldb, M, batch, strideB, lastBatchM);
+}
+
+// one tile (or a batch of tiles): B <- alpha B op(T)^-1
+int trsm_right(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, int diag, int m, int n, double alpha,
+               const double* T, int ldt, double* B, int ldb, double* winv, int batch, long long strideB, int lastBatchM) {
+    if (m <= 0 || n <= 0 || batch <= 0) return 0;
+    int rc = invert_diag_blocks(ctx, s, uplo, diag, n, T, ldt, winv);
+    if (rc) return rc;
+    return trsm_right_rec(ctx, s, uplo, trans != dplasmaNoTrans, 0, n, alpha, T, ldt, winv, B, ldb, m, batch, strideB,
+                          lastBatchM);
+}
+
+// dplasma_ztrsm, Right side, on staged matrices (single process): X op(A) = alpha B.
+static int trsm_right_tiled(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, int diag, double alpha,
+                            const DevMatrix& A, const DevMatrix& B) {
+    int rc = ensure_winv(ctx, A.nb);
+    if (rc) return rc;
+    const int mt = B.mt, nt = B.nt;
+    const bool tr = trans != dplasmaNoTrans;
+    const bool forward = (uplo == dplasmaUpper) != tr;  // op(A) upper: tile columns left to right
+    for (int kk = 0; kk < nt; kk++) {
+        const int k = forward ? kk : nt - 1 - kk;
+        const int tk = B.colsOfTile(k);
+        // alpha: the NoTrans DAGs scale at their first step (ztrsm_RUN.jdf:46), the Trans DAGs solve with alpha
+        // at every step and update with -1/alpha (ztrsm_RLT.jdf:48,128-132)
+        const double salpha = tr ? alpha : ((kk == 0) ? alpha : 1.0);
+        const double galpha = tr ? -1.0 / alpha : -1.0;
+        const double gbeta = tr ? 1.0 : ((kk == 0) ? alpha : 1.0);
+        double* winv = ctx->wInv + (size_t)(kk & 1) * ctx->wInvSlot;
+        rc = trsm_right(ctx, s, uplo, trans, diag, B.mb, tk, salpha, A.tile(k, k), A.mb, B.tile(0, k), B.mb, winv, mt,
+                        B.tileElems, B.rowsOfTile(mt - 1));
+        if (rc) return rc;
+        const int lo = forward ? k + 1 : 0, hi = forward ? nt : k;
+        for (int n = lo; n < hi; n++) {
+            // B(:,n) = gbeta B(:,n) + galpha B(:,k) op(A)(k,n), batched over the tile rows of B
+            const bool stored_kn = (uplo == dplasmaUpper) ? (k < n) : (k > n);   // is A(k,n) in the stored triangle?
+            // NoTrans: op(A)(k,n) = A(k,n) (always stored in the direction we walk) -> B'[c][kk] = A(k,n)[kk + c ld]: K-major
+            // Trans:   op(A)(k,n) = A(n,k)^T                                       -> B'[c][kk] = A(n,k)[c + kk ld]: M-major
+            const double* Akn = tr ? A.tile(n, k) : A.tile(k, n);
+            (void)stored_kn;
+            rc = gemm_single(ctx, s, B.mb, B.colsOfTile(n), tk, galpha, B.tile(0, k), B.mb, false, Akn, A.mb, !tr, gbeta,
+                             B.tile(0, n), B.mb, 0, mt, B.tileElems, 0, B.tileElems, B.rowsOfTile(mt - 1));
+            if (rc) return rc;
+        }
+    }
+    return 0;
+}
+
 }  // namespace dpb
 
 using namespace dpb;
@@ -130,8 +218,8 @@ int dplasma_dtrsm(parsec_context_t* parsec, dplasma_enum_t side, dplasma_enum_t 
     if (trans != dplasmaNoTrans && trans != dplasmaTrans && trans != dplasmaConjTrans) { fprintf(stderr, "dplasma_dtrsm: illegal value of trans\n"); return -3; }
     if (diag != dplasmaUnit && diag != dplasmaNonUnit) { fprintf(stderr, "dplasma_dtrsm: illegal value of diag\n"); return -4; }
     if (!parsec) return -100;
-    if (side == dplasmaRight) {
-        fprintf(stderr, "dplasma_dtrsm: side Right is outside the Cholesky path and not built here\n");
+    if (side == dplasmaRight && A->super.nodes > 1) {
+        fprintf(stderr, "dplasma_dtrsm: side Right on a process grid is not built here\n");
         return -1;
     }
     cudaSetDevice(parsec->device);
@@ -141,6 +229,8 @@ int dplasma_dtrsm(parsec_context_t* parsec, dplasma_enum_t side, dplasma_enum_t 
     if (!rc && alpha == 0.0) {
         // BLAS semantics: alpha == 0 -> B = 0, A is not referenced
         rc = launch_fill(parsec, parsec->sPanel, dB.base, (long long)dB.lmt * dB.lnt * dB.tileElems, 0.0);
+    } else if (!rc && side == dplasmaRight) {
+        rc = trsm_right_tiled(parsec, parsec->sPanel, uplo, trans, diag, alpha, dA, dB);
     } else
     if (!rc) rc = (A->super.nodes > 1) ? trsm_left_multi(parsec, parsec->sPanel, uplo, trans, diag, alpha, dA, dB)
                                        : trsm_left_tiled(parsec, parsec->sPanel, uplo, trans, diag, alpha, dA, dB);
@@ -201,7 +291,9 @@ int dplasma_b200_dtrsm_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t 
     int rc = ensure_winv(ctx, na);
     if (rc) return rc;
     if (side == dplasmaLeft) return trsm_left(ctx, s, uplo, trans, diag, m, n, alpha, T, ldt, C, ldc, ctx->wInv);
-    // Right side, the form the factorization uses: C <- alpha C op(T)^-1  (src/zpotrf_L.jdf:236-240)
+    if (!(uplo == dplasmaLower && trans != dplasmaNoTrans && alpha == 1.0))
+        return trsm_right(ctx, s, uplo, trans, diag, m, n, alpha, T, ldt, C, ldc, ctx->wInv, 1, 0, m);
+    // Right side, the form the factorization uses: C <- C L^-T  (src/zpotrf_L.jdf:236-240)
     if (uplo == dplasmaLower && trans != dplasmaNoTrans && alpha == 1.0) {
         rc = 0;
         for (int j0 = 0; j0 < n && !rc; j0 += IB)

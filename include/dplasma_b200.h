@@ -155,7 +155,8 @@ int dplasma_dposv(parsec_context_t *parsec, dplasma_enum_t uplo, parsec_tiled_ma
 /* :84, src/zpotrs_wrapper.c:58-98 */
 int dplasma_dpotrs(parsec_context_t *parsec, dplasma_enum_t uplo, const parsec_tiled_matrix_t *A,
                    parsec_tiled_matrix_t *B);
-/* :51, src/ztrsm_wrapper.c:263-310 (Left side variants: ztrsm_LLN/LLT/LUN/LUT.jdf) */
+/* :51, src/ztrsm_wrapper.c:263-310: all eight side/uplo/trans variants (ztrsm_{L,R}{L,U}{N,T}.jdf) on one
+ * process; the Left variants also on a process grid */
 int dplasma_dtrsm(parsec_context_t *parsec, dplasma_enum_t side, dplasma_enum_t uplo,
                   dplasma_enum_t trans, dplasma_enum_t diag, double alpha,
                   const parsec_tiled_matrix_t *A, parsec_tiled_matrix_t *B);

@@ -295,6 +295,7 @@ int P(potrf)(int uplo, int N, int nb, T *A, int lda)
 
 /* ---------------- dplasma_ztrsm, Left side (src/ztrsm_wrapper.c:94-163 picks the DAG):
  * LLN ztrsm_LLN.jdf:40-51,122-135 ; LLT ztrsm_LLT.jdf:40-51,123-136 ; LUN / LUT mirror.
+ * and the four Right-side DAGs (ztrsm_R{L,U}{N,T}.jdf).
  * Returns the reference's argument-check codes (ztrsm_wrapper.c:274-296). */
 int P(trsm)(int side, int uplo, int trans, int diag, int M, int NRHS, int mb, int nbr, T alpha,
             const T *A, int lda, T *B, int ldb)
@@ -303,8 +304,43 @@ int P(trsm)(int side, int uplo, int trans, int diag, int M, int NRHS, int mb, in
     if (uplo != ORC_UPPER && uplo != ORC_LOWER) return -2;
     if (trans != ORC_NOTRANS && trans != ORC_TRANS && trans != ORC_CONJTRANS) return -3;
     if (diag != ORC_UNIT && diag != ORC_NONUNIT) return -4;
-    if (side != ORC_LEFT) return -1; /* oracle restates only the Left variants (posv path) */
     int mt = (M + mb - 1) / mb, nt = (NRHS + nbr - 1) / nbr;
+    if (side == ORC_RIGHT) {
+        /* X op(A) = alpha B, A is NRHS x NRHS with nbr x nbr tiles, lda given.
+         * ztrsm_RUN.jdf:40-57,120-140 / ztrsm_RLT.jdf:40-56,120-138 walk the tile columns upward,
+         * ztrsm_RLN.jdf / ztrsm_RUT.jdf downward.  NoTrans DAGs scale by alpha at their first step and
+         * update with beta = lalpha; Trans DAGs solve with alpha at every step and update with -1/alpha. */
+        int upperEff = (uplo == ORC_UPPER) == (trans == ORC_NOTRANS);
+        for (int kk = 0; kk < nt; kk++) {
+            int k = upperEff ? kk : nt - 1 - kk;
+            int tk = (k == nt - 1) ? NRHS - k * nbr : nbr;
+            int tr = (trans != ORC_NOTRANS);
+            T salpha = tr ? alpha : ((kk == 0) ? alpha : (T)1.0);
+            T galpha = tr ? (T)(-1.0) / alpha : (T)(-1.0);
+            T gbeta = tr ? (T)1.0 : ((kk == 0) ? alpha : (T)1.0);
+            for (int m = 0; m < mt; m++) {
+                int tm = (m == mt - 1) ? M - m * mb : mb;
+                P(trsm_tile)(ORC_RIGHT, uplo, trans, diag, tm, tk, salpha, A + (size_t)k * nbr + (size_t)k * nbr * lda, lda,
+                             B + (size_t)m * mb + (size_t)k * nbr * ldb, ldb);
+            }
+            int lo = upperEff ? k + 1 : 0, hi = upperEff ? nt : k;
+            for (int n = lo; n < hi; n++) {
+                int tn = (n == nt - 1) ? NRHS - n * nbr : nbr;
+                for (int m = 0; m < mt; m++) {
+                    int tm = (m == mt - 1) ? M - m * mb : mb;
+                    const T *Bk = B + (size_t)m * mb + (size_t)k * nbr * ldb;
+                    T *Bn = B + (size_t)m * mb + (size_t)n * nbr * ldb;
+                    if (!tr)
+                        P(gemm_tile)(ORC_NOTRANS, ORC_NOTRANS, tm, tn, tk, galpha, Bk, ldb,
+                                     A + (size_t)k * nbr + (size_t)n * nbr * lda, lda, gbeta, Bn, ldb);
+                    else
+                        P(gemm_tile)(ORC_NOTRANS, trans, tm, tn, tk, galpha, Bk, ldb,
+                                     A + (size_t)n * nbr + (size_t)k * nbr * lda, lda, gbeta, Bn, ldb);
+                }
+            }
+        }
+        return 0;
+    }
     int forward = (uplo == ORC_LOWER) == (trans == ORC_NOTRANS);
     for (int kk = 0; kk < mt; kk++) {
         int k = forward ? kk : mt - 1 - kk;

@@ -538,3 +538,37 @@ def test_c_driver_written_like_the_reference_test():
         assert out.returncode == 0, out.stdout + out.stderr
         assert "Factorization is CORRECT" in out.stdout and "Solution is CORRECT" in out.stdout
         assert "[****] TIME(s)" in out.stdout
+
+
+# ------------------------------------------------------------------ Right-side triangular solves
+@pytest.mark.parametrize("uplo,trans", [(Lower, NoTrans), (Lower, Trans), (Upper, NoTrans), (Upper, Trans)])
+@pytest.mark.parametrize("m,n,diag", [(200, 256, NonUnit), (37, 93, NonUnit), (64, 130, Unit)])
+def test_dtrsm_tile_right_all_variants(ctx, oracle, uplo, trans, m, n, diag):
+    import torch
+    rng = np.random.default_rng(m + 3 * n)
+    T = oracle.plgsy(float(n), UpperLower, n, n, 5)
+    assert oracle.potrf_tile(uplo, T) == 0
+    if diag == Unit:
+        T = np.asfortranarray(T / 50.0)
+    B0 = np.asfortranarray(rng.standard_normal((m, n)))
+    want = B0.copy(order="F")
+    oracle.trsm_tile(Right, uplo, trans, diag, 1.25, T, want)
+    tT, tB = (torch.from_numpy(x.T.copy()).cuda() for x in (T, B0))
+    assert ctx.lib.dplasma_b200_dtrsm_tile(ctx.ptr, None, Right, uplo, trans, diag, m, n, 1.25, dev(tT), n, dev(tB), m) == 0
+    torch.cuda.synchronize()
+    assert relerr(tB.cpu().numpy().T, want) < VTOL
+
+
+@pytest.mark.parametrize("uplo,trans", [(Lower, NoTrans), (Lower, Trans), (Upper, NoTrans), (Upper, Trans)])
+def test_dtrsm_tiled_right(ctx, oracle, uplo, trans):
+    """dplasma_dtrsm(Right, ...): src/ztrsm_RLN.jdf / RLT / RUN / RUT"""
+    M, N, mb, nb = 230, 300, 48, 64
+    T = oracle.plgsy(float(N), uplo, N, nb, SEED_A)
+    oracle.potrf(uplo, T, nb)
+    B = oracle.plrnt(M, N, mb, nb, 7)
+    want = B.copy(order="F")
+    assert oracle.trsm(Right, uplo, trans, NonUnit, 1.5, T, want, mb, nb) == 0
+    dT, dB = make_host(ctx, T, nb, nb), make_host(ctx, B, mb, nb)
+    assert ctx.lib.dplasma_dtrsm(ctx.ptr, Right, uplo, trans, NonUnit, 1.5, dT.ref, dB.ref) == 0
+    assert relerr(read_host(dB, M, N, mb, nb), want) < 1e-10
+    dT.free(); dB.free()

@@ -152,3 +152,23 @@ def test_reference_library_agrees_when_present(oracle):
         F2 = F1.copy(order="F")
         assert oracle.potrf(Lower, F1, 32, p) == R.potrf(Lower, F2, 32, p) == 0
         np.testing.assert_allclose(F1, F2, rtol=RTOL, atol=1e-15)
+
+
+@pytest.mark.parametrize("p", ["d", "z"])
+def test_tiled_trsm_all_eight_variants_against_numpy(oracle, p):
+    """dplasma_ztrsm restated for Left and Right, both triangles, N / T(C): op(A) X = alpha B resp. X op(A) = alpha B"""
+    rng = np.random.default_rng(3)
+    M, R, nb = 150, 70, 32
+    for side in (Left, Right):
+        na = M if side == Left else R
+        G = rng.standard_normal((na, na)) + (1j * rng.standard_normal((na, na)) if p == "z" else 0)
+        for uplo in (Lower, Upper):
+            Tm = np.asfortranarray((np.tril(G) if uplo == Lower else np.triu(G)) + na * np.eye(na)).astype(G.dtype)
+            for trans in (NoTrans, ConjTrans):
+                B = np.asfortranarray(rng.standard_normal((M, R)) + (1j * rng.standard_normal((M, R)) if p == "z" else 0)).astype(G.dtype)
+                X = B.copy(order="F")
+                mb, nbr = (nb, 24) if side == Left else (24, nb)
+                assert oracle.trsm(side, uplo, trans, NonUnit, 0.5, Tm, X, mb, nbr, p) == 0
+                op = Tm if trans == NoTrans else Tm.conj().T
+                got = op @ X if side == Left else X @ op
+                np.testing.assert_allclose(got, 0.5 * B, rtol=1e-11, atol=1e-11)
