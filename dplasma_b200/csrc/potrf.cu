@@ -351,7 +351,7 @@ int parsec_context_start(parsec_context_t* ctx) {
     for (size_t i = 0; i < ctx->queue.size(); i++) {
         parsec_taskpool_s* tp = ctx->queue[i];
         // early column write-back: single-process lower factorizations of staged matrices
-        const bool canEarly = tp->dA.owned && tp->uplo == dplasmaLower && tp->dA.P * tp->dA.Q == 1;
+        const bool canEarly = tp->dA.owned && tp->uplo == dplasmaLower;
         ctx->curTp = canEarly ? tp : nullptr;
         ctx->earlyOut = canEarly ? 0 : -1;
         int rc = potrf_enqueue(ctx, tp);

@@ -190,6 +190,14 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
                                       A.rowsOfTile(lastGm));
                 if (rc) return rc;
             }
+            // my tiles of tile column k are final: a staged (host) matrix gets them back now
+            if (ctx->curTp && ctx->earlyOut >= 0) {
+                cudaEvent_t evCol = dist_event(ctx, evi++);
+                DPB_CUDA(cudaEventRecord(evCol, sp));
+                rc = stage_out_column(ctx, ctx->curTp->A, &ctx->curTp->dA, jlk, dplasmaLower, evCol);
+                if (rc) return rc;
+                ctx->earlyOut = jlk + 1;
+            }
         }
         if (k + 1 >= nt) break;
         // ---- (2) + (3): panel broadcasts ----

@@ -266,3 +266,38 @@ def nccl_pdpotrf_worker(rank, world, port, P, Q, N, nb, uplo_name, q):
         ctx.close()
     finally:
         dist.destroy_process_group()
+
+
+def nccl_host_potrf_worker(rank, world, port, P, Q, N, nb, kind, q):
+    """GPU: dplasma_dpotrf on a grid with the matrix in pinned HOST memory (tile or sym-packed storage):
+    staged in, factored, finished tile columns written back early on the copy stream."""
+    import torch
+    import dplasma_b200 as dp
+    from tests.util import full_to_local, local_to_full
+    from oracle.oracle import Oracle
+    torch.cuda.set_device(rank)
+    dist = _init(rank, world, port, "nccl")
+    try:
+        lib = dp.load()
+        ctx = dp.Context(lib)
+        ids = [ctx.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.comm_init(ids[0], rank, world)
+        orc = Oracle()
+        A0 = orc.plgsy(float(N), dp.Lower, N, nb, 3872)
+        sym = dp.Lower if kind == "sym" else None
+        d = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, kind=kind, uplo=dp.Lower if kind == "sym" else dp.UpperLower, where="host")
+        loc0 = full_to_local(A0, nb, nb, P, Q, rank, sym_uplo=sym)
+        d.host_array()[:d.elems] = loc0
+        info = lib.dplasma_dpotrf(ctx.ptr, dp.Lower, d.ref)
+        want = A0.copy(order="F")
+        assert orc.potrf(dp.Lower, want, nb) == 0
+        got = local_to_full(d.host_array()[:d.elems].copy(), N, N, nb, nb, P, Q, rank, sym_uplo=sym)
+        wl = full_to_local(np.tril(want), nb, nb, P, Q, rank, sym_uplo=sym)
+        gl = full_to_local(np.tril(got), nb, nb, P, Q, rank, sym_uplo=sym)
+        err = float(np.abs(gl - wl).max() / np.abs(want).max()) if gl.size else 0.0
+        q.put((rank, info, err))
+        d.free()
+        ctx.close()
+    finally:
+        dist.destroy_process_group()

@@ -129,3 +129,27 @@ def test_zpotrf_baseline_config5_residual():
     res = run_grid(2, 2, 49152, 512, False, cplx=True)
     for rank, info, bad, resid, err, t, info_bad in res:
         assert info == 0 and bad == 0 and 0.0 <= resid < 60.0, (rank, info, bad, resid)
+
+
+@pytest.mark.parametrize("P,Q", [(1, 2), (2, 2), (2, 4)])
+@pytest.mark.parametrize("kind", ["tile", "sym"])
+def test_dpotrf_grid_host_matrix(P, Q, kind):
+    """the reference's own situation: the distributed matrix lives in host memory on every rank"""
+    import torch
+    import torch.multiprocessing as mp
+    from tests.dist_workers import nccl_host_potrf_worker
+    world = P * Q
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=nccl_host_potrf_worker, args=(r, world, port, P, Q, 1500, 128, kind, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for rank, info, err in res:
+        assert info == 0 and err < 1e-11, (rank, info, err)
