@@ -101,6 +101,10 @@ class Lib:
         proto("dplasma_zplrnt", i, [vp, i, pBC, u64])
         proto("check_zpotrf", i, [vp, i, i, pBC, pBC])
         proto("dplasma_zlanhe", d, [vp, i, i, pBC])
+        proto("dplasma_zlange", d, [vp, i, pBC])
+        proto("dplasma_zposv", i, [vp, i, pBC, pBC])
+        proto("dplasma_zpotrs", i, [vp, i, pBC, pBC])
+        proto("check_zaxmb", i, [vp, i, i, pBC, pBC, pBC])
         proto("dplasma_b200_last_check_result", d, [vp])
         proto("dplasma_dlansy", d, [vp, i, i, pBC])
         proto("dplasma_dlange", d, [vp, i, pBC])

@@ -32,6 +32,10 @@ static int inf_norm(parsec_context_s* ctx, const DevMatrix& A, bool sym, int upl
     return 0;
 }
 
+int inf_norm_public(parsec_context_s* ctx, const DevMatrix& A, bool sym, int uplo, double* out) {
+    return inf_norm(ctx, A, sym, uplo, out);
+}
+
 }  // namespace dpb
 
 using namespace dpb;

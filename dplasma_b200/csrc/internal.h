@@ -98,6 +98,13 @@ int launch_potrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda,
                       int* dInfo, int infoBase);
 int launch_trsm_panel_fused(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, int n, const double* winv,
                             double* B, int ldb, long long tileStride, int rowsPerTile, int lastTileRows, int ntiles);
+int launch_ztranspose(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst, int ldd, int m,
+                      int n, int conj);
+int launch_zconj(parsec_context_s* ctx, cudaStream_t s, double* p, long long ncomplex);
+int launch_ztrtri_blocks(parsec_context_s* ctx, cudaStream_t s, const double* T, int ldt, int n, double* winv,
+                         double* winvT);
+int trsm_rec_entry(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, const double* winv, int n, double* B,
+                   int ldb, int M, int batch, long long strideB, int lastBatchM);
 int launch_zpotrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv, int* dInfo,
                        int infoBase);
 int launch_potrf_colblock(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, int j0, double* winv,

@@ -620,6 +620,109 @@ __global__ void __launch_bounds__(256) zpotrf_leaf_kernel(double* __restrict__ A
         winv[2 * e + 1] = (i >= j) ? Xi[i][j] : 0.0;
     }
 }
+// ---------------------------------------------------------------------------------------
+// Helpers of the complex solves (zpotrs): rectangular (conjugate) transposition of interleaved
+// complex tiles, in-place conjugation, and the inverses of the 64x64 diagonal blocks of a
+// lower-triangular complex tile (W and its plain transpose W^T).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ztranspose_rect_kernel(const double2* __restrict__ src, int lds,
+                                                              double2* __restrict__ dst, int ldd, int m, int n, int conj) {
+    __shared__ double2 t[32][33];
+    const int bi = blockIdx.x * 32, bj = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int j = ty; j < 32; j += 8)
+        if (bi + tx < m && bj + j < n) t[j][tx] = src[(bi + tx) + (size_t)(bj + j) * lds];
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8)
+        if (bj + tx < n && bi + j < m) {
+            double2 v = t[tx][j];
+            if (conj) v.y = -v.y;
+            dst[(bj + tx) + (size_t)(bi + j) * ldd] = v;
+        }
+}
+// dst (n x m, ld ldd) = src (m x n, ld lds)^T or ^H ; pointers in doubles, dimensions in complex elements
+int launch_ztranspose(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst, int ldd, int m,
+                      int n, int conj) {
+    if (m <= 0 || n <= 0) return 0;
+    dim3 grid((m + 31) / 32, (n + 31) / 32);
+    ztranspose_rect_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const double2*>(src), lds,
+                                                reinterpret_cast<double2*>(dst), ldd, m, n, conj);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+__global__ void zconj_kernel(double* p, long long ncomplex) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < ncomplex; e += (long long)gridDim.x * blockDim.x)
+        p[2 * e + 1] = -p[2 * e + 1];
+}
+int launch_zconj(parsec_context_s* ctx, cudaStream_t s, double* p, long long ncomplex) {
+    if (ncomplex <= 0) return 0;
+    long long blocks = (ncomplex + 255) / 256;
+    if (blocks > 1184) blocks = 1184;
+    zconj_kernel<<<(int)blocks, 256, 0, s>>>(p, ncomplex);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+// one CTA per 64x64 diagonal block of the lower-triangular n x n complex tile T:
+// winv[b] = inverse (64x64 complex, ld 64), winvT[b] = its plain transpose
+__global__ void __launch_bounds__(256) ztrtri_blocks_kernel(const double* __restrict__ T, int ldt, int n,
+                                                            double* __restrict__ winv, double* __restrict__ winvT) {
+    extern __shared__ double leaf_smem[];
+    double(*Sr)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem);
+    double(*Si)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem + IB * LEAF_LD);
+    double(*Xr)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem + 2 * IB * LEAF_LD);
+    double(*Xi)[LEAF_LD] = reinterpret_cast<double(*)[LEAF_LD]>(leaf_smem + 3 * IB * LEAF_LD);
+    const int j0 = blockIdx.x * IB, nn = min(IB, n - j0), tid = threadIdx.x;
+    const double* A = T + 2 * (j0 + (size_t)j0 * ldt);
+    for (int e = tid; e < IB * IB; e += 256) {
+        const int i = e % IB, j = e / IB;
+        double re = (i == j) ? 1.0 : 0.0, im = 0.0;
+        if (i < nn && j < nn && i >= j) { re = A[2 * (i + (size_t)j * ldt)]; im = A[2 * (i + (size_t)j * ldt) + 1]; }
+        Sr[i][j] = re; Si[i][j] = im; Xr[i][j] = 0.0; Xi[i][j] = 0.0;
+    }
+    __syncthreads();
+    if (tid < IB) {
+        const int c = tid;
+        // 1 / L_cc (complex in general; real for a Cholesky factor)
+        {
+            const double dr = Sr[c][c], di = Si[c][c], den = dr * dr + di * di;
+            Xr[c][c] = dr / den; Xi[c][c] = -di / den;
+        }
+        for (int i = c + 1; i < IB; i++) {
+            double sr = 0.0, si = 0.0;
+            for (int l = c; l < i; l++) {
+                sr += Sr[i][l] * Xr[l][c] - Si[i][l] * Xi[l][c];
+                si += Sr[i][l] * Xi[l][c] + Si[i][l] * Xr[l][c];
+            }
+            const double dr = Sr[i][i], di = Si[i][i], den = dr * dr + di * di;
+            // x = -(s) / L_ii
+            Xr[i][c] = -(sr * dr + si * di) / den;
+            Xi[i][c] = -(si * dr - sr * di) / den;
+        }
+    }
+    __syncthreads();
+    double* W = winv + (size_t)blockIdx.x * IB * IB * 2;
+    double* Wt = winvT + (size_t)blockIdx.x * IB * IB * 2;
+    for (int e = tid; e < IB * IB; e += 256) {
+        const int i = e % IB, j = e / IB;
+        const double re = (i >= j) ? Xr[i][j] : 0.0, im = (i >= j) ? Xi[i][j] : 0.0;
+        W[2 * e] = re; W[2 * e + 1] = im;
+        Wt[2 * (j + (size_t)i * IB)] = re; Wt[2 * (j + (size_t)i * IB) + 1] = im;
+    }
+}
+int launch_ztrtri_blocks(parsec_context_s* ctx, cudaStream_t s, const double* T, int ldt, int n, double* winv,
+                         double* winvT) {
+    if (n <= 0) return 0;
+    static bool attr = false;
+    const int smem = 4 * IB * LEAF_LD * (int)sizeof(double);
+    if (!attr) {
+        DPB_CUDA(cudaFuncSetAttribute(ztrtri_blocks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr = true;
+    }
+    ztrtri_blocks_kernel<<<(n + IB - 1) / IB, 256, smem, s>>>(T, ldt, n, winv, winvT);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
 int launch_zpotrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv, int* dInfo,
                        int infoBase) {
     static bool attr = false;

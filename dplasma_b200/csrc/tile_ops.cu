@@ -110,6 +110,12 @@ static int trsm_rec(parsec_context_s* ctx, cudaStream_t s, const double* L, int 
     return trsm_rec(ctx, s, L, ldl, winv, j0 + n1, n2, B, ldb, M, batch, strideB, lastBatchM);
 }
 
+// B <- B L^-H through the recursion (both precisions), for callers that bring their own inverses
+int trsm_rec_entry(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, const double* winv, int n, double* B,
+                   int ldb, int M, int batch, long long strideB, int lastBatchM) {
+    return trsm_rec(ctx, s, L, ldl, winv, 0, n, B, ldb, M, batch, strideB, lastBatchM);
+}
+
 int trsm_panel_lower(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, int n, const double* winv,
                      double* B, int ldb, int M, int batch, long long strideB, int lastBatchM) {
     if (batch <= 0 || M <= 0) return 0;

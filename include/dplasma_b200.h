@@ -187,6 +187,13 @@ int check_zpotrf(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec
                  parsec_tiled_matrix_t *A0);
 double dplasma_zlanhe(parsec_context_t *parsec, dplasma_enum_t ntype, dplasma_enum_t uplo,
                       const parsec_tiled_matrix_t *A);
+double dplasma_zlange(parsec_context_t *parsec, dplasma_enum_t ntype, const parsec_tiled_matrix_t *A);
+/* dplasma_z.h:81,84,279: complex solves and their check; dplasmaLower on one process in this build */
+int dplasma_zposv(parsec_context_t *parsec, dplasma_enum_t uplo, parsec_tiled_matrix_t *A, parsec_tiled_matrix_t *B);
+int dplasma_zpotrs(parsec_context_t *parsec, dplasma_enum_t uplo, const parsec_tiled_matrix_t *A,
+                   parsec_tiled_matrix_t *B);
+int check_zaxmb(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec_tiled_matrix_t *A,
+                parsec_tiled_matrix_t *b, parsec_tiled_matrix_t *x);
 /* the numbers the two checks print (src/dplasma_zcheck.c:105,203), for callers that want them */
 double dplasma_b200_last_check_result(parsec_context_t *parsec);
 /* dplasma_zlanhe / dplasma_zlange, InfNorm only (src/dplasma_zcheck.c:101-103,194-196) */

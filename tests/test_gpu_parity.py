@@ -572,3 +572,33 @@ def test_dtrsm_tiled_right(ctx, oracle, uplo, trans):
     assert ctx.lib.dplasma_dtrsm(ctx.ptr, Right, uplo, trans, NonUnit, 1.5, dT.ref, dB.ref) == 0
     assert relerr(read_host(dB, M, N, mb, nb), want) < 1e-10
     dT.free(); dB.free()
+
+
+# ------------------------------------------------------------------ complex solves
+def zmake_rect(ctx, B, mb, nbr):
+    M, R = B.shape
+    d = dp.BlockCyclic(ctx.lib, M, R, mb, nbr, where="host", cplx=True)
+    d.host_array()[:d.elems] = full_to_local(B, mb, nbr).view(np.float64)
+    return d
+
+
+@pytest.mark.parametrize("N,nb,K,nbr", [(378, 93, 67, 31), (1024, 128, 200, 96), (640, 64, 64, 64)])
+def test_zposv_lower_vs_oracle(ctx, oracle, N, nb, K, nbr):
+    """zposv = zpotrf + L then L^H solves (src/zposv_wrapper.c:102-110) against the oracle, plus check_zaxmb"""
+    A0 = oracle.plgsy(float(N), Lower, N, nb, SEED_A, "z")
+    B = oracle.plrnt(N, K, nb, nbr, SEED_B_POSV, "z")
+    dA, dB = zmake_host(ctx, A0, nb), zmake_rect(ctx, B, nb, nbr)
+    assert ctx.lib.dplasma_zposv(ctx.ptr, Lower, dA.ref, dB.ref) == 0
+    X = local_to_full(dB.host_array()[:dB.elems].view(np.complex128), N, K, nb, nbr)
+    Aw, want = A0.copy(order="F"), B.copy(order="F")
+    assert oracle.posv(Lower, Aw, want, nb, nbr, "z") == 0
+    assert relerr(X, want) < 1e-10
+    bad, res = oracle.check_axmb(Lower, A0, B.copy(order="F"), X, "z")
+    assert bad == 0 and res < 60.0
+    dA0, dB0 = zmake_host(ctx, A0, nb), zmake_rect(ctx, B, nb, nbr)
+    assert ctx.lib.check_zaxmb(ctx.ptr, 0, Lower, dA0.ref, dB0.ref, dB.ref) == 0
+    got = ctx.lib.dplasma_b200_last_check_result(ctx.ptr)
+    assert 0.0 <= got < 60.0 and abs(got - res) < 0.5 * max(res, 0.05)
+    assert ctx.lib.dplasma_zlange(ctx.ptr, dp.InfNorm, dB.ref) == pytest.approx(oracle.lange_inf(np.asfortranarray(X), "z"), rel=1e-12)
+    for d in (dA, dB, dA0, dB0):
+        d.free()
