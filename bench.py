@@ -128,7 +128,7 @@ def run_reference(args):
     if rank != 0:
         return
     # bounded sample of the workload: same algorithm, tile kernels and generator, smaller N
-    N, nb = (8192, 256)
+    N, nb = (16384, 256)
     kind, cores, blas, ts = cpu_reference_run(N, nb, args.steps, min(args.warmup, 1))
     t = sum(ts) / len(ts)
     val = flops_dpotrf(N) / t / 1e12
