@@ -93,6 +93,12 @@ class Lib:
         proto("dplasma_dplrnt", i, [vp, i, pBC, u64])
         proto("check_dpotrf", i, [vp, i, i, pBC, pBC])
         proto("check_daxmb", i, [vp, i, i, pBC, pBC, pBC])
+        proto("dplasma_dtrtri", i, [vp, i, i, pBC])
+        proto("dplasma_dlauum", i, [vp, i, pBC])
+        proto("dplasma_dpotri", i, [vp, i, pBC])
+        proto("dplasma_dpoinv", i, [vp, i, pBC])
+        proto("dplasma_dpoinv_sync", i, [vp, i, pBC])
+        proto("check_dpoinv", i, [vp, i, i, pBC, pBC])
         proto("dplasma_zpotrf_New", vp, [i, pBC, C.POINTER(i)])
         proto("dplasma_zpotrf_Destruct", None, [vp])
         proto("dplasma_zpotrf_Destroy", None, [vp])
@@ -118,6 +124,8 @@ class Lib:
         proto("dplasma_b200_dsyrk_tile", i, [vp, vp, i, i, i, i, d, vp, i, d, vp, i])
         proto("dplasma_b200_dgemm_tile", i, [vp, vp, i, i, i, i, i, d, vp, i, vp, i, d, vp, i])
         proto("pdpotrf_", None, [C.c_char_p, C.POINTER(i), vp, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(i)])
+        proto("pdtrsm_", None, [C.c_char_p] * 4 + [C.POINTER(i), C.POINTER(i), C.POINTER(d), vp, C.POINTER(i), C.POINTER(i),
+                                C.POINTER(i), vp, C.POINTER(i), C.POINTER(i), C.POINTER(i)])
         proto("parsec_init_wrapper_", None, [])
         proto("parsec_fini_wrapper_", None, [])
         proto("dplasma_b200_blacs_gridinit", None, [i] * 5)

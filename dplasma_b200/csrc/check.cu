@@ -32,6 +32,42 @@ static int inf_norm(parsec_context_s* ctx, const DevMatrix& A, bool sym, int upl
     return 0;
 }
 
+// B <- B - sym(A) X on one GPU, A symmetric and stored in `uplo` (dplasma_zhemm(Left, uplo, -1, A, X, 1, B),
+// src/dplasma_zcheck.c:199,289): per tile column n of A, one batched launch for the stored tiles (m,n),
+// one for the mirrored tiles (n,m)^T and one for the symmetrised diagonal tile, per tile column of X.
+// diagCopy: one tile of scratch.
+int symm_residual_1gpu(parsec_context_s* parsec, cudaStream_t s, int uplo, const DevMatrix& dA, const DevMatrix& dX,
+                       const DevMatrix& dB, double* diagCopy) {
+    int rc = 0;
+    for (int n = 0; !rc && n < dA.nt; n++) {
+        const int tn = dA.colsOfTile(n);
+        rc = launch_copy_tril(parsec, s, dA.tile(n, n), dA.mb, diagCopy, dA.mb, tn, uplo, 1);
+        for (int c = 0; !rc && c < dB.nt; c++) {
+            const int nc = dB.colsOfTile(c);
+            const double* Xn = dX.tile(n, c);
+            // diagonal tile
+            rc = gemm_single(parsec, s, tn, nc, tn, -1.0, diagCopy, dA.mb, false, Xn, dX.mb, true, 1.0, dB.tile(n, c), dB.mb, 0);
+            // rows below n: A(m,n) stored (Lower) or A(n,m)^T (Upper)
+            const int below = dA.mt - n - 1;
+            if (!rc && below > 0) {
+                const bool st = (uplo == dplasmaLower);
+                rc = gemm_single(parsec, s, dA.mb, nc, tn, -1.0, st ? dA.tile(n + 1, n) : dA.tile(n, n + 1), dA.mb, !st, Xn,
+                                 dX.mb, true, 1.0, dB.tile(n + 1, c), dB.mb, 0, below,
+                                 st ? dA.tileElems : (long long)dA.lmt * dA.tileElems, 0, dB.tileElems,
+                                 dA.rowsOfTile(dA.mt - 1));
+            }
+            // rows above n: A(m,n) stored (Upper) or A(n,m)^T (Lower)
+            if (!rc && n > 0) {
+                const bool st = (uplo == dplasmaUpper);
+                rc = gemm_single(parsec, s, dA.mb, nc, tn, -1.0, st ? dA.tile(0, n) : dA.tile(n, 0), dA.mb, !st, Xn, dX.mb,
+                                 true, 1.0, dB.tile(0, c), dB.mb, 0, n, st ? dA.tileElems : (long long)dA.lmt * dA.tileElems,
+                                 0, dB.tileElems, dA.mb);
+            }
+        }
+    }
+    return rc;
+}
+
 int inf_norm_public(parsec_context_s* ctx, const DevMatrix& A, bool sym, int uplo, double* out) {
     return inf_norm(ctx, A, sym, uplo, out);
 }
@@ -247,34 +283,7 @@ int check_daxmb(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec_
     if (!rc && cudaMalloc(&diagCopy, (size_t)dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
     // b <- b - A x with A symmetric, stored in uplo (dplasma_zhemm(Left, uplo, -1, A, x, 1, b), :199)
     if (!rc && multi) rc = symm_residual_multi(parsec, s, uplo, dA, dX, dB);
-    // single process: per tile column n of A, one batched launch for the stored tiles (m,n), one
-    // for the mirrored tiles (n,m)^T and one for the symmetrised diagonal tile, per RHS tile column
-    for (int n = 0; !rc && !multi && n < dA.nt; n++) {
-        const int tn = dA.colsOfTile(n);
-        rc = launch_copy_tril(parsec, s, dA.tile(n, n), dA.mb, diagCopy, dA.mb, tn, uplo, 1);
-        for (int c = 0; !rc && c < dB.nt; c++) {
-            const int nc = dB.colsOfTile(c);
-            const double* Xn = dX.tile(n, c);
-            // diagonal tile
-            rc = gemm_single(parsec, s, tn, nc, tn, -1.0, diagCopy, dA.mb, false, Xn, dX.mb, true, 1.0, dB.tile(n, c), dB.mb, 0);
-            // rows below n: A(m,n) stored (Lower) or A(n,m)^T (Upper)
-            const int below = dA.mt - n - 1;
-            if (!rc && below > 0) {
-                const bool st = (uplo == dplasmaLower);
-                rc = gemm_single(parsec, s, dA.mb, nc, tn, -1.0, st ? dA.tile(n + 1, n) : dA.tile(n, n + 1), dA.mb, !st, Xn,
-                                 dX.mb, true, 1.0, dB.tile(n + 1, c), dB.mb, 0, below,
-                                 st ? dA.tileElems : (long long)dA.lmt * dA.tileElems, 0, dB.tileElems,
-                                 dA.rowsOfTile(dA.mt - 1));
-            }
-            // rows above n: A(m,n) stored (Upper) or A(n,m)^T (Lower)
-            if (!rc && n > 0) {
-                const bool st = (uplo == dplasmaUpper);
-                rc = gemm_single(parsec, s, dA.mb, nc, tn, -1.0, st ? dA.tile(0, n) : dA.tile(n, 0), dA.mb, !st, Xn, dX.mb,
-                                 true, 1.0, dB.tile(0, c), dB.mb, 0, n, st ? dA.tileElems : (long long)dA.lmt * dA.tileElems,
-                                 0, dB.tileElems, dA.mb);
-            }
-        }
-    }
+    if (!rc && !multi) rc = symm_residual_1gpu(parsec, s, uplo, dA, dX, dB, diagCopy);
     if (!rc) rc = inf_norm(parsec, dB, false, 0, &Rnorm);
     if (!rc) rc = stage_out(parsec, b, &dB, dplasmaUpperLower);
     cudaStreamSynchronize(s);

@@ -172,6 +172,10 @@ int trsm_left_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, 
 int symm_residual_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, const DevMatrix& A, const DevMatrix& X,
                         const DevMatrix& B);
 int check_update_multi(parsec_context_s* ctx, const DevMatrix& L, const DevMatrix& R);
+// check.cu
+int symm_residual_1gpu(parsec_context_s* ctx, cudaStream_t s, int uplo, const DevMatrix& A, const DevMatrix& X,
+                       const DevMatrix& B, double* diagCopy);
+int inf_norm_public(parsec_context_s* ctx, const DevMatrix& A, bool sym, int uplo, double* out);
 // potrf.cu
 int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp);
 int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,

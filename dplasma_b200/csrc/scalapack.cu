@@ -73,4 +73,47 @@ void pdpotrf_(char* UPLO, int* N, double* A, int* IA, int* JA, int* DESCA, int* 
     *info = rc;
 }
 
+// pdtrsm_: src/scalapack_wrappers/dplasma_wrapper_pdtrsm.c:203-327.  op(A) X = alpha B (Left) or
+// X op(A) = alpha B (Right); A is M x M (Left) or N x N (Right) (:263-268), B is M x N.
+void pdtrsm_(char* SIDE, char* UPLO, char* TRANS, char* DIAG, int* M, int* N, double* ALPHA, double* A, int* IA,
+             int* JA, int* DESCA, double* B, int* IB, int* JB, int* DESCB) {
+    if (*M == 0 || *N == 0) return;
+    auto up = [](char c) { return (c >= 'a' && c <= 'z') ? (char)(c - 32) : c; };
+    // OP_SIDE / OP_UPLO / OP_TRANS / OP_DIAG, common.h:146-181
+    const int side = up(*SIDE) == 'L' ? dplasmaLeft : dplasmaRight;
+    const int uplo = up(*UPLO) == 'U' ? dplasmaUpper : dplasmaLower;
+    const int trans = up(*TRANS) == 'N' ? dplasmaNoTrans : (up(*TRANS) == 'T' ? dplasmaTrans : dplasmaConjTrans);
+    const int diag = up(*DIAG) == 'U' ? dplasmaUnit : dplasmaNonUnit;
+    const int Am = (side == dplasmaLeft) ? *M : *N;
+    const int ictxt = DESCA[1];
+    if (DESCA[4] != DESCA[5] || DESCB[4] != DESCB[5] || DESCA[4] != DESCB[4]) {
+        fprintf(stderr, "pdtrsm_: square blocks of one size required (A %dx%d, B %dx%d)\n", DESCA[4], DESCA[5], DESCB[4],
+                DESCB[5]);
+        return;
+    }
+    if (*IA != 1 || *JA != 1 || *IB != 1 || *JB != 1 || DESCA[2] != Am || DESCA[3] != Am || DESCB[2] != *M ||
+        DESCB[3] != *N || DESCB[1] != ictxt) {
+        fprintf(stderr, "pdtrsm_: only IA=JA=IB=JB=1 and whole matrices on one context are supported\n");
+        return;
+    }
+    GridInfo g{1, 1, 0, 0};
+    auto it = g_grids.find(ictxt);
+    if (it != g_grids.end()) g = it->second;
+    if (!g_wrapper_ctx) parsec_init_wrapper_();
+    if (!g_wrapper_ctx) return;
+    const int rank = g.myrow * g.npcol + g.mycol, nb = DESCA[4];
+    parsec_matrix_block_cyclic_t dcA, dcB;
+    parsec_matrix_block_cyclic_lapack_init(&dcA, PARSEC_MATRIX_DOUBLE, PARSEC_MATRIX_LAPACK, rank, nb, nb, Am, Am, 0, 0, Am,
+                                           Am, g.nprow, g.npcol, 1, 1, DESCA[6], DESCA[7], DESCA[8], 0);
+    dcA.super.lln = dcA.super.sln;
+    dcA.mat = A;
+    parsec_matrix_block_cyclic_lapack_init(&dcB, PARSEC_MATRIX_DOUBLE, PARSEC_MATRIX_LAPACK, rank, nb, nb, *M, *N, 0, 0, *M,
+                                           *N, g.nprow, g.npcol, 1, 1, DESCB[6], DESCB[7], DESCB[8], 0);
+    dcB.super.lln = dcB.super.sln;
+    dcB.mat = B;
+    const int rc = dplasma_dtrsm(g_wrapper_ctx, side, uplo, trans, diag, *ALPHA, (parsec_tiled_matrix_t*)&dcA,
+                                 (parsec_tiled_matrix_t*)&dcB);
+    if (rc) fprintf(stderr, "pdtrsm_: dplasma_dtrsm returned %d\n", rc);
+}
+
 }  // extern "C"

@@ -172,6 +172,23 @@ int check_dpotrf(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec
 /* :279, src/dplasma_zcheck.c:180-225 (b is overwritten with b - A x like the reference) */
 int check_daxmb(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec_tiled_matrix_t *A,
                 parsec_tiled_matrix_t *b, parsec_tiled_matrix_t *x);
+/* ---- inversion after the factorization; real double, one process.  The reference runs all
+ *      tile bodies of these DAGs on the CPU (no CUDA body in ztrtri_*.jdf / zlauum_*.jdf / zpoinv_*.jdf). ---- */
+/* dplasma_z.h:86, src/ztrtri_wrapper.c:194-230 (DAGs src/ztrtri_L.jdf, ztrtri_U.jdf).  Returns 0, -1 (uplo),
+ * -2 (diag), -6 (A not square), -101 (could not run), or i > 0: A(i,i) is exactly zero (INFO = k*mb + info,
+ * src/ztrtri_L.jdf:180-186) */
+int dplasma_dtrtri(parsec_context_t *parsec, dplasma_enum_t uplo, dplasma_enum_t diag, parsec_tiled_matrix_t *A);
+/* dplasma_z.h:78, src/zlauum_wrapper.c:184-214 (DAGs src/zlauum_L.jdf, zlauum_U.jdf): Lower A <- L^T L, Upper A <- U U^T */
+int dplasma_dlauum(parsec_context_t *parsec, dplasma_enum_t uplo, parsec_tiled_matrix_t *A);
+/* dplasma_z.h:85, src/zpotri_wrapper.c:55-86: inverse of an SPD matrix from its Cholesky factor */
+int dplasma_dpotri(parsec_context_t *parsec, dplasma_enum_t uplo, parsec_tiled_matrix_t *A);
+/* dplasma_z.h:79-80, src/zpoinv_wrapper.c:184-207,255-272: factor + invert in one call */
+int dplasma_dpoinv(parsec_context_t *parsec, dplasma_enum_t uplo, parsec_tiled_matrix_t *A);
+int dplasma_dpoinv_sync(parsec_context_t *parsec, dplasma_enum_t uplo, parsec_tiled_matrix_t *A);
+/* dplasma_z.h:281, src/dplasma_zcheck.c:265-315: ||Id - Ainv A||_1 / (||A||_1 ||Ainv||_1 N eps) > 10 -> 1.
+ * A is read as a general (full) matrix like the reference's dplasma_zhemm operand, Ainv from its uplo triangle. */
+int check_dpoinv(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec_tiled_matrix_t *A,
+                 parsec_tiled_matrix_t *Ainv);
 /* ---- complex double (zpotrf, BASELINE configs[4]); A->mtype must be PARSEC_MATRIX_COMPLEX_DOUBLE,
  *      tiles hold interleaved (re,im) dplasma_complex64_t.  Both triangles on one GPU, dplasmaLower on a grid.
  *      src/include/dplasma/dplasma_z.h:82,107,109,172,239,280 ---- */
@@ -249,6 +266,11 @@ int dplasma_b200_dgemm_tile(parsec_context_t *ctx, void *stream, dplasma_enum_t 
 
 /* ---- ScaLAPACK-compatible entry: src/scalapack_wrappers/dplasma_wrapper_pdpotrf.c:133-297 ---- */
 void pdpotrf_(char *UPLO, int *N, double *A, int *IA, int *JA, int *DESCA, int *info);
+/* src/scalapack_wrappers/dplasma_wrapper_pdtrsm.c:203-327: like the reference's wrapper the operands are
+ * always redistributed into tiles (:303-307); square equal blocks, IA=JA=IB=JB=1, whole matrices.
+ * ScaLAPACK's pdtrsm has no info argument: argument errors are printed and the call returns. */
+void pdtrsm_(char *SIDE, char *UPLO, char *TRANS, char *DIAG, int *M, int *N, double *ALPHA, double *A, int *IA,
+             int *JA, int *DESCA, double *B, int *IB, int *JB, int *DESCB);
 /* dplasma_wrapper_parsec_init.c:98-124 */
 void parsec_init_wrapper_(void);
 void parsec_fini_wrapper_(void);

@@ -4,7 +4,7 @@
 # Compiles, from the sources where they lie under /root/reference (nothing is copied
 # into the repo), the reference's CPU tile kernels and matrix generators that sit on the
 # tiled-Cholesky path:
-#   src/cores/core_z{potrf,trsm,herk,syrk,gemm,plgsy,plghe,plrnt}.c  (d and z precisions,
+#   src/cores/core_z{potrf,trsm,herk,syrk,gemm,plgsy,plghe,plrnt,trtri,lauum,trmm}.c  (d and z precisions,
 #   expanded by the reference's own tools/PrecisionGenerator exactly like
 #   cmake_modules/PrecisionGenerator.cmake does: one file + one precision per call)
 # and links them with the image's bundled OpenBLAS 0.3.15 (CBLAS + LAPACKE, LP64).
@@ -51,7 +51,7 @@ gen "$R/src/cores/core_zcblas.h" ds "$OUT/inc/cores" || true
 gen "$R/src/cores/core_zcblas.h" zc "$OUT/inc/cores" || true
 OBJS=()
 CF="-O2 -fPIC -w -I$OUT/inc -I$OUT/inc/cores -I$R/src -I$R/src/include -I$R/src/cores"
-for f in potrf trsm herk syrk gemm plgsy plghe plrnt; do
+for f in potrf trsm herk syrk gemm plgsy plghe plrnt trtri lauum trmm; do
   for p in d z; do
     gen "$R/src/cores/core_z$f.c" $p "$OUT/gen"
   done

@@ -100,6 +100,19 @@ class Oracle:
             g("check_potrf").restype = _c_int
             g("check_axmb").argtypes = [_c_int, _c_int, _c_int, _vp, _c_int, _vp, _c_int, _vp, _c_int, ctypes.POINTER(_c_dbl)]
             g("check_axmb").restype = _c_int
+            g("trtri_tile").argtypes = [_c_int, _c_int, _c_int, _vp, _c_int, ctypes.POINTER(_c_int)]
+            g("trtri_tile").restype = None
+            g("lauum_tile").argtypes = [_c_int, _c_int, _vp, _c_int]
+            g("lauum_tile").restype = None
+            g("trmm_tile").argtypes = [_c_int, _c_int, _c_int, _c_int, _c_int, _c_int, sc, _vp, _c_int, _vp, _c_int]
+            g("trmm_tile").restype = None
+            g("trtri").argtypes = [_c_int, _c_int, _c_int, _c_int, _vp, _c_int]
+            g("trtri").restype = _c_int
+            for f in ("lauum", "potri", "poinv"):
+                g(f).argtypes = [_c_int, _c_int, _c_int, _vp, _c_int]
+                g(f).restype = _c_int
+            g("check_poinv").argtypes = [_c_int, _c_int, _vp, _c_int, _vp, _c_int, ctypes.POINTER(_c_dbl)]
+            g("check_poinv").restype = _c_int
 
     @staticmethod
     def _dt(p):
@@ -185,6 +198,44 @@ class Oracle:
                                                       ctypes.byref(r))
         return bad, r.value
 
+    # ---- inversion: src/ztrtri_wrapper.c, zlauum_wrapper.c, zpotri_wrapper.c, zpoinv_wrapper.c
+    def trtri_tile(self, uplo, diag, A, p="d"):
+        info = _c_int(0)
+        getattr(self.lib, f"orc_{p}trtri_tile")(uplo, diag, A.shape[0], _ptr(A), A.shape[0], ctypes.byref(info))
+        return info.value
+
+    def lauum_tile(self, uplo, A, p="d"):
+        getattr(self.lib, f"orc_{p}lauum_tile")(uplo, A.shape[0], _ptr(A), A.shape[0])
+
+    def trmm_tile(self, side, uplo, trans, diag, alpha, A, B, p="d"):
+        m, n = B.shape
+        getattr(self.lib, f"orc_{p}trmm_tile")(side, uplo, trans, diag, m, n, self._sc(p, alpha),
+                                               _ptr(A), A.shape[0], _ptr(B), B.shape[0])
+
+    def trtri(self, uplo, diag, A, nb, p="d"):
+        N = A.shape[0]
+        return getattr(self.lib, f"orc_{p}trtri")(uplo, diag, N, nb, _ptr(A), N)
+
+    def lauum(self, uplo, A, nb, p="d"):
+        N = A.shape[0]
+        return getattr(self.lib, f"orc_{p}lauum")(uplo, N, nb, _ptr(A), N)
+
+    def potri(self, uplo, A, nb, p="d"):
+        N = A.shape[0]
+        return getattr(self.lib, f"orc_{p}potri")(uplo, N, nb, _ptr(A), N)
+
+    def poinv(self, uplo, A, nb, p="d"):
+        N = A.shape[0]
+        return getattr(self.lib, f"orc_{p}poinv")(uplo, N, nb, _ptr(A), N)
+
+    def check_poinv(self, uplo, A, Ainv, p="d"):
+        """A is read as a general (full) matrix, Ainv from its uplo triangle.  returns (suspicious, result)
+        -- src/dplasma_zcheck.c:265-315"""
+        r = _c_dbl(0)
+        N = A.shape[0]
+        bad = getattr(self.lib, f"orc_{p}check_poinv")(uplo, N, _ptr(A), N, _ptr(Ainv), N, ctypes.byref(r))
+        return bad, r.value
+
 
 class Reference:
     """The reference's own compiled CPU tile kernels under an OpenMP restatement of its DAG
@@ -209,6 +260,10 @@ class Reference:
         L.ref_dtrsm.argtypes = [_c_int] * 8 + [_c_dbl, _vp, _c_int, _vp, _c_int]
         L.ref_dpotrs.argtypes = [_c_int] * 5 + [_vp, _c_int, _vp, _c_int]
         L.ref_dposv.argtypes = [_c_int] * 5 + [_vp, _c_int, _vp, _c_int]
+        if hasattr(L, "ref_dtrtri"):
+            L.ref_dtrtri.argtypes = [_c_int, _c_int, _c_int, _c_int, _vp, _c_int]
+            for f in ("ref_dlauum", "ref_dpotri", "ref_dpoinv"):
+                getattr(L, f).argtypes = [_c_int, _c_int, _c_int, _vp, _c_int]
         L.ref_time_dpotrf.restype = _c_dbl
         L.ref_time_dpotrf.argtypes = [_c_int, _c_int, _c_int, _c_u64, ctypes.POINTER(_c_int)]
 
@@ -243,6 +298,22 @@ class Reference:
     def posv(self, uplo, A, B, nb, nbr):
         N, R = B.shape
         return self.lib.ref_dposv(uplo, N, R, nb, nbr, _ptr(A), N, _ptr(B), N)
+
+    def trtri(self, uplo, diag, A, nb):
+        N = A.shape[0]
+        return self.lib.ref_dtrtri(uplo, diag, N, nb, _ptr(A), N)
+
+    def lauum(self, uplo, A, nb):
+        N = A.shape[0]
+        return self.lib.ref_dlauum(uplo, N, nb, _ptr(A), N)
+
+    def potri(self, uplo, A, nb):
+        N = A.shape[0]
+        return self.lib.ref_dpotri(uplo, N, nb, _ptr(A), N)
+
+    def poinv(self, uplo, A, nb):
+        N = A.shape[0]
+        return self.lib.ref_dpoinv(uplo, N, nb, _ptr(A), N)
 
     def time_dpotrf(self, uplo, N, nb, seed=3872):
         """seconds for the factorization only (generation excluded), and info"""

@@ -485,5 +485,223 @@ int P(check_axmb)(int uplo, int N, int NRHS, const T *A, int lda, T *b, int ldb,
     if (result) *result = res;
     return (isnan(Xnorm) || isinf(Xnorm) || isnan(res) || isinf(res) || res > 60.0) ? 1 : 0;
 }
+/* ---------------- inversion after the factorization ---------------- */
+/* CORE_ztrtri -> LAPACKE_ztrtri_work (src/cores/core_ztrtri.c:66-72): in-place inverse of the
+ * uplo triangle; info = i (1-based) if A(i,i) == 0 with NonUnit (nothing is modified then). */
+void P(trtri_tile)(int uplo, int diag, int n, T *A, int lda, int *info)
+{
+    *info = 0;
+    if (diag != ORC_UNIT)
+        for (int i = 0; i < n; i++)
+            if (A[i + (size_t)i * lda] == 0) { *info = i + 1; return; }
+    if (uplo == ORC_LOWER) {
+        /* column j of inv(L): x_jj = 1/l_jj ; x_ij = -(sum_{l=j}^{i-1} l_il x_lj) / l_ii, against a
+         * private copy of the triangle (the inverse overwrites A column by column) */
+        T *L = (T *)malloc((size_t)n * n * sizeof(T));
+        for (int j = 0; j < n; j++)
+            for (int i = j; i < n; i++) L[i + (size_t)j * n] = A[i + (size_t)j * lda];
+        for (int j = 0; j < n; j++) {
+            T xjj = (diag == ORC_UNIT) ? (T)1 : 1 / L[j + (size_t)j * n];
+            if (diag != ORC_UNIT) A[j + (size_t)j * lda] = xjj;
+            for (int i = j + 1; i < n; i++) {
+                T s = L[i + (size_t)j * n] * xjj;
+                for (int l = j + 1; l < i; l++) s += L[i + (size_t)l * n] * A[l + (size_t)j * lda];
+                A[i + (size_t)j * lda] = (diag == ORC_UNIT) ? -s : -s / L[i + (size_t)i * n];
+            }
+        }
+        free(L);
+    } else {
+        T *U = (T *)malloc((size_t)n * n * sizeof(T));
+        for (int j = 0; j < n; j++)
+            for (int i = 0; i <= j; i++) U[i + (size_t)j * n] = A[i + (size_t)j * lda];
+        /* column j of inv(U), rows j down to 0 */
+        for (int j = 0; j < n; j++) {
+            T xjj = (diag == ORC_UNIT) ? (T)1 : 1 / U[j + (size_t)j * n];
+            if (diag != ORC_UNIT) A[j + (size_t)j * lda] = xjj;
+            for (int i = j - 1; i >= 0; i--) {
+                T s = U[i + (size_t)j * n] * xjj;
+                for (int l = i + 1; l < j; l++) s += U[i + (size_t)l * n] * A[l + (size_t)j * lda];
+                A[i + (size_t)j * lda] = (diag == ORC_UNIT) ? -s : -s / U[i + (size_t)i * n];
+            }
+        }
+        free(U);
+    }
+}
+
+/* CORE_zlauum -> LAPACKE_zlauum_work (src/cores/core_zlauum.c): Lower: A <- L^H L ; Upper: A <- U U^H,
+ * the uplo triangle only. */
+void P(lauum_tile)(int uplo, int n, T *A, int lda)
+{
+    T *W = (T *)malloc((size_t)(n > 0 ? n : 1) * n * sizeof(T));
+    for (int j = 0; j < n; j++)
+        for (int i = 0; i < n; i++) {
+            int stored = (uplo == ORC_LOWER) ? (i >= j) : (i <= j);
+            W[i + (size_t)j * n] = stored ? A[i + (size_t)j * lda] : 0;
+        }
+    for (int j = 0; j < n; j++) {
+        int i0 = (uplo == ORC_LOWER) ? j : 0, i1 = (uplo == ORC_LOWER) ? n : j + 1;
+        for (int i = i0; i < i1; i++) {
+            T s = 0;
+            if (uplo == ORC_LOWER)
+                for (int l = i; l < n; l++) s += ORC_CONJ(W[l + (size_t)i * n]) * W[l + (size_t)j * n];
+            else
+                for (int l = j; l < n; l++) s += W[i + (size_t)l * n] * ORC_CONJ(W[j + (size_t)l * n]);
+            A[i + (size_t)j * lda] = (i == j) ? (T)creal(s) : s;
+        }
+    }
+    free(W);
+}
+
+/* CORE_ztrmm -> cblas_ztrmm (src/cores/core_ztrmm.c): B <- alpha op(A) B (Left) or alpha B op(A) (Right) */
+void P(trmm_tile)(int side, int uplo, int trans, int diag, int m, int n, T alpha, const T *A, int lda,
+                  T *B, int ldb)
+{
+    int na = (side == ORC_LEFT) ? m : n;
+    T *W = (T *)malloc((size_t)na * na * sizeof(T)); /* op(A) as a dense matrix */
+    for (int j = 0; j < na; j++)
+        for (int i = 0; i < na; i++) {
+            int r = (trans == ORC_NOTRANS) ? i : j, c = (trans == ORC_NOTRANS) ? j : i;
+            int stored = (uplo == ORC_LOWER) ? (r >= c) : (r <= c);
+            T v = 0;
+            if (r == c) v = (diag == ORC_UNIT) ? (T)1 : A[r + (size_t)c * lda];
+            else if (stored) v = A[r + (size_t)c * lda];
+            if (trans == ORC_CONJTRANS) v = ORC_CONJ(v);
+            W[i + (size_t)j * na] = v;
+        }
+    T *R = (T *)malloc((size_t)m * n * sizeof(T));
+    for (int j = 0; j < n; j++)
+        for (int i = 0; i < m; i++) {
+            T s = 0;
+            if (side == ORC_LEFT)
+                for (int l = 0; l < m; l++) s += W[i + (size_t)l * na] * B[l + (size_t)j * ldb];
+            else
+                for (int l = 0; l < n; l++) s += B[i + (size_t)l * ldb] * W[l + (size_t)j * na];
+            R[i + (size_t)j * m] = alpha * s;
+        }
+    for (int j = 0; j < n; j++)
+        for (int i = 0; i < m; i++) B[i + (size_t)j * ldb] = R[i + (size_t)j * m];
+    free(R);
+    free(W);
+}
+
+/* dplasma_ztrtri: src/ztrtri_L.jdf:21-58 (trsm Right, -1), :60-106 (gemm), :108-142 (trsm Left),
+ * :160-187 (trtri, INFO = k*mb + info); upper mirror src/ztrtri_U.jdf.  Step k of the DAG. */
+int P(trtri)(int uplo, int diag, int N, int nb, T *A, int lda)
+{
+    int nt = (N + nb - 1) / nb, INFO = 0;
+    for (int k = 0; k < nt; k++) {
+        int tk = TD(k), info = 0;
+        if (uplo == ORC_LOWER) {
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = k + 1; m < nt; m++)
+                P(trsm_tile)(ORC_RIGHT, uplo, ORC_NOTRANS, diag, TD(m), tk, -1.0, TL(k, k), lda, TL(m, k), lda);
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = k + 1; m < nt; m++)
+                for (int n = 0; n < k; n++)
+                    P(gemm_tile)(ORC_NOTRANS, ORC_NOTRANS, TD(m), nb, tk, 1.0, TL(m, k), lda, TL(k, n), lda, 1.0,
+                                 TL(m, n), lda);
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = 0; n < k; n++)
+                P(trsm_tile)(ORC_LEFT, uplo, ORC_NOTRANS, diag, tk, nb, 1.0, TL(k, k), lda, TL(k, n), lda);
+        } else {
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = k + 1; n < nt; n++)
+                P(trsm_tile)(ORC_LEFT, uplo, ORC_NOTRANS, diag, tk, TD(n), -1.0, TL(k, k), lda, TL(k, n), lda);
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = k + 1; n < nt; n++)
+                for (int m = 0; m < k; m++)
+                    P(gemm_tile)(ORC_NOTRANS, ORC_NOTRANS, nb, TD(n), tk, 1.0, TL(m, k), lda, TL(k, n), lda, 1.0,
+                                 TL(m, n), lda);
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = 0; m < k; m++)
+                P(trsm_tile)(ORC_RIGHT, uplo, ORC_NOTRANS, diag, nb, tk, 1.0, TL(k, k), lda, TL(m, k), lda);
+        }
+        P(trtri_tile)(uplo, diag, tk, TL(k, k), lda, &info);
+        if (info != 0 && INFO == 0) INFO = k * nb + info;
+    }
+    return INFO;
+}
+
+/* dplasma_zlauum: src/zlauum_L.jdf:38-65 (herk C), :66-98 (gemm C,N), :99-130 (trmm Left C),
+ * :131-155 (lauum tile); upper mirror src/zlauum_U.jdf. */
+int P(lauum)(int uplo, int N, int nb, T *A, int lda)
+{
+    int nt = (N + nb - 1) / nb;
+    for (int k = 0; k < nt; k++) {
+        int tk = TD(k);
+        if (uplo == ORC_LOWER) {
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = 0; n < k; n++) {
+                P(herk_tile)(uplo, ORC_CONJTRANS, nb, tk, 1.0, TL(k, n), lda, 1.0, TL(n, n), lda);
+                for (int m = n + 1; m < k; m++)
+                    P(gemm_tile)(ORC_CONJTRANS, ORC_NOTRANS, nb, nb, tk, 1.0, TL(k, m), lda, TL(k, n), lda, 1.0,
+                                 TL(m, n), lda);
+            }
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = 0; n < k; n++)
+                P(trmm_tile)(ORC_LEFT, uplo, ORC_CONJTRANS, ORC_NONUNIT, tk, nb, 1.0, TL(k, k), lda, TL(k, n), lda);
+        } else {
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = 0; m < k; m++) {
+                P(herk_tile)(uplo, ORC_NOTRANS, nb, tk, 1.0, TL(m, k), lda, 1.0, TL(m, m), lda);
+                for (int n = m + 1; n < k; n++)
+                    P(gemm_tile)(ORC_NOTRANS, ORC_CONJTRANS, nb, nb, tk, 1.0, TL(m, k), lda, TL(n, k), lda, 1.0,
+                                 TL(m, n), lda);
+            }
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = 0; m < k; m++)
+                P(trmm_tile)(ORC_RIGHT, uplo, ORC_CONJTRANS, ORC_NONUNIT, nb, tk, 1.0, TL(k, k), lda, TL(m, k), lda);
+        }
+        P(lauum_tile)(uplo, tk, TL(k, k), lda);
+    }
+    return 0;
+}
+
+/* src/zpotri_wrapper.c:55-86 */
+int P(potri)(int uplo, int N, int nb, T *A, int lda)
+{
+    int info = P(trtri)(uplo, ORC_NONUNIT, N, nb, A, lda);
+    P(lauum)(uplo, N, nb, A, lda);
+    return info;
+}
+/* src/zpoinv_wrapper.c:184-207 (one DAG, INFO of the factorization) */
+int P(poinv)(int uplo, int N, int nb, T *A, int lda)
+{
+    int info = P(potrf)(uplo, N, nb, A, lda);
+    if (info) return info;
+    return P(potri)(uplo, N, nb, A, lda);
+}
+
+/* check_zpoinv (src/dplasma_zcheck.c:265-315): R = Id - Ainv A (hemm Left, Ainv stored in uplo, A read
+ * as a general matrix); result = ||R||_1 / (||A||_1 ||Ainv||_1 N eps); suspicious iff not finite or > 10. */
+int P(check_poinv)(int uplo, int N, const T *A, int lda, const T *Ainv, int ldi, double *result)
+{
+    double Anorm = P(lanhe_inf)(uplo, N, A, lda);      /* one norm == inf norm for hermitian */
+    double Inorm = P(lanhe_inf)(uplo, N, Ainv, ldi);
+    double *cs = (double *)calloc((size_t)N, sizeof(double)), Rnorm = 0.0;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int c = 0; c < N; c++) {
+        double colsum = 0.0;
+        for (int i = 0; i < N; i++) {
+            T s = (i == c) ? (T)1 : (T)0;
+            for (int j = 0; j < N; j++) {
+                T a;
+                if (i == j) a = (T)creal(Ainv[i + (size_t)i * ldi]);
+                else if ((uplo == ORC_LOWER) == (i > j)) a = Ainv[i + (size_t)j * ldi];
+                else a = ORC_CONJ(Ainv[j + (size_t)i * ldi]);
+                s -= a * A[j + (size_t)c * lda];
+            }
+            colsum += ORC_ABS(s);
+        }
+        cs[c] = colsum;
+    }
+    for (int c = 0; c < N; c++)
+        if (cs[c] > Rnorm || isnan(cs[c])) Rnorm = cs[c];
+    free(cs);
+    double eps = 0x1.0p-53;
+    double res = Rnorm / ((Anorm * Inorm) * N * eps);
+    if (result) *result = res;
+    return (isinf(Inorm) || isnan(res) || isinf(res) || res > 10.0) ? 1 : 0;
+}
 #undef TL
 #undef TD

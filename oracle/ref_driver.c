@@ -313,6 +313,112 @@ int ref_dposv(int uplo, int N, int NRHS, int nb, int nbr, double *A, int lda, do
     return info;
 }
 
+/* ---- inversion after the factorization -------------------------------
+ * trtri: src/ztrtri_L.jdf:21-58 (trsm Right, alpha=-1), :60-106 (gemm), :108-142 (trsm Left),
+ *        :160-187 (CORE_ztrtri, INFO = k*mb + info); upper mirror src/ztrtri_U.jdf:24-58,
+ *        62-110,114-149,170-194.
+ * lauum: src/zlauum_L.jdf:38-65 (herk ConjTrans), :66-98 (gemm C,N), :99-130 (trmm Left,
+ *        ConjTrans), :131-155 (CORE_zlauum); upper mirror src/zlauum_U.jdf:42-70,75-108,
+ *        112-143,147-170.
+ * Step k of each DAG is run here with the tasks of the step in the order the flows force
+ * (the steps are sequential along the RW chain of every tile).                          */
+int ref_dtrtri(int uplo, int diag, int N, int nb, double *A, int lda)
+{
+    int nt = (N + nb - 1) / nb, INFO = 0;
+    openblas_set_num_threads(1);
+    for (int k = 0; k < nt; k++) {
+        int tk = tdim(N, nb, k);
+        double *Akk = TILE(A, lda, nb, k, k);
+        if (uplo == PlasmaLower) {
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = k + 1; m < nt; m++)
+                CORE_dtrsm(PlasmaRight, uplo, PlasmaNoTrans, diag, tdim(N, nb, m), tk, -1.0, Akk, lda,
+                           TILE(A, lda, nb, m, k), lda);
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
+            for (int m = k + 1; m < nt; m++)
+                for (int n = 0; n < k; n++)
+                    CORE_dgemm(PlasmaNoTrans, PlasmaNoTrans, tdim(N, nb, m), nb, tk, 1.0,
+                               TILE(A, lda, nb, m, k), lda, TILE(A, lda, nb, k, n), lda, 1.0,
+                               TILE(A, lda, nb, m, n), lda);
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = 0; n < k; n++)
+                CORE_dtrsm(PlasmaLeft, uplo, PlasmaNoTrans, diag, tk, nb, 1.0, Akk, lda,
+                           TILE(A, lda, nb, k, n), lda);
+        } else {
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = k + 1; n < nt; n++)
+                CORE_dtrsm(PlasmaLeft, uplo, PlasmaNoTrans, diag, tk, tdim(N, nb, n), -1.0, Akk, lda,
+                           TILE(A, lda, nb, k, n), lda);
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
+            for (int m = 0; m < k; m++)
+                for (int n = k + 1; n < nt; n++)
+                    CORE_dgemm(PlasmaNoTrans, PlasmaNoTrans, nb, tdim(N, nb, n), tk, 1.0,
+                               TILE(A, lda, nb, m, k), lda, TILE(A, lda, nb, k, n), lda, 1.0,
+                               TILE(A, lda, nb, m, n), lda);
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = 0; m < k; m++)
+                CORE_dtrsm(PlasmaRight, uplo, PlasmaNoTrans, diag, nb, tk, 1.0, Akk, lda,
+                           TILE(A, lda, nb, m, k), lda);
+        }
+        int info = 0;
+        CORE_dtrtri(uplo, diag, tk, Akk, lda, &info);
+        if (info != 0 && INFO == 0) INFO = k * nb + info;
+    }
+    return INFO;
+}
+int ref_dlauum(int uplo, int N, int nb, double *A, int lda)
+{
+    int nt = (N + nb - 1) / nb;
+    openblas_set_num_threads(1);
+    for (int k = 0; k < nt; k++) {
+        int tk = tdim(N, nb, k);
+        double *Akk = TILE(A, lda, nb, k, k);
+        if (uplo == PlasmaLower) {
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = 0; n < k; n++) {
+                CORE_dsyrk(uplo, PlasmaTrans, nb, tk, 1.0, TILE(A, lda, nb, k, n), lda, 1.0,
+                           TILE(A, lda, nb, n, n), lda);
+                for (int m = n + 1; m < k; m++)
+                    CORE_dgemm(PlasmaTrans, PlasmaNoTrans, nb, nb, tk, 1.0, TILE(A, lda, nb, k, m), lda,
+                               TILE(A, lda, nb, k, n), lda, 1.0, TILE(A, lda, nb, m, n), lda);
+            }
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int n = 0; n < k; n++)
+                CORE_dtrmm(PlasmaLeft, uplo, PlasmaTrans, PlasmaNonUnit, tk, nb, 1.0, Akk, lda,
+                           TILE(A, lda, nb, k, n), lda);
+        } else {
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = 0; m < k; m++) {
+                CORE_dsyrk(uplo, PlasmaNoTrans, nb, tk, 1.0, TILE(A, lda, nb, m, k), lda, 1.0,
+                           TILE(A, lda, nb, m, m), lda);
+                for (int n = m + 1; n < k; n++)
+                    CORE_dgemm(PlasmaNoTrans, PlasmaTrans, nb, nb, tk, 1.0, TILE(A, lda, nb, m, k), lda,
+                               TILE(A, lda, nb, n, k), lda, 1.0, TILE(A, lda, nb, m, n), lda);
+            }
+#pragma omp parallel for schedule(dynamic, 1)
+            for (int m = 0; m < k; m++)
+                CORE_dtrmm(PlasmaRight, uplo, PlasmaTrans, PlasmaNonUnit, nb, tk, 1.0, Akk, lda,
+                           TILE(A, lda, nb, m, k), lda);
+        }
+        CORE_dlauum(uplo, tk, Akk, lda);
+    }
+    return 0;
+}
+/* src/zpotri_wrapper.c:55-86 ; src/zpoinv_wrapper.c:255-272 (the _sync form: three DAGs in a row) */
+int ref_dpotri(int uplo, int N, int nb, double *A, int lda)
+{
+    int info = ref_dtrtri(uplo, PlasmaNonUnit, N, nb, A, lda);
+    ref_dlauum(uplo, N, nb, A, lda);
+    return info;
+}
+int ref_dpoinv(int uplo, int N, int nb, double *A, int lda)
+{
+    int info = ref_dpotrf(uplo, N, nb, A, lda);
+    info = ref_dtrtri(uplo, PlasmaNonUnit, N, nb, A, lda);
+    ref_dlauum(uplo, N, nb, A, lda);
+    return info;
+}
+
 /* Timed run used by bench.py (--impl reference and cpu_baseline): generate with the
  * reference generator, factor with the reference tile kernels under the OpenMP DAG with
  * single-threaded BLAS inside tasks (INSTALL.rst:642-650).  Returns seconds of the

@@ -57,6 +57,18 @@ def test_new_rejects_bad_uplo_and_sets_info():
     assert lib.dplasma_dtrsm(None, dp.Left, dp.Lower, dp.NoTrans, 5, 1.0, C.byref(s), C.byref(s)) == -4
     assert lib.dplasma_dposv(None, 7, C.byref(s), C.byref(s)) == -1   # src/zposv_wrapper.c:73-76
     assert lib.dplasma_dpotrs(None, 7, C.byref(s), C.byref(s)) == -1
+    # inversion path: src/ztrtri_wrapper.c:203-216, zlauum_wrapper.c:192-200, zpotri_wrapper.c:62-65
+    r = dp.capi.BlockCyclicStruct()
+    lib.parsec_matrix_block_cyclic_init(C.byref(r), dp.MATRIX_DOUBLE, dp.MATRIX_TILE, 0, 4, 4, 8, 12, 0, 0, 8, 12, 1, 1, 1, 1, 0, 0)
+    assert lib.dplasma_dtrtri(None, 7, dp.NonUnit, C.byref(s)) == -1
+    assert lib.dplasma_dtrtri(None, dp.Lower, 7, C.byref(s)) == -2
+    assert lib.dplasma_dtrtri(None, dp.Lower, dp.NonUnit, C.byref(r)) == -6
+    assert lib.dplasma_dlauum(None, 7, C.byref(s)) == -1
+    assert lib.dplasma_dlauum(None, dp.Upper, C.byref(r)) == -6
+    assert lib.dplasma_dpotri(None, 7, C.byref(s)) == -1
+    assert lib.dplasma_dpoinv(None, 7, C.byref(s)) == -1
+    assert lib.dplasma_dpoinv_sync(None, 7, C.byref(s)) == -1
+    assert lib.dplasma_dpotri(None, dp.Lower, C.byref(s)) == -100  # no context: nothing runs
 
 
 @pytest.mark.parametrize("M,N,mb,nb,P,Q", [(378, 378, 93, 93, 1, 1), (378, 367, 93, 93, 2, 2), (1000, 1000, 120, 120, 2, 4),
