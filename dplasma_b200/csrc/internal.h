@@ -180,5 +180,5 @@ int inf_norm_public(parsec_context_s* ctx, const DevMatrix& A, bool sym, int upl
 int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp);
 int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,
                     long long rowStride, const double* colPanel, long long colStride, int gnFirst,
-                    int gnEnd, double alpha, int K, int kTile = 0, long long kTileStride = 0);
+                    int gnEnd, double alpha, int K, int kTile = 0, long long kTileStride = 0, int rowFirstFixed = -1);
 }  // namespace dpb

@@ -27,7 +27,7 @@ static cudaEvent_t get_event(parsec_context_s* ctx, size_t idx) {
 // gnFirst <= gn < gnEnd and gm >= gn; diagonal tiles only in their lower part (SYRK).
 int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,
                     long long rowStride, const double* colPanel, long long colStride, int gnFirst, int gnEnd,
-                    double alpha, int K, int kTile, long long kTileStride) {
+                    double alpha, int K, int kTile, long long kTileStride, int rowFirstFixed) {
     const int jl0 = C.firstLocalColGE(gnFirst), jl1 = std::min(C.firstLocalColGE(gnEnd), C.lnt);
     const int rowEnd = std::min(C.firstLocalRowGE(C.mt), C.lmt);
     for (int c0 = jl0; c0 < jl1; c0 += kMaxCols) {
@@ -58,7 +58,9 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
         long long tiles = 0;
         for (int c = 0; c < ncols; c++) {
             const int gn = (c0 + c) * C.Q + C.pcol;
-            d.rowFirst[c] = std::min(C.firstLocalRowGE(gn), rowEnd);
+            // rowFirstFixed >= 0: a rectangle of tiles (every column starts at that local tile row) instead of
+            // the trapezoid below the diagonal (potri.cu)
+            d.rowFirst[c] = std::min(rowFirstFixed >= 0 ? rowFirstFixed : C.firstLocalRowGE(gn), rowEnd);
             tiles += rowEnd - d.rowFirst[c];
         }
         if (tiles == 0) continue;

@@ -7,17 +7,17 @@
 //
 // The reference runs every tile body of these DAGs on the CPU (CORE_ztrsm / CORE_zgemm /
 // CORE_ztrmm / CORE_zherk / CORE_ztrtri / CORE_zlauum; none of the four JDFs has a CUDA body).
-// Here step k of each DAG is a handful of batched launches of the DMMA engine:
+// Here step k of each DAG is a handful of launches of the DMMA engine, every product in the engine's
+// fastest form (C += A B^T, both operands M-major) after one transposition of the step's tile row:
 //   trtri, step k:  W = inv(A(k,k))                            (tile solve against the identity)
 //                   A(m,k) = -A(m,k) W            m > k        (one launch, batched over m)
-//                   A(m,n) += A(m,k) A(k,n)       m > k > n    (one launch per n, batched over m)
+//                   A(m,n) += A(m,k) A(k,n)       m > k > n    (ONE grouped launch over the rectangle)
 //                   A(k,n) = W A(k,n)             n < k        (one launch, batched over n)
-//   lauum, step k:  A(m,n) += A(k,m)^T A(k,n)     n <= m < k   (two launches per n: diagonal tile, rest)
+//   lauum, step k:  A(m,n) += A(k,m)^T A(k,n)     n <= m < k   (ONE grouped launch: the factorization's
+//                                                               trailing-update kernel on the leading tiles)
 //                   A(k,n) = tril(A(k,k))^T A(k,n)             (one launch, batched over n)
 //                   A(k,k) = tril(A(k,k))^T tril(A(k,k))
-// Products that would overwrite one of their own operands read a private copy of that panel
-// (one tile row / tile column of scratch).  Upper runs as Lower on the transposed tile grid,
-// like the factorization (potrf.cu).  Single process only.
+// Upper runs as Lower on the transposed tile grid, like the factorization (potrf.cu).  Single process only.
 #include <cmath>
 #include <cstdio>
 #include <algorithm>
@@ -93,21 +93,44 @@ __global__ void __launch_bounds__(1024) diag_zero_scan_kernel(DevMatrix A, int* 
     if (threadIdx.x == 0 && best[0] != 0x7fffffff && *info == 0) *info = best[0] + 1;
 }
 
-// gather the tiles (k, 0..cnt-1) of tile row k (strided by a tile column) into contiguous scratch
-static int copy_tile_row(cudaStream_t s, const DevMatrix& A, int k, int cnt, double* dst) {
-    const size_t tb = (size_t)A.tileElems * sizeof(double), pitch = (size_t)A.lmt * tb;
-    if (cnt <= 0) return 0;
-    if (pitch < ((size_t)1 << 31)) {
-        DPB_CUDA(cudaMemcpy2DAsync(dst, tb, A.tile(k, 0), pitch, tb, (size_t)cnt, cudaMemcpyDeviceToDevice, s));
-        return 0;
+// dst_t = (src_t)^T for t = 0..cnt-1: src tile t (rows x cols valid, ld) at src + t*srcStride, dst tile t
+// (cols x rows) at dst + t*dstStride.  One CTA per 32x32 block; blockIdx.z walks the tiles.
+__global__ void __launch_bounds__(256) transpose_tiles_kernel(const double* __restrict__ src, long long srcStride,
+                                                              double* __restrict__ dst, long long dstStride, int ld,
+                                                              int rows, int cols) {
+    __shared__ double t[32][33];
+    const double* S = src + (size_t)blockIdx.z * srcStride;
+    double* D = dst + (size_t)blockIdx.z * dstStride;
+    const int bi = blockIdx.x * 32, bj = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int j = ty; j < 32; j += 8)
+        if (bi + tx < rows && bj + j < cols) t[j][tx] = S[(bi + tx) + (size_t)(bj + j) * ld];
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8)
+        if (bj + tx < cols && bi + j < rows) D[(bj + tx) + (size_t)(bi + j) * ld] = t[tx][j];
+}
+static int launch_transpose_tiles(parsec_context_s* ctx, cudaStream_t s, const double* src, long long srcStride,
+                                  double* dst, long long dstStride, int ld, int rows, int cols, int cnt) {
+    if (cnt <= 0 || rows <= 0 || cols <= 0) return 0;
+    for (int t0 = 0; t0 < cnt; t0 += 65535) {
+        const int c = std::min(65535, cnt - t0);
+        dim3 grid((rows + 31) / 32, (cols + 31) / 32, c);
+        transpose_tiles_kernel<<<grid, 256, 0, s>>>(src + (size_t)t0 * srcStride, srcStride, dst + (size_t)t0 * dstStride,
+                                                    dstStride, ld, rows, cols);
+        ctx->launches++;
     }
-    for (int n = 0; n < cnt; n++)
-        DPB_CUDA(cudaMemcpyAsync(dst + (size_t)n * A.tileElems, A.tile(k, n), tb, cudaMemcpyDeviceToDevice, s));
-    return 0;
+    return (int)cudaGetLastError();
 }
 
-// A <- inv(A), A lower triangular on a single-process tile grid.  W: one tile, Wp: nt tiles of scratch.
-static int trtri_lower_1gpu(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int diag, double* W, double* Wp) {
+// Every product below is brought to the engine's fastest form, C += A B^T with both operands M-major
+// (the form of the factorization's trailing update), by transposing the tile row of the step once
+// (an HBM-bound pass over k tiles); the transposed copy doubles as the private copy a product needs
+// when it overwrites its own operand.
+
+// A <- inv(A), A lower triangular on a single-process tile grid.
+// Scratch: W, W2 one tile each, Wp nt tiles.
+static int trtri_lower_1gpu(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int diag, double* W, double* W2,
+                            double* Wp) {
     const int nt = A.nt, nb = A.nb, ld = A.mb;
     const long long te = A.tileElems, cs = (long long)A.lmt * te;
     int rc = ensure_winv(ctx, nb);
@@ -121,20 +144,23 @@ static int trtri_lower_1gpu(parsec_context_s* ctx, cudaStream_t s, const DevMatr
         if (!rc) rc = trsm_left(ctx, s, dplasmaLower, dplasmaNoTrans, diag, tk, tk, 1.0, Akk, ld, W, ld, winv);
         if (rc) return rc;
         if (below > 0) {
-            // A(m,k) = -A(m,k) inv(A(k,k))  (trtri_ztrsmR, :21-58)
+            // A(m,k) = -A(m,k) inv(A(k,k)) = -A(m,k) (W^T)^T  (trtri_ztrsmR, :21-58), one launch batched over m
+            rc = launch_transpose(ctx, s, W, ld, W2, ld, tk, tk);
+            if (rc) return rc;
             DPB_CUDA(cudaMemcpyAsync(Wp, A.tile(k + 1, k), (size_t)below * te * sizeof(double), cudaMemcpyDeviceToDevice, s));
-            rc = gemm_single(ctx, s, ld, tk, tk, -1.0, Wp, ld, false, W, ld, true, 0.0, A.tile(k + 1, k), ld, 0, below, te,
+            rc = gemm_single(ctx, s, ld, tk, tk, -1.0, Wp, ld, false, W2, ld, false, 0.0, A.tile(k + 1, k), ld, 0, below, te,
                              0, te, A.rowsOfTile(nt - 1));
-            // A(m,n) += A(m,k) A(k,n), n < k  (trtri_zgemm, :60-106)
-            for (int n = 0; !rc && n < k; n++)
-                rc = gemm_single(ctx, s, ld, nb, tk, 1.0, A.tile(k + 1, k), ld, false, A.tile(k, n), ld, true, 1.0,
-                                 A.tile(k + 1, n), ld, 0, below, te, 0, te, A.rowsOfTile(nt - 1));
             if (rc) return rc;
         }
         if (k > 0) {
-            // A(k,n) = inv(A(k,k)) A(k,n)  (trtri_ztrsmL, :108-142)
-            rc = copy_tile_row(s, A, k, k, Wp);
-            if (!rc) rc = gemm_single(ctx, s, tk, nb, tk, 1.0, W, ld, false, Wp, ld, true, 0.0, A.tile(k, 0), ld, 0, k, 0, te,
+            // Wp(n) = A(k,n)^T, n < k
+            rc = launch_transpose_tiles(ctx, s, A.tile(k, 0), cs, Wp, te, ld, tk, nb, k);
+            // A(m,n) += A(m,k) A(k,n) = A(m,k) Wp(n)^T for the whole rectangle m > k > n  (trtri_zgemm, :60-106):
+            // one grouped launch
+            if (!rc && below > 0)
+                rc = trailing_update(ctx, s, A, A.tile(0, k), te, Wp, te, 0, k, 1.0, tk, 0, 0, k + 1);
+            // A(k,n) = inv(A(k,k)) A(k,n) = W Wp(n)^T  (trtri_ztrsmL, :108-142), one launch batched over n
+            if (!rc) rc = gemm_single(ctx, s, tk, nb, tk, 1.0, W, ld, false, Wp, ld, false, 0.0, A.tile(k, 0), ld, 0, k, 0, te,
                                       cs, tk);
             if (rc) return rc;
         }
@@ -145,34 +171,36 @@ static int trtri_lower_1gpu(parsec_context_s* ctx, cudaStream_t s, const DevMatr
 }
 
 // A <- L^T L on the lower triangle of a single-process tile grid
-static int lauum_lower_1gpu(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, double* W, double* Wp) {
+static int lauum_lower_1gpu(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, double* W, double* W2, double* Wp) {
     const int nt = A.nt, nb = A.nb, ld = A.mb;
     const long long te = A.tileElems, cs = (long long)A.lmt * te;
     int rc = 0;
     for (int k = 0; k < nt; k++) {
         const int tk = A.rowsOfTile(k);
         double* Akk = A.tile(k, k);
-        // W = tril(A(k,k)), zeros above the diagonal
+        // W2 = tril(A(k,k))^T (zeros below the diagonal)
         rc = launch_copy_tril(ctx, s, Akk, ld, W, ld, tk, dplasmaLower, 0);
+        if (!rc) rc = launch_transpose(ctx, s, W, ld, W2, ld, tk, tk);
         if (rc) return rc;
         if (k > 0) {
-            rc = copy_tile_row(s, A, k, k, Wp);
-            for (int n = 0; !rc && n < k; n++) {
-                const double* Rn = Wp + (size_t)n * te;
-                // A(n,n) += A(k,n)^T A(k,n), lower  (lauum_zherk, src/zlauum_L.jdf:38-65)
-                rc = gemm_single(ctx, s, nb, nb, tk, 1.0, Rn, ld, true, Rn, ld, true, 1.0, A.tile(n, n), ld, 1);
-                // A(m,n) += A(k,m)^T A(k,n), n < m < k  (lauum_zgemm, :66-98)
-                if (!rc && k - 1 - n > 0)
-                    rc = gemm_single(ctx, s, nb, nb, tk, 1.0, Rn + te, ld, true, Rn, ld, true, 1.0, A.tile(n + 1, n), ld, 0,
-                                     k - 1 - n, te, 0, te, nb);
+            // Wp(n) = A(k,n)^T, n < k
+            rc = launch_transpose_tiles(ctx, s, A.tile(k, 0), cs, Wp, te, ld, tk, nb, k);
+            // A(m,n) += A(k,m)^T A(k,n) = Wp(m) Wp(n)^T, n <= m < k, diagonal tiles in their lower part only
+            // (lauum_zherk, src/zlauum_L.jdf:38-65, and lauum_zgemm, :66-98): the factorization's grouped
+            // trailing-update launch on the leading k x k tiles
+            if (!rc) {
+                DevMatrix V = A;
+                V.mt = V.nt = k;
+                V.M = V.N = k * nb;
+                rc = trailing_update(ctx, s, V, Wp, te, Wp, te, 0, k, 1.0, tk);
             }
-            // A(k,n) = A(k,k)^T A(k,n)  (lauum_ztrmm, :99-130)
-            if (!rc) rc = gemm_single(ctx, s, tk, nb, tk, 1.0, W, ld, true, Wp, ld, true, 0.0, A.tile(k, 0), ld, 0, k, 0, te,
-                                      cs, tk);
+            // A(k,n) = A(k,k)^T A(k,n) = W2 Wp(n)^T  (lauum_ztrmm, :99-130), one launch batched over n
+            if (!rc) rc = gemm_single(ctx, s, tk, nb, tk, 1.0, W2, ld, false, Wp, ld, false, 0.0, A.tile(k, 0), ld, 0, k, 0,
+                                      te, cs, tk);
             if (rc) return rc;
         }
-        // A(k,k) = A(k,k)^T A(k,k), lower  (lauum_zlauum, :131-155)
-        rc = gemm_single(ctx, s, tk, tk, tk, 1.0, W, ld, true, W, ld, true, 0.0, Akk, ld, 1);
+        // A(k,k) = A(k,k)^T A(k,k) = W2 W2^T, lower  (lauum_zlauum, :131-155)
+        rc = gemm_single(ctx, s, tk, tk, tk, 1.0, W2, ld, false, W2, ld, false, 0.0, Akk, ld, 1);
         if (rc) return rc;
     }
     return 0;
@@ -196,12 +224,13 @@ static int run_inverse_chain(parsec_context_s* ctx, const char* name, int ops, i
     cudaSetDevice(ctx->device);
     cudaStream_t s = ctx->sPanel;
     DevMatrix dA;
-    double *W = nullptr, *Wp = nullptr;
+    double *W = nullptr, *W2 = nullptr, *Wp = nullptr;
     for (cudaEvent_t e : ctx->evIn) cudaEventDestroy(e);
     ctx->evIn.clear();
     int rc = stage_in(ctx, A, &dA, true, uplo);
     if (!rc && (dA.mb != dA.nb || dA.mt != dA.nt)) rc = -3;
     if (!rc && cudaMalloc(&W, (size_t)dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
+    if (!rc && cudaMalloc(&W2, (size_t)dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
     if (!rc && cudaMalloc(&Wp, (size_t)dA.nt * dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
     if (!rc && cudaMemsetAsync(ctx->dInfo, 0, sizeof(int), s) != cudaSuccess) rc = -201;
     if (!rc) *ctx->hInfo = 0;
@@ -230,9 +259,9 @@ static int run_inverse_chain(parsec_context_s* ctx, const char* name, int ops, i
                 ctx->launches++;
                 rc = (int)cudaGetLastError();
             }
-            if (!rc) rc = trtri_lower_1gpu(ctx, s, dA, diag, W, Wp);
+            if (!rc) rc = trtri_lower_1gpu(ctx, s, dA, diag, W, W2, Wp);
         }
-        if (!rc && (ops & OP_LAUUM)) rc = lauum_lower_1gpu(ctx, s, dA, W, Wp);
+        if (!rc && (ops & OP_LAUUM)) rc = lauum_lower_1gpu(ctx, s, dA, W, W2, Wp);
         if (!rc && uplo == dplasmaUpper) rc = launch_transpose_grid(ctx, s, dA);
     }
     if (!rc) rc = (int)cudaEventRecord(ctx->evStop, s);
@@ -242,6 +271,7 @@ static int run_inverse_chain(parsec_context_s* ctx, const char* name, int ops, i
     float ms = 0.f;
     if (!rc && cudaEventElapsedTime(&ms, ctx->evStart, ctx->evStop) == cudaSuccess) ctx->lastElapsed = ms * 1e-3;
     if (W) cudaFree(W);
+    if (W2) cudaFree(W2);
     if (Wp) cudaFree(Wp);
     stage_free(&dA);
     if (rc) return rc < 0 ? rc : -1000 - rc;

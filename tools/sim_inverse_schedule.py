@@ -47,7 +47,7 @@ def run(N, nb, diag_unit=False):
     Lin = L.copy()
     U0 = rng.standard_normal((N, N))
     Lin += np.triu(U0, 1)  # junk in the other triangle: must be ignored and preserved
-    mem = Mem(nt * nt * te + te + nt * te)
+    mem = Mem(nt * nt * te + te + nt * te + te)
     W = nt * nt * te
     Wp = W + te
 
@@ -62,6 +62,30 @@ def run(N, nb, diag_unit=False):
             blk = Lin[i * nb:(i + 1) * nb, j * nb:(j + 1) * nb]
             mem.mat(tile(i, j), nb, blk.shape[0], blk.shape[1])[:, :] = blk
     ld = nb
+    W2 = Wp + nt * te
+
+    def transpose_tiles(src, sstride, dst, dstride, rows_, cols_, cnt):
+        for t in range(cnt):
+            mem.mat(dst + t * dstride, ld, cols_, rows_)[:, :] = mem.mat(src + t * sstride, ld, rows_, cols_).T
+
+    def trailing_update(mt_view, rowPanel, rowStride, colPanel, colStride, gn0, gn1, alpha, K, rowFirstFixed=-1, rowEnd=None):
+        rowEnd = mt_view if rowEnd is None else rowEnd
+        pend = []
+        for n_ in range(gn0, gn1):
+            first = rowFirstFixed if rowFirstFixed >= 0 else n_
+            for m_ in range(first, rowEnd):
+                tm = rows(m_) if mt_view == nt else nb
+                Am = mem.mat(rowPanel + m_ * rowStride, nb, tm, K)
+                Bm = mem.mat(colPanel + n_ * colStride, nb, nb, K)
+                Cm = mem.mat(tile(m_, n_), nb, tm, nb)
+                pend.append((Cm, Cm + alpha * (Am @ Bm.T), m_ == n_))
+        for Cm, R, dg in pend:
+            if dg:
+                mask = np.tril(np.ones(Cm.shape, bool))
+                Cm[mask] = R[mask]
+            else:
+                Cm[:, :] = R
+
     # ---- trtri
     for k in range(nt):
         tk, below = rows(k), nt - k - 1
@@ -71,16 +95,15 @@ def run(N, nb, diag_unit=False):
             T = np.tril(Akk, -1) + np.eye(tk)
         mem.mat(W, ld, tk, tk)[:, :] = np.linalg.inv(T)  # identity + trsm_left
         if below > 0:
+            mem.mat(W2, ld, tk, tk)[:, :] = mem.mat(W, ld, tk, tk).T.copy()
             n = below * te
             mem.a[Wp:Wp + n] = mem.a[tile(k + 1, k):tile(k + 1, k) + n]
-            gemm_single(mem, ld, tk, tk, -1.0, Wp, ld, False, W, ld, True, 0.0, tile(k + 1, k), ld, 0, below, te, 0, te, rows(nt - 1))
-            for n_ in range(k):
-                gemm_single(mem, ld, nb, tk, 1.0, tile(k + 1, k), ld, False, tile(k, n_), ld, True, 1.0, tile(k + 1, n_), ld, 0,
-                            below, te, 0, te, rows(nt - 1))
+            gemm_single(mem, ld, tk, tk, -1.0, Wp, ld, False, W2, ld, False, 0.0, tile(k + 1, k), ld, 0, below, te, 0, te, rows(nt - 1))
         if k > 0:
-            for n_ in range(k):
-                mem.a[Wp + n_ * te:Wp + (n_ + 1) * te] = mem.a[tile(k, n_):tile(k, n_) + te]
-            gemm_single(mem, tk, nb, tk, 1.0, W, ld, False, Wp, ld, True, 0.0, tile(k, 0), ld, 0, k, 0, te, cs, tk)
+            transpose_tiles(tile(k, 0), cs, Wp, te, tk, nb, k)
+            if below > 0:
+                trailing_update(nt, tile(0, k), te, Wp, te, 0, k, 1.0, tk, rowFirstFixed=k + 1)
+            gemm_single(mem, tk, nb, tk, 1.0, W, ld, False, Wp, ld, False, 0.0, tile(k, 0), ld, 0, k, 0, te, cs, tk)
         Wm = mem.mat(W, ld, tk, tk)
         mask = np.tril(np.ones((tk, tk), bool), -1 if diag_unit else 0)
         Akk[mask] = Wm[mask]
@@ -100,18 +123,12 @@ def run(N, nb, diag_unit=False):
     for k in range(nt):
         tk = rows(k)
         Akk = mem.mat(tile(k, k), ld, tk, tk)
-        mem.mat(W, ld, tk, tk)[:, :] = np.tril(Akk)
+        mem.mat(W2, ld, tk, tk)[:, :] = np.tril(Akk).T
         if k > 0:
-            for n_ in range(k):
-                mem.a[Wp + n_ * te:Wp + (n_ + 1) * te] = mem.a[tile(k, n_):tile(k, n_) + te]
-            for n_ in range(k):
-                Rn = Wp + n_ * te
-                gemm_single(mem, nb, nb, tk, 1.0, Rn, ld, True, Rn, ld, True, 1.0, tile(n_, n_), ld, 1)
-                if k - 1 - n_ > 0:
-                    gemm_single(mem, nb, nb, tk, 1.0, Rn + te, ld, True, Rn, ld, True, 1.0, tile(n_ + 1, n_), ld, 0, k - 1 - n_,
-                                te, 0, te, nb)
-            gemm_single(mem, tk, nb, tk, 1.0, W, ld, True, Wp, ld, True, 0.0, tile(k, 0), ld, 0, k, 0, te, cs, tk)
-        gemm_single(mem, tk, tk, tk, 1.0, W, ld, True, W, ld, True, 0.0, tile(k, k), ld, 1)
+            transpose_tiles(tile(k, 0), cs, Wp, te, tk, nb, k)
+            trailing_update(k, Wp, te, Wp, te, 0, k, 1.0, tk)
+            gemm_single(mem, tk, nb, tk, 1.0, W2, ld, False, Wp, ld, False, 0.0, tile(k, 0), ld, 0, k, 0, te, cs, tk)
+        gemm_single(mem, tk, tk, tk, 1.0, W2, ld, False, W2, ld, False, 0.0, tile(k, k), ld, 1)
     got2 = np.zeros((N, N))
     for j in range(nt):
         for i in range(nt):
