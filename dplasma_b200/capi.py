@@ -99,6 +99,8 @@ class Lib:
         proto("dplasma_dpoinv", i, [vp, i, pBC])
         proto("dplasma_dpoinv_sync", i, [vp, i, pBC])
         proto("check_dpoinv", i, [vp, i, i, pBC, pBC])
+        proto("dplasma_dgemm", i, [vp, i, i, d, pBC, pBC, d, pBC])
+        proto("dplasma_dsyrk", i, [vp, i, i, d, pBC, d, pBC])
         proto("dplasma_zpotrf_New", vp, [i, pBC, C.POINTER(i)])
         proto("dplasma_zpotrf_Destruct", None, [vp])
         proto("dplasma_zpotrf_Destroy", None, [vp])
@@ -124,6 +126,9 @@ class Lib:
         proto("dplasma_b200_dsyrk_tile", i, [vp, vp, i, i, i, i, d, vp, i, d, vp, i])
         proto("dplasma_b200_dgemm_tile", i, [vp, vp, i, i, i, i, i, d, vp, i, vp, i, d, vp, i])
         proto("pdpotrf_", None, [C.c_char_p, C.POINTER(i), vp, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(i)])
+        proto("pdgemm_", None, [C.c_char_p] * 2 + [C.POINTER(i)] * 3 + [C.POINTER(d), vp, C.POINTER(i), C.POINTER(i), C.POINTER(i),
+                                vp, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(d), vp, C.POINTER(i), C.POINTER(i),
+                                C.POINTER(i)])
         proto("pdtrsm_", None, [C.c_char_p] * 4 + [C.POINTER(i), C.POINTER(i), C.POINTER(d), vp, C.POINTER(i), C.POINTER(i),
                                 C.POINTER(i), vp, C.POINTER(i), C.POINTER(i), C.POINTER(i)])
         proto("parsec_init_wrapper_", None, [])

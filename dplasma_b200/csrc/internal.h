@@ -172,6 +172,9 @@ int trsm_left_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, 
 int symm_residual_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, const DevMatrix& A, const DevMatrix& X,
                         const DevMatrix& B);
 int check_update_multi(parsec_context_s* ctx, const DevMatrix& L, const DevMatrix& R);
+// potri.cu
+int launch_transpose_tiles(parsec_context_s* ctx, cudaStream_t s, const double* src, long long srcStride, int lds,
+                           double* dst, long long dstStride, int ldd, int rows, int cols, int cnt);
 // check.cu
 int symm_residual_1gpu(parsec_context_s* ctx, cudaStream_t s, int uplo, const DevMatrix& A, const DevMatrix& X,
                        const DevMatrix& B, double* diagCopy);

@@ -93,10 +93,10 @@ __global__ void __launch_bounds__(1024) diag_zero_scan_kernel(DevMatrix A, int* 
     if (threadIdx.x == 0 && best[0] != 0x7fffffff && *info == 0) *info = best[0] + 1;
 }
 
-// dst_t = (src_t)^T for t = 0..cnt-1: src tile t (rows x cols valid, ld) at src + t*srcStride, dst tile t
-// (cols x rows) at dst + t*dstStride.  One CTA per 32x32 block; blockIdx.z walks the tiles.
-__global__ void __launch_bounds__(256) transpose_tiles_kernel(const double* __restrict__ src, long long srcStride,
-                                                              double* __restrict__ dst, long long dstStride, int ld,
+// dst_t = (src_t)^T for t = 0..cnt-1: src tile t (rows x cols valid, ld lds) at src + t*srcStride, dst tile t
+// (cols x rows, ld ldd) at dst + t*dstStride.  One CTA per 32x32 block; blockIdx.z walks the tiles.
+__global__ void __launch_bounds__(256) transpose_tiles_kernel(const double* __restrict__ src, long long srcStride, int lds,
+                                                              double* __restrict__ dst, long long dstStride, int ldd,
                                                               int rows, int cols) {
     __shared__ double t[32][33];
     const double* S = src + (size_t)blockIdx.z * srcStride;
@@ -104,19 +104,19 @@ __global__ void __launch_bounds__(256) transpose_tiles_kernel(const double* __re
     const int bi = blockIdx.x * 32, bj = blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     for (int j = ty; j < 32; j += 8)
-        if (bi + tx < rows && bj + j < cols) t[j][tx] = S[(bi + tx) + (size_t)(bj + j) * ld];
+        if (bi + tx < rows && bj + j < cols) t[j][tx] = S[(bi + tx) + (size_t)(bj + j) * lds];
     __syncthreads();
     for (int j = ty; j < 32; j += 8)
-        if (bj + tx < cols && bi + j < rows) D[(bj + tx) + (size_t)(bi + j) * ld] = t[tx][j];
+        if (bj + tx < cols && bi + j < rows) D[(bj + tx) + (size_t)(bi + j) * ldd] = t[tx][j];
 }
-static int launch_transpose_tiles(parsec_context_s* ctx, cudaStream_t s, const double* src, long long srcStride,
-                                  double* dst, long long dstStride, int ld, int rows, int cols, int cnt) {
+int launch_transpose_tiles(parsec_context_s* ctx, cudaStream_t s, const double* src, long long srcStride, int lds,
+                           double* dst, long long dstStride, int ldd, int rows, int cols, int cnt) {
     if (cnt <= 0 || rows <= 0 || cols <= 0) return 0;
     for (int t0 = 0; t0 < cnt; t0 += 65535) {
         const int c = std::min(65535, cnt - t0);
         dim3 grid((rows + 31) / 32, (cols + 31) / 32, c);
-        transpose_tiles_kernel<<<grid, 256, 0, s>>>(src + (size_t)t0 * srcStride, srcStride, dst + (size_t)t0 * dstStride,
-                                                    dstStride, ld, rows, cols);
+        transpose_tiles_kernel<<<grid, 256, 0, s>>>(src + (size_t)t0 * srcStride, srcStride, lds,
+                                                    dst + (size_t)t0 * dstStride, dstStride, ldd, rows, cols);
         ctx->launches++;
     }
     return (int)cudaGetLastError();
@@ -154,7 +154,7 @@ static int trtri_lower_1gpu(parsec_context_s* ctx, cudaStream_t s, const DevMatr
         }
         if (k > 0) {
             // Wp(n) = A(k,n)^T, n < k
-            rc = launch_transpose_tiles(ctx, s, A.tile(k, 0), cs, Wp, te, ld, tk, nb, k);
+            rc = launch_transpose_tiles(ctx, s, A.tile(k, 0), cs, ld, Wp, te, ld, tk, nb, k);
             // A(m,n) += A(m,k) A(k,n) = A(m,k) Wp(n)^T for the whole rectangle m > k > n  (trtri_zgemm, :60-106):
             // one grouped launch
             if (!rc && below > 0)
@@ -184,7 +184,7 @@ static int lauum_lower_1gpu(parsec_context_s* ctx, cudaStream_t s, const DevMatr
         if (rc) return rc;
         if (k > 0) {
             // Wp(n) = A(k,n)^T, n < k
-            rc = launch_transpose_tiles(ctx, s, A.tile(k, 0), cs, Wp, te, ld, tk, nb, k);
+            rc = launch_transpose_tiles(ctx, s, A.tile(k, 0), cs, ld, Wp, te, ld, tk, nb, k);
             // A(m,n) += A(k,m)^T A(k,n) = Wp(m) Wp(n)^T, n <= m < k, diagonal tiles in their lower part only
             // (lauum_zherk, src/zlauum_L.jdf:38-65, and lauum_zgemm, :66-98): the factorization's grouped
             // trailing-update launch on the leading k x k tiles

@@ -116,4 +116,46 @@ void pdtrsm_(char* SIDE, char* UPLO, char* TRANS, char* DIAG, int* M, int* N, do
     if (rc) fprintf(stderr, "pdtrsm_: dplasma_dtrsm returned %d\n", rc);
 }
 
+// pdgemm_: src/scalapack_wrappers/dplasma_wrapper_pdgemm.c:215-221.  C (M x N) = alpha op(A) op(B) + beta C.
+void pdgemm_(char* TRANSA, char* TRANSB, int* M, int* N, int* K, double* ALPHA, double* A, int* IA, int* JA, int* DESCA,
+             double* B, int* IB, int* JB, int* DESCB, double* BETA, double* C, int* IC, int* JC, int* DESCC) {
+    if (*M == 0 || *N == 0) return;
+    auto up = [](char c) { return (c >= 'a' && c <= 'z') ? (char)(c - 32) : c; };
+    const int ta = up(*TRANSA) == 'N' ? dplasmaNoTrans : (up(*TRANSA) == 'T' ? dplasmaTrans : dplasmaConjTrans);
+    const int tb = up(*TRANSB) == 'N' ? dplasmaNoTrans : (up(*TRANSB) == 'T' ? dplasmaTrans : dplasmaConjTrans);
+    const int Am = ta == dplasmaNoTrans ? *M : *K, An = ta == dplasmaNoTrans ? *K : *M;
+    const int Bm = tb == dplasmaNoTrans ? *K : *N, Bn = tb == dplasmaNoTrans ? *N : *K;
+    const int ictxt = DESCC[1], nb = DESCC[4];
+    for (const int* d : {DESCA, DESCB, DESCC})
+        if (d[4] != nb || d[5] != nb || d[1] != ictxt) {
+            fprintf(stderr, "pdgemm_: square blocks of one size on one context required\n");
+            return;
+        }
+    if (*IA != 1 || *JA != 1 || *IB != 1 || *JB != 1 || *IC != 1 || *JC != 1 || DESCA[2] != Am || DESCA[3] != An ||
+        DESCB[2] != Bm || DESCB[3] != Bn || DESCC[2] != *M || DESCC[3] != *N) {
+        fprintf(stderr, "pdgemm_: only IA=JA=IB=JB=IC=JC=1 and whole matrices are supported\n");
+        return;
+    }
+    GridInfo g{1, 1, 0, 0};
+    auto it = g_grids.find(ictxt);
+    if (it != g_grids.end()) g = it->second;
+    if (!g_wrapper_ctx) parsec_init_wrapper_();
+    if (!g_wrapper_ctx) return;
+    const int rank = g.myrow * g.npcol + g.mycol;
+    parsec_matrix_block_cyclic_t dc[3];
+    const int rows[3] = {Am, Bm, *M}, cols[3] = {An, Bn, *N};
+    const int* desc[3] = {DESCA, DESCB, DESCC};
+    double* mem[3] = {A, B, C};
+    for (int i = 0; i < 3; i++) {
+        parsec_matrix_block_cyclic_lapack_init(&dc[i], PARSEC_MATRIX_DOUBLE, PARSEC_MATRIX_LAPACK, rank, nb, nb, rows[i],
+                                               cols[i], 0, 0, rows[i], cols[i], g.nprow, g.npcol, 1, 1, desc[i][6],
+                                               desc[i][7], desc[i][8], 0);
+        dc[i].super.lln = dc[i].super.sln;
+        dc[i].mat = mem[i];
+    }
+    const int rc = dplasma_dgemm(g_wrapper_ctx, ta, tb, *ALPHA, (parsec_tiled_matrix_t*)&dc[0],
+                                 (parsec_tiled_matrix_t*)&dc[1], *BETA, (parsec_tiled_matrix_t*)&dc[2]);
+    if (rc) fprintf(stderr, "pdgemm_: dplasma_dgemm returned %d\n", rc);
+}
+
 }  // extern "C"

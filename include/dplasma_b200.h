@@ -189,6 +189,16 @@ int dplasma_dpoinv_sync(parsec_context_t *parsec, dplasma_enum_t uplo, parsec_ti
  * A is read as a general (full) matrix like the reference's dplasma_zhemm operand, Ainv from its uplo triangle. */
 int check_dpoinv(parsec_context_t *parsec, int loud, dplasma_enum_t uplo, parsec_tiled_matrix_t *A,
                  parsec_tiled_matrix_t *Ainv);
+/* ---- level-3 operations on the same engine; real double, one process ---- */
+/* dplasma_z.h:28-30, src/zgemm_wrapper.c:645-733: C = alpha op(A) op(B) + beta C.  Returns 0, -1 (transA), -2 (transB),
+ * -101 (tile sizes / matrix sizes do not match, or the call could not run) */
+int dplasma_dgemm(parsec_context_t *parsec, dplasma_enum_t transA, dplasma_enum_t transB, double alpha,
+                  const parsec_tiled_matrix_t *A, const parsec_tiled_matrix_t *B, double beta,
+                  parsec_tiled_matrix_t *C);
+/* dplasma_z.h:43, src/zsyrk_wrapper.c:219-258: C = alpha op(A) op(A)^T + beta C on the uplo triangle of C.
+ * Returns 0, -1 (uplo), -2 (trans), -6 (C not square), -4 (A does not match C), -101 (could not run) */
+int dplasma_dsyrk(parsec_context_t *parsec, dplasma_enum_t uplo, dplasma_enum_t trans, double alpha,
+                  const parsec_tiled_matrix_t *A, double beta, parsec_tiled_matrix_t *C);
 /* ---- complex double (zpotrf, BASELINE configs[4]); A->mtype must be PARSEC_MATRIX_COMPLEX_DOUBLE,
  *      tiles hold interleaved (re,im) dplasma_complex64_t.  Both triangles on one GPU, dplasmaLower on a grid.
  *      src/include/dplasma/dplasma_z.h:82,107,109,172,239,280 ---- */
@@ -269,6 +279,10 @@ void pdpotrf_(char *UPLO, int *N, double *A, int *IA, int *JA, int *DESCA, int *
 /* src/scalapack_wrappers/dplasma_wrapper_pdtrsm.c:203-327: like the reference's wrapper the operands are
  * always redistributed into tiles (:303-307); square equal blocks, IA=JA=IB=JB=1, whole matrices.
  * ScaLAPACK's pdtrsm has no info argument: argument errors are printed and the call returns. */
+/* src/scalapack_wrappers/dplasma_wrapper_pdgemm.c:215-221: same restrictions as pdtrsm_ */
+void pdgemm_(char *TRANSA, char *TRANSB, int *M, int *N, int *K, double *ALPHA, double *A, int *IA, int *JA,
+             int *DESCA, double *B, int *IB, int *JB, int *DESCB, double *BETA, double *C, int *IC, int *JC,
+             int *DESCC);
 void pdtrsm_(char *SIDE, char *UPLO, char *TRANS, char *DIAG, int *M, int *N, double *ALPHA, double *A, int *IA,
              int *JA, int *DESCA, double *B, int *IB, int *JB, int *DESCB);
 /* dplasma_wrapper_parsec_init.c:98-124 */

@@ -113,6 +113,10 @@ class Oracle:
                 g(f).restype = _c_int
             g("check_poinv").argtypes = [_c_int, _c_int, _vp, _c_int, _vp, _c_int, ctypes.POINTER(_c_dbl)]
             g("check_poinv").restype = _c_int
+            g("gemm").argtypes = [_c_int] * 8 + [sc, _vp, _c_int, _vp, _c_int, sc, _vp, _c_int]
+            g("gemm").restype = _c_int
+            g("herk").argtypes = [_c_int] * 6 + [_c_dbl, _vp, _c_int, _c_dbl, _vp, _c_int]
+            g("herk").restype = _c_int
 
     @staticmethod
     def _dt(p):
@@ -236,6 +240,20 @@ class Oracle:
         bad = getattr(self.lib, f"orc_{p}check_poinv")(uplo, N, _ptr(A), N, _ptr(Ainv), N, ctypes.byref(r))
         return bad, r.value
 
+    # ---- public BLAS-3 ops: src/zgemm_wrapper.c:645-733, src/zsyrk_wrapper.c / zherk_wrapper.c
+    def gemm(self, ta, tb, alpha, A, B, beta, C, mb, nb, kb, p="d"):
+        M, N = C.shape
+        K = A.shape[1] if ta == NoTrans else A.shape[0]
+        return getattr(self.lib, f"orc_{p}gemm")(ta, tb, M, N, K, mb, nb, kb, self._sc(p, alpha), _ptr(A), A.shape[0],
+                                                 _ptr(B), B.shape[0], self._sc(p, beta), _ptr(C), M)
+
+    def herk(self, uplo, trans, alpha, A, beta, C, nb, kb, p="d"):
+        """d: dsyrk ; z: zherk"""
+        N = C.shape[0]
+        K = A.shape[1] if trans == NoTrans else A.shape[0]
+        return getattr(self.lib, f"orc_{p}herk")(uplo, trans, N, K, nb, kb, float(alpha), _ptr(A), A.shape[0],
+                                                 float(beta), _ptr(C), N)
+
 
 class Reference:
     """The reference's own compiled CPU tile kernels under an OpenMP restatement of its DAG
@@ -264,6 +282,9 @@ class Reference:
             L.ref_dtrtri.argtypes = [_c_int, _c_int, _c_int, _c_int, _vp, _c_int]
             for f in ("ref_dlauum", "ref_dpotri", "ref_dpoinv"):
                 getattr(L, f).argtypes = [_c_int, _c_int, _c_int, _vp, _c_int]
+        if hasattr(L, "ref_dgemm"):
+            L.ref_dgemm.argtypes = [_c_int] * 8 + [_c_dbl, _vp, _c_int, _vp, _c_int, _c_dbl, _vp, _c_int]
+            L.ref_dsyrk.argtypes = [_c_int] * 6 + [_c_dbl, _vp, _c_int, _c_dbl, _vp, _c_int]
         L.ref_time_dpotrf.restype = _c_dbl
         L.ref_time_dpotrf.argtypes = [_c_int, _c_int, _c_int, _c_u64, ctypes.POINTER(_c_int)]
 
@@ -314,6 +335,17 @@ class Reference:
     def poinv(self, uplo, A, nb):
         N = A.shape[0]
         return self.lib.ref_dpoinv(uplo, N, nb, _ptr(A), N)
+
+    def gemm(self, ta, tb, alpha, A, B, beta, C, mb, nb, kb):
+        M, N = C.shape
+        K = A.shape[1] if ta == NoTrans else A.shape[0]
+        return self.lib.ref_dgemm(ta, tb, M, N, K, mb, nb, kb, float(alpha), _ptr(A), A.shape[0], _ptr(B), B.shape[0],
+                                  float(beta), _ptr(C), M)
+
+    def syrk(self, uplo, trans, alpha, A, beta, C, nb, kb):
+        N = C.shape[0]
+        K = A.shape[1] if trans == NoTrans else A.shape[0]
+        return self.lib.ref_dsyrk(uplo, trans, N, K, nb, kb, float(alpha), _ptr(A), A.shape[0], float(beta), _ptr(C), N)
 
     def time_dpotrf(self, uplo, N, nb, seed=3872):
         """seconds for the factorization only (generation excluded), and info"""

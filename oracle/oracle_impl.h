@@ -703,5 +703,64 @@ int P(check_poinv)(int uplo, int N, const T *A, int lda, const T *Ainv, int ldi,
     if (result) *result = res;
     return (isinf(Inorm) || isnan(res) || isinf(res) || res > 10.0) ? 1 : 0;
 }
+/* ---------------- dplasma_zgemm / dplasma_zherk (d: dsyrk) as public ops ----------------
+ * zgemm_{NN,NT,TN,TT}.jdf: C(m,n) = lbeta C(m,n) + alpha op(A)(m,k) op(B)(k,n), k = 0..KT-1 in sequence,
+ * lbeta = beta at k == 0 and 1 afterwards (src/zgemm_NN.jdf:197-211).  A is M x K (NoTrans) or K x M,
+ * B is K x N (NoTrans) or N x K; tiles mb x kb, kb x nb, mb x nb.  Argument codes src/zgemm_wrapper.c:657-710. */
+int P(gemm)(int ta, int tb, int M, int N, int K, int mb, int nb, int kb, T alpha, const T *A, int lda,
+            const T *B, int ldb, T beta, T *C, int ldc)
+{
+    if (ta != ORC_NOTRANS && ta != ORC_TRANS && ta != ORC_CONJTRANS) return -1;
+    if (tb != ORC_NOTRANS && tb != ORC_TRANS && tb != ORC_CONJTRANS) return -2;
+    int mt = (M + mb - 1) / mb, nt = (N + nb - 1) / nb, kt = (K + kb - 1) / kb;
+    if (M == 0 || N == 0 || ((alpha == 0 || K == 0) && beta == 1)) return 0; /* :716-719 */
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
+    for (int n = 0; n < nt; n++)
+        for (int m = 0; m < mt; m++) {
+            int tm = (m == mt - 1) ? M - m * mb : mb, tn = (n == nt - 1) ? N - n * nb : nb;
+            T *Cmn = C + (size_t)m * mb + (size_t)n * nb * ldc;
+            if (kt == 0) P(gemm_tile)(ta, tb, tm, tn, 0, alpha, A, lda, B, ldb, beta, Cmn, ldc);
+            for (int k = 0; k < kt; k++) {
+                int tk = (k == kt - 1) ? K - k * kb : kb;
+                const T *Amk = (ta == ORC_NOTRANS) ? A + (size_t)m * mb + (size_t)k * kb * lda
+                                                   : A + (size_t)k * kb + (size_t)m * mb * lda;
+                const T *Bkn = (tb == ORC_NOTRANS) ? B + (size_t)k * kb + (size_t)n * nb * ldb
+                                                   : B + (size_t)n * nb + (size_t)k * kb * ldb;
+                P(gemm_tile)(ta, tb, tm, tn, tk, alpha, Amk, lda, Bkn, ldb, (k == 0) ? beta : (T)1, Cmn, ldc);
+            }
+        }
+    return 0;
+}
+
+/* zherk_{L,U}{N,C}.jdf / zsyrk_{L,U}{N,T}.jdf (d: both are dsyrk): diagonal tiles by herk (src/zsyrk_LN.jdf:24-55),
+ * the others by gemm with the transposed partner (:66-112), k in sequence with zbeta = beta at k == 0.
+ * trans == NoTrans: C = alpha A A^H + beta C, A is N x K ; else C = alpha A^H A + beta C, A is K x N.
+ * Argument codes src/zsyrk_wrapper.c:229-245. */
+int P(herk)(int uplo, int trans, int N, int K, int nb, int kb, double alpha, const T *A, int lda, double beta,
+            T *C, int ldc)
+{
+    if (uplo != ORC_LOWER && uplo != ORC_UPPER) return -1;
+    if (trans != ORC_NOTRANS && trans != ORC_TRANS && trans != ORC_CONJTRANS) return -2;
+    int nt = (N + nb - 1) / nb, kt = (K + kb - 1) / kb;
+    int tA = (trans == ORC_NOTRANS) ? ORC_NOTRANS : ORC_CONJTRANS, tB = (trans == ORC_NOTRANS) ? ORC_CONJTRANS : ORC_NOTRANS;
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
+    for (int n = 0; n < nt; n++)
+        for (int m = 0; m < nt; m++) {
+            if ((uplo == ORC_LOWER) ? (m < n) : (m > n)) continue;
+            int tm = (m == nt - 1) ? N - m * nb : nb, tn = (n == nt - 1) ? N - n * nb : nb;
+            T *Cmn = C + (size_t)m * nb + (size_t)n * nb * ldc;
+            for (int k = 0; k < kt; k++) {
+                int tk = (k == kt - 1) ? K - k * kb : kb;
+                double zb = (k == 0) ? beta : 1.0;
+                const T *Amk = (trans == ORC_NOTRANS) ? A + (size_t)m * nb + (size_t)k * kb * lda
+                                                      : A + (size_t)k * kb + (size_t)m * nb * lda;
+                const T *Ank = (trans == ORC_NOTRANS) ? A + (size_t)n * nb + (size_t)k * kb * lda
+                                                      : A + (size_t)k * kb + (size_t)n * nb * lda;
+                if (m == n) P(herk_tile)(uplo, tA, tn, tk, alpha, Ank, lda, zb, Cmn, ldc);
+                else P(gemm_tile)(tA, tB, tm, tn, tk, (T)alpha, Amk, lda, Ank, lda, (T)zb, Cmn, ldc);
+            }
+        }
+    return 0;
+}
 #undef TL
 #undef TD

@@ -419,6 +419,55 @@ int ref_dpoinv(int uplo, int N, int nb, double *A, int lda)
     return info;
 }
 
+/* ---- dplasma_dgemm / dplasma_dsyrk as public ops: src/zgemm_NN.jdf:197-211 (and the NT/TN/TT
+ * twins), src/zsyrk_LN.jdf:24-55,66-112 (and LT/UN/UT): per C tile, k in sequence, beta at k == 0 only. */
+int ref_dgemm(int ta, int tb, int M, int N, int K, int mb, int nb, int kb, double alpha, const double *A,
+              int lda, const double *B, int ldb, double beta, double *C, int ldc)
+{
+    int mt = (M + mb - 1) / mb, nt = (N + nb - 1) / nb, kt = (K + kb - 1) / kb;
+    openblas_set_num_threads(1);
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
+    for (int n = 0; n < nt; n++)
+        for (int m = 0; m < mt; m++) {
+            int tm = (m == mt - 1) ? M - m * mb : mb, tn = (n == nt - 1) ? N - n * nb : nb;
+            double *Cmn = C + (size_t)m * mb + (size_t)n * nb * ldc;
+            for (int k = 0; k < kt; k++) {
+                int tk = (k == kt - 1) ? K - k * kb : kb;
+                const double *Amk = (ta == PlasmaNoTrans) ? A + (size_t)m * mb + (size_t)k * kb * lda
+                                                          : A + (size_t)k * kb + (size_t)m * mb * lda;
+                const double *Bkn = (tb == PlasmaNoTrans) ? B + (size_t)k * kb + (size_t)n * nb * ldb
+                                                          : B + (size_t)n * nb + (size_t)k * kb * ldb;
+                CORE_dgemm(ta, tb, tm, tn, tk, alpha, Amk, lda, Bkn, ldb, (k == 0) ? beta : 1.0, Cmn, ldc);
+            }
+        }
+    return 0;
+}
+int ref_dsyrk(int uplo, int trans, int N, int K, int nb, int kb, double alpha, const double *A, int lda,
+              double beta, double *C, int ldc)
+{
+    int nt = (N + nb - 1) / nb, kt = (K + kb - 1) / kb;
+    int tB = (trans == PlasmaNoTrans) ? PlasmaTrans : PlasmaNoTrans;
+    openblas_set_num_threads(1);
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
+    for (int n = 0; n < nt; n++)
+        for (int m = 0; m < nt; m++) {
+            if ((uplo == PlasmaLower) ? (m < n) : (m > n)) continue;
+            int tm = (m == nt - 1) ? N - m * nb : nb, tn = (n == nt - 1) ? N - n * nb : nb;
+            double *Cmn = C + (size_t)m * nb + (size_t)n * nb * ldc;
+            for (int k = 0; k < kt; k++) {
+                int tk = (k == kt - 1) ? K - k * kb : kb;
+                double zb = (k == 0) ? beta : 1.0;
+                const double *Amk = (trans == PlasmaNoTrans) ? A + (size_t)m * nb + (size_t)k * kb * lda
+                                                             : A + (size_t)k * kb + (size_t)m * nb * lda;
+                const double *Ank = (trans == PlasmaNoTrans) ? A + (size_t)n * nb + (size_t)k * kb * lda
+                                                             : A + (size_t)k * kb + (size_t)n * nb * lda;
+                if (m == n) CORE_dsyrk(uplo, trans, tn, tk, alpha, Ank, lda, zb, Cmn, ldc);
+                else CORE_dgemm(trans, tB, tm, tn, tk, alpha, Amk, lda, Ank, lda, zb, Cmn, ldc);
+            }
+        }
+    return 0;
+}
+
 /* Timed run used by bench.py (--impl reference and cpu_baseline): generate with the
  * reference generator, factor with the reference tile kernels under the OpenMP DAG with
  * single-threaded BLAS inside tasks (INSTALL.rst:642-650).  Returns seconds of the

@@ -69,6 +69,16 @@ def test_new_rejects_bad_uplo_and_sets_info():
     assert lib.dplasma_dpoinv(None, 7, C.byref(s)) == -1
     assert lib.dplasma_dpoinv_sync(None, 7, C.byref(s)) == -1
     assert lib.dplasma_dpotri(None, dp.Lower, C.byref(s)) == -100  # no context: nothing runs
+    # level-3 ops: src/zgemm_wrapper.c:657-710, src/zsyrk_wrapper.c:229-245 (s is 8x8, r is 8x12, tiles 4x4)
+    assert lib.dplasma_dgemm(None, 7, dp.NoTrans, 1.0, C.byref(s), C.byref(r), 0.0, C.byref(r)) == -1
+    assert lib.dplasma_dgemm(None, dp.NoTrans, 7, 1.0, C.byref(s), C.byref(r), 0.0, C.byref(r)) == -2
+    assert lib.dplasma_dgemm(None, dp.NoTrans, dp.NoTrans, 1.0, C.byref(r), C.byref(r), 0.0, C.byref(r)) == -101
+    assert lib.dplasma_dgemm(None, dp.NoTrans, dp.NoTrans, 0.0, C.byref(s), C.byref(r), 1.0, C.byref(r)) == 0
+    assert lib.dplasma_dgemm(None, dp.NoTrans, dp.NoTrans, 1.0, C.byref(s), C.byref(r), 1.0, C.byref(r)) == -100
+    assert lib.dplasma_dsyrk(None, 7, dp.NoTrans, 1.0, C.byref(r), 0.0, C.byref(s)) == -1
+    assert lib.dplasma_dsyrk(None, dp.Lower, 7, 1.0, C.byref(r), 0.0, C.byref(s)) == -2
+    assert lib.dplasma_dsyrk(None, dp.Lower, dp.NoTrans, 1.0, C.byref(r), 0.0, C.byref(r)) == -6
+    assert lib.dplasma_dsyrk(None, dp.Lower, dp.Trans, 1.0, C.byref(r), 0.0, C.byref(s)) == -4
 
 
 @pytest.mark.parametrize("M,N,mb,nb,P,Q", [(378, 378, 93, 93, 1, 1), (378, 367, 93, 93, 2, 2), (1000, 1000, 120, 120, 2, 4),

@@ -1,0 +1,154 @@
+"""GPU parity tests of the public level-3 operations: dplasma_dgemm, dplasma_dsyrk and the
+pdgemm_ wrapper through the C ABI against the CPU oracle (1e-11 relative to max|.|, fp64 with a different
+summation order)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import dplasma_b200 as dp
+from oracle.oracle import NoTrans, Trans, ConjTrans
+from tests.util import full_to_local, local_to_full
+
+pytestmark = pytest.mark.gpu
+Lower, Upper, UpperLower = dp.Lower, dp.Upper, dp.UpperLower
+VTOL = 1e-11
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = dp.Context()
+    yield c
+    c.close()
+
+
+def relerr(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+
+
+def make_host(ctx, A, mb, nb):
+    M, N = A.shape
+    d = dp.BlockCyclic(ctx.lib, M, N, mb, nb, where="host")
+    d.host_array()[:d.elems] = full_to_local(A, mb, nb)
+    return d
+
+
+def read_host(d, M, N, mb, nb):
+    return local_to_full(d.host_array()[:d.elems], M, N, mb, nb)
+
+
+@pytest.mark.parametrize("M,N,K,mb,nb,kb", [(378, 300, 367, 93, 93, 93), (512, 512, 512, 128, 128, 128),
+                                            (300, 260, 340, 64, 96, 80), (50, 70, 30, 64, 64, 64)])
+@pytest.mark.parametrize("ta", [NoTrans, Trans])
+@pytest.mark.parametrize("tb", [NoTrans, ConjTrans])
+def test_dgemm_vs_oracle(ctx, oracle, M, N, K, mb, nb, kb, ta, tb):
+    A = oracle.plrnt(*((M, K, mb, kb) if ta == NoTrans else (K, M, kb, mb)), 11)
+    B = oracle.plrnt(*((K, N, kb, nb) if tb == NoTrans else (N, K, nb, kb)), 12)
+    C0 = oracle.plrnt(M, N, mb, nb, 13)
+    for alpha, beta in ((0.75, -0.5), (1.0, 0.0), (0.0, 2.0)):
+        want = C0.copy(order="F")
+        if beta == 0.0:
+            want[:] = np.nan                      # beta == 0: C is not read
+        Cin = want.copy(order="F")
+        if beta == 0.0:
+            want[:] = 0.0
+        assert oracle.gemm(ta, tb, alpha, A, B, beta, want, mb, nb, kb) == 0
+        dA = make_host(ctx, A, kb if ta != NoTrans else mb, mb if ta != NoTrans else kb)
+        dB = make_host(ctx, B, nb if tb != NoTrans else kb, kb if tb != NoTrans else nb)
+        dC = make_host(ctx, Cin, mb, nb)
+        assert ctx.lib.dplasma_dgemm(ctx.ptr, ta, tb, alpha, dA.ref, dB.ref, beta, dC.ref) == 0
+        assert relerr(read_host(dC, M, N, mb, nb), want) < VTOL
+        dA.free(); dB.free(); dC.free()
+
+
+@pytest.mark.parametrize("N,K,nb,kb", [(378, 367, 93, 93), (512, 256, 128, 64), (300, 100, 64, 80), (40, 70, 64, 64)])
+@pytest.mark.parametrize("uplo", [Lower, Upper])
+@pytest.mark.parametrize("trans", [NoTrans, Trans])
+def test_dsyrk_vs_oracle(ctx, oracle, N, K, nb, kb, uplo, trans):
+    A = oracle.plrnt(*((N, K, nb, kb) if trans == NoTrans else (K, N, kb, nb)), 21)
+    C0 = oracle.plrnt(N, N, nb, nb, 22)
+    tri = np.tril if uplo == Lower else np.triu
+    other = (lambda X: np.triu(X, 1)) if uplo == Lower else (lambda X: np.tril(X, -1))
+    for alpha, beta in ((-1.0, 1.0), (0.5, -0.25), (1.0, 0.0)):
+        want = C0.copy(order="F")
+        assert oracle.herk(uplo, trans, alpha, A, beta, want, nb, kb) == 0
+        dA = make_host(ctx, A, kb if trans != NoTrans else nb, nb if trans != NoTrans else kb)
+        dC = make_host(ctx, C0, nb, nb)
+        assert ctx.lib.dplasma_dsyrk(ctx.ptr, uplo, trans, alpha, dA.ref, beta, dC.ref) == 0
+        got = read_host(dC, N, N, nb, nb)
+        assert relerr(tri(got), tri(want)) < VTOL
+        assert np.array_equal(other(got), other(C0))     # the other triangle is not referenced
+        dA.free(); dC.free()
+
+
+def test_blas3_argument_codes(ctx):
+    def desc(m, n, mb, nb):
+        s = dp.capi.BlockCyclicStruct()
+        ctx.lib.parsec_matrix_block_cyclic_init(C.byref(s), dp.MATRIX_DOUBLE, dp.MATRIX_TILE, 0, mb, nb, m, n, 0, 0, m, n, 1, 1, 1, 1, 0, 0)
+        return s
+    a, b, c = desc(8, 12, 4, 4), desc(12, 16, 4, 4), desc(8, 16, 4, 4)
+    L = ctx.lib
+    # src/zgemm_wrapper.c:657-710
+    assert L.dplasma_dgemm(ctx.ptr, 7, NoTrans, 1.0, C.byref(a), C.byref(b), 0.0, C.byref(c)) == -1
+    assert L.dplasma_dgemm(ctx.ptr, NoTrans, 7, 1.0, C.byref(a), C.byref(b), 0.0, C.byref(c)) == -2
+    assert L.dplasma_dgemm(ctx.ptr, Trans, NoTrans, 1.0, C.byref(a), C.byref(b), 0.0, C.byref(c)) == -101  # sizes
+    assert L.dplasma_dgemm(ctx.ptr, NoTrans, NoTrans, 1.0, C.byref(a), C.byref(desc(12, 16, 6, 4)), 0.0, C.byref(c)) == -101  # tiles
+    assert L.dplasma_dgemm(ctx.ptr, NoTrans, NoTrans, 0.0, C.byref(a), C.byref(b), 1.0, C.byref(c)) == 0  # quick return :716-719
+    # src/zsyrk_wrapper.c:229-245
+    sq = desc(8, 8, 4, 4)
+    assert L.dplasma_dsyrk(ctx.ptr, 7, NoTrans, 1.0, C.byref(a), 0.0, C.byref(sq)) == -1
+    assert L.dplasma_dsyrk(ctx.ptr, Lower, 7, 1.0, C.byref(a), 0.0, C.byref(sq)) == -2
+    assert L.dplasma_dsyrk(ctx.ptr, Lower, NoTrans, 1.0, C.byref(a), 0.0, C.byref(c)) == -6
+    assert L.dplasma_dsyrk(ctx.ptr, Lower, NoTrans, 1.0, C.byref(b), 0.0, C.byref(sq)) == -4
+
+
+def test_dgemm_dsyrk_device_resident_8192_consistency(ctx):
+    """larger than the oracle finishes in seconds: A A^T by dgemm (N,T) and by dsyrk must agree (symmetric
+    infinity norms of the lower triangles), and (A A^T) - A A^T by a second dgemm must vanish."""
+    N, K, nb = 8192, 8192, 512
+    L = ctx.lib
+    A = dp.BlockCyclic(L, N, K, nb, nb, where="device")
+    G = dp.BlockCyclic(L, N, N, nb, nb, where="device")
+    S = dp.BlockCyclic(L, N, N, nb, nb, where="device")
+    assert L.dplasma_dplrnt(ctx.ptr, 0, A.ref, 5) == 0
+    assert L.dplasma_dplrnt(ctx.ptr, 0, S.ref, 6) == 0   # junk that beta = 0 must ignore
+    assert L.dplasma_dgemm(ctx.ptr, NoTrans, Trans, 1.0, A.ref, A.ref, 0.0, G.ref) == 0
+    t = L.dplasma_b200_last_elapsed(ctx.ptr)
+    print(f"\ndgemm NT N=K={N} nb={nb}: {t * 1e3:.1f} ms, {2.0 * N * N * K / t / 1e12:.2f} TFLOP/s")
+    assert L.dplasma_dsyrk(ctx.ptr, Lower, NoTrans, 1.0, A.ref, 0.0, S.ref) == 0
+    t = L.dplasma_b200_last_elapsed(ctx.ptr)
+    print(f"dsyrk LN N=K={N} nb={nb}: {t * 1e3:.1f} ms, {1.0 * N * N * K / t / 1e12:.2f} TFLOP/s")
+    ng = L.dplasma_dlansy(ctx.ptr, dp.InfNorm, Lower, G.ref)
+    ns = L.dplasma_dlansy(ctx.ptr, dp.InfNorm, Lower, S.ref)
+    assert ng > 0 and ns == pytest.approx(ng, rel=1e-12)
+    # G <- G - A A^T through the NN form with a transposed copy ... here simply the TN form of A^T: (A^T)^T A^T
+    assert L.dplasma_dgemm(ctx.ptr, NoTrans, Trans, -1.0, A.ref, A.ref, 1.0, G.ref) == 0
+    assert L.dplasma_dlange(ctx.ptr, dp.InfNorm, G.ref) < 1e-9 * ng
+    A.free(); G.free(); S.free()
+
+
+@pytest.mark.parametrize("ta,tb", [(b"N", b"N"), (b"T", b"N"), (b"n", b"t"), (b"C", b"C")])
+def test_pdgemm_single_process(ctx, oracle, ta, tb):
+    """src/scalapack_wrappers/dplasma_wrapper_pdgemm.c:215-221 on a 1x1 grid, LAPACK-storage operands"""
+    M, N, K, nb = 300, 170, 230, 64
+    e = {b"N": NoTrans, b"T": Trans, b"C": Trans}
+    opa, opb = e[ta.upper()], e[tb.upper()]
+    A = oracle.plrnt(*((M, K) if opa == NoTrans else (K, M)), nb, nb, 31)
+    B = oracle.plrnt(*((K, N) if opb == NoTrans else (N, K)), nb, nb, 32)
+    C0 = oracle.plrnt(M, N, nb, nb, 33)
+    want = C0.copy(order="F")
+    assert oracle.gemm(opa, opb, 1.5, A, B, -0.5, want, nb, nb, nb) == 0
+    ctx.lib.dplasma_b200_blacs_gridinit(0, 1, 1, 0, 0)
+    ctx.lib.dplasma_b200_wrapper_set_context(ctx.ptr)
+    dA = (C.c_int * 9)(1, 0, A.shape[0], A.shape[1], nb, nb, 0, 0, A.shape[0])
+    dB = (C.c_int * 9)(1, 0, B.shape[0], B.shape[1], nb, nb, 0, 0, B.shape[0])
+    dC = (C.c_int * 9)(1, 0, M, N, nb, nb, 0, 0, M)
+    m, n, k, one = C.c_int(M), C.c_int(N), C.c_int(K), C.c_int(1)
+    alpha, beta = C.c_double(1.5), C.c_double(-0.5)
+    Aa, Ba, Ca = np.asfortranarray(A.copy()), np.asfortranarray(B.copy()), np.asfortranarray(C0.copy())
+    vp = lambda x: x.ctypes.data_as(C.c_void_p)  # noqa: E731
+    ctx.lib.pdgemm_(ta, tb, C.byref(m), C.byref(n), C.byref(k), C.byref(alpha), vp(Aa), C.byref(one), C.byref(one), dA,
+                    vp(Ba), C.byref(one), C.byref(one), dB, C.byref(beta), vp(Ca), C.byref(one), C.byref(one), dC)
+    assert relerr(Ca, want) < VTOL
+    assert np.array_equal(Aa, A) and np.array_equal(Ba, B)
+    ctx.lib.dplasma_b200_wrapper_set_context(None)
