@@ -101,6 +101,14 @@ class Lib:
         proto("check_dpoinv", i, [vp, i, i, pBC, pBC])
         proto("dplasma_dgemm", i, [vp, i, i, d, pBC, pBC, d, pBC])
         proto("dplasma_dsyrk", i, [vp, i, i, d, pBC, d, pBC])
+        proto("dplasma_dtrsm_New", vp, [i, i, i, i, d, pBC, pBC])
+        proto("dplasma_dtrtri_New", vp, [i, i, pBC, C.POINTER(i)])
+        proto("dplasma_dlauum_New", vp, [i, pBC])
+        proto("dplasma_dpoinv_New", vp, [i, pBC, C.POINTER(i)])
+        proto("dplasma_dgemm_New", vp, [i, i, d, pBC, pBC, d, pBC])
+        proto("dplasma_dsyrk_New", vp, [i, i, d, pBC, d, pBC])
+        for _n in ("trsm", "trtri", "lauum", "poinv", "gemm", "syrk"):
+            proto(f"dplasma_d{_n}_Destruct", None, [vp])
         proto("dplasma_zpotrf_New", vp, [i, pBC, C.POINTER(i)])
         proto("dplasma_zpotrf_Destruct", None, [vp])
         proto("dplasma_zpotrf_Destroy", None, [vp])

@@ -46,7 +46,7 @@ struct NcclApi;  // comm.cu
 
 }  // namespace dpb
 
-enum TaskKind { TP_POTRF = 1 };
+enum TaskKind { TP_POTRF = 1, TP_TRSM, TP_TRTRI, TP_LAUUM, TP_POINV, TP_GEMM, TP_SYRK };
 
 struct parsec_taskpool_s {
     int kind;
@@ -56,6 +56,12 @@ struct parsec_taskpool_s {
     int hmb;
     dpb::DevMatrix dA;
     bool staged;
+    // operands of the other operations (taskpools.cu); A doubles as the first (const) operand
+    int side = 0, trans = 0, trans2 = 0, diag = 0;
+    double alpha = 1.0, beta = 0.0;
+    const parsec_tiled_matrix_t* B = nullptr;
+    parsec_tiled_matrix_t* C = nullptr;
+    bool done = false;  // ran to completion inside parsec_context_start (mixed queues run in order)
 };
 
 struct parsec_context_s {
@@ -84,6 +90,7 @@ struct parsec_context_s {
     parsec_taskpool_s* curTp = nullptr;  // taskpool being enqueued (for early write-back of finished columns)
     int earlyOut = 0;                    // columns of curTp already written back by the copy stream
     std::vector<cudaEvent_t> evIn;       // per local tile column: its host-to-device copy has landed (pipelined stage-in)
+    double seqElapsed = -1.0;  // >= 0: GPU seconds summed over a queue that ran operation by operation
     int cplx = 0;         // set by the drivers while they work on a complex (esz = 2) matrix
     int gemmPreload = 1;  // internal products preload C into the accumulators; the tile seam API does not
     // optional per-kernel profile of the trailing-update launches (bench.py roofline leg)
@@ -173,6 +180,11 @@ int symm_residual_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, const D
                         const DevMatrix& B);
 int check_update_multi(parsec_context_s* ctx, const DevMatrix& L, const DevMatrix& R);
 // potri.cu
+enum { OP_TRTRI = 1, OP_LAUUM = 2, OP_POTRF = 4 };
+int run_inverse_chain(parsec_context_s* ctx, const char* name, int ops, int uplo, int diag, parsec_tiled_matrix_t* A,
+                      int* info_out);
+// taskpools.cu
+int run_queue_in_order(parsec_context_s* ctx);
 int launch_transpose_tiles(parsec_context_s* ctx, cudaStream_t s, const double* src, long long srcStride, int lds,
                            double* dst, long long dstStride, int ldd, int rows, int cols, int cnt);
 // check.cu

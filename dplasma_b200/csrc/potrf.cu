@@ -329,6 +329,9 @@ int parsec_context_add_taskpool(parsec_context_t* ctx, parsec_taskpool_t* tp) {
 int parsec_context_start(parsec_context_t* ctx) {
     if (!ctx) return -1;
     cudaSetDevice(ctx->device);
+    // a queue that holds anything but factorizations runs operation by operation, in order (taskpools.cu)
+    for (parsec_taskpool_s* tp : ctx->queue)
+        if (tp->kind != TP_POTRF) return run_queue_in_order(ctx);
     DPB_CUDA(cudaMemsetAsync(ctx->dInfo, 0, sizeof(int), ctx->sPanel));
     for (cudaEvent_t e : ctx->evIn) cudaEventDestroy(e);
     ctx->evIn.clear();
@@ -389,10 +392,12 @@ int parsec_context_wait(parsec_context_t* ctx) {
     DPB_CUDA(cudaStreamSynchronize(ctx->sUpdate));
     DPB_CUDA(cudaStreamSynchronize(ctx->sCopy));
     float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, ctx->evStart, ctx->evStop) == cudaSuccess) ctx->lastElapsed = ms * 1e-3;
+    if (ctx->seqElapsed >= 0.0) ctx->lastElapsed = ctx->seqElapsed;
+    else if (cudaEventElapsedTime(&ms, ctx->evStart, ctx->evStop) == cudaSuccess) ctx->lastElapsed = ms * 1e-3;
+    ctx->seqElapsed = -1.0;
     dpb::trace_dump();
     for (parsec_taskpool_s* tp : ctx->queue) {
-        if (tp->info && *tp->info == 0) *tp->info = *ctx->hInfo;  // rank-local until the wrapper reduces it
+        if (!tp->done && tp->info && *tp->info == 0) *tp->info = *ctx->hInfo;  // rank-local until the wrapper reduces it
         stage_free(&tp->dA);
     }
     ctx->queue.clear();

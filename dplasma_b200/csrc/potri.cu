@@ -206,18 +206,16 @@ static int lauum_lower_1gpu(parsec_context_s* ctx, cudaStream_t s, const DevMatr
     return 0;
 }
 
-enum { OP_TRTRI = 1, OP_LAUUM = 2, OP_POTRF = 4 };
-
 // stage A, run the requested chain of operations on the GPU, stage the triangle back
-static int run_inverse_chain(parsec_context_s* ctx, const char* name, int ops, int uplo, int diag,
-                             parsec_tiled_matrix_t* A, int* info_out) {
+int run_inverse_chain(parsec_context_s* ctx, const char* name, int ops, int uplo, int diag, parsec_tiled_matrix_t* A,
+                      int* info_out) {
     *info_out = 0;
     if (!ctx) return -100;
     if (A->super.nodes > 1) {
         fprintf(stderr, "%s: not built for a process grid yet (single process only)\n", name);
         return -2;
     }
-    if (A->mtype != PARSEC_MATRIX_DOUBLE) {
+    if (A->mtype != PARSEC_MATRIX_DOUBLE && (ops & (OP_TRTRI | OP_LAUUM))) {
         fprintf(stderr, "%s: only real double precision is built\n", name);
         return -3;
     }
@@ -229,9 +227,10 @@ static int run_inverse_chain(parsec_context_s* ctx, const char* name, int ops, i
     ctx->evIn.clear();
     int rc = stage_in(ctx, A, &dA, true, uplo);
     if (!rc && (dA.mb != dA.nb || dA.mt != dA.nt)) rc = -3;
-    if (!rc && cudaMalloc(&W, (size_t)dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
-    if (!rc && cudaMalloc(&W2, (size_t)dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
-    if (!rc && cudaMalloc(&Wp, (size_t)dA.nt * dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
+    const bool inv = (ops & (OP_TRTRI | OP_LAUUM)) != 0;
+    if (!rc && inv && cudaMalloc(&W, (size_t)dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
+    if (!rc && inv && cudaMalloc(&W2, (size_t)dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
+    if (!rc && inv && cudaMalloc(&Wp, (size_t)dA.nt * dA.tileElems * sizeof(double)) != cudaSuccess) rc = -200;
     if (!rc && cudaMemsetAsync(ctx->dInfo, 0, sizeof(int), s) != cudaSuccess) rc = -201;
     if (!rc) *ctx->hInfo = 0;
     if (!rc) rc = (int)cudaEventRecord(ctx->evStart, s);

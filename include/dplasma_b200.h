@@ -199,6 +199,27 @@ int dplasma_dgemm(parsec_context_t *parsec, dplasma_enum_t transA, dplasma_enum_
  * Returns 0, -1 (uplo), -2 (trans), -6 (C not square), -4 (A does not match C), -101 (could not run) */
 int dplasma_dsyrk(parsec_context_t *parsec, dplasma_enum_t uplo, dplasma_enum_t trans, double alpha,
                   const parsec_tiled_matrix_t *A, double beta, parsec_tiled_matrix_t *C);
+/* ---- taskpool forms of the operations above (dplasma_z.h:125-127,144-146,153-154,170-173,213,219,221,237-240): _New
+ *      records the operation and returns NULL on an illegal argument; a context whose queue holds any of them
+ *      runs the queue operation by operation in the order it was filled (what a composition such as
+ *      src/zpotri_wrapper.c:68-80 needs); _Destruct frees the object ---- */
+parsec_taskpool_t *dplasma_dtrsm_New(dplasma_enum_t side, dplasma_enum_t uplo, dplasma_enum_t trans,
+                                     dplasma_enum_t diag, double alpha, const parsec_tiled_matrix_t *A,
+                                     parsec_tiled_matrix_t *B);
+parsec_taskpool_t *dplasma_dtrtri_New(dplasma_enum_t uplo, dplasma_enum_t diag, parsec_tiled_matrix_t *A, int *info);
+parsec_taskpool_t *dplasma_dlauum_New(dplasma_enum_t uplo, parsec_tiled_matrix_t *A);
+parsec_taskpool_t *dplasma_dpoinv_New(dplasma_enum_t uplo, parsec_tiled_matrix_t *A, int *info);
+parsec_taskpool_t *dplasma_dgemm_New(dplasma_enum_t transA, dplasma_enum_t transB, double alpha,
+                                     const parsec_tiled_matrix_t *A, const parsec_tiled_matrix_t *B, double beta,
+                                     parsec_tiled_matrix_t *C);
+parsec_taskpool_t *dplasma_dsyrk_New(dplasma_enum_t uplo, dplasma_enum_t trans, double alpha,
+                                     const parsec_tiled_matrix_t *A, double beta, parsec_tiled_matrix_t *C);
+void dplasma_dtrsm_Destruct(parsec_taskpool_t *tp);
+void dplasma_dtrtri_Destruct(parsec_taskpool_t *tp);
+void dplasma_dlauum_Destruct(parsec_taskpool_t *tp);
+void dplasma_dpoinv_Destruct(parsec_taskpool_t *tp);
+void dplasma_dgemm_Destruct(parsec_taskpool_t *tp);
+void dplasma_dsyrk_Destruct(parsec_taskpool_t *tp);
 /* ---- complex double (zpotrf, BASELINE configs[4]); A->mtype must be PARSEC_MATRIX_COMPLEX_DOUBLE,
  *      tiles hold interleaved (re,im) dplasma_complex64_t.  Both triangles on one GPU, dplasmaLower on a grid.
  *      src/include/dplasma/dplasma_z.h:82,107,109,172,239,280 ---- */

@@ -79,6 +79,23 @@ def test_new_rejects_bad_uplo_and_sets_info():
     assert lib.dplasma_dsyrk(None, dp.Lower, 7, 1.0, C.byref(r), 0.0, C.byref(s)) == -2
     assert lib.dplasma_dsyrk(None, dp.Lower, dp.NoTrans, 1.0, C.byref(r), 0.0, C.byref(r)) == -6
     assert lib.dplasma_dsyrk(None, dp.Lower, dp.Trans, 1.0, C.byref(r), 0.0, C.byref(s)) == -4
+    # taskpool forms: NULL on an illegal argument, an object otherwise (nothing runs before parsec_context_start)
+    assert lib.dplasma_dtrsm_New(5, dp.Lower, dp.NoTrans, dp.NonUnit, 1.0, C.byref(s), C.byref(s)) is None
+    assert lib.dplasma_dtrtri_New(dp.Lower, 5, C.byref(s), C.byref(info)) is None
+    assert lib.dplasma_dlauum_New(5, C.byref(s)) is None
+    assert lib.dplasma_dpoinv_New(5, C.byref(s), C.byref(info)) is None
+    assert lib.dplasma_dgemm_New(dp.NoTrans, 5, 1.0, C.byref(s), C.byref(s), 0.0, C.byref(s)) is None
+    assert lib.dplasma_dsyrk_New(dp.Lower, 5, 1.0, C.byref(s), 0.0, C.byref(s)) is None
+    info.value = 9
+    for tp, destruct in ((lib.dplasma_dtrsm_New(dp.Left, dp.Lower, dp.NoTrans, dp.NonUnit, 1.0, C.byref(s), C.byref(s)), lib.dplasma_dtrsm_Destruct),
+                         (lib.dplasma_dtrtri_New(dp.Lower, dp.NonUnit, C.byref(s), C.byref(info)), lib.dplasma_dtrtri_Destruct),
+                         (lib.dplasma_dlauum_New(dp.Upper, C.byref(s)), lib.dplasma_dlauum_Destruct),
+                         (lib.dplasma_dpoinv_New(dp.Upper, C.byref(s), C.byref(info)), lib.dplasma_dpoinv_Destruct),
+                         (lib.dplasma_dgemm_New(dp.NoTrans, dp.Trans, 1.0, C.byref(s), C.byref(s), 0.0, C.byref(s)), lib.dplasma_dgemm_Destruct),
+                         (lib.dplasma_dsyrk_New(dp.Lower, dp.Trans, 1.0, C.byref(s), 0.0, C.byref(s)), lib.dplasma_dsyrk_Destruct)):
+        assert tp
+        destruct(tp)
+    assert info.value == 0
 
 
 @pytest.mark.parametrize("M,N,mb,nb,P,Q", [(378, 378, 93, 93, 1, 1), (378, 367, 93, 93, 2, 2), (1000, 1000, 120, 120, 2, 4),

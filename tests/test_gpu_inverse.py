@@ -237,3 +237,61 @@ def test_pdtrsm_single_process(ctx, oracle, side, uplo, trans, diag):
     assert relerr(Ba, want) < 1e-10
     assert np.array_equal(Ta, T)
     ctx.lib.dplasma_b200_wrapper_set_context(None)
+
+
+def test_taskpool_composition_runs_in_queue_order(ctx, oracle):
+    """src/zpotri_wrapper.c:68-80 (PARSEC_COMPOSITION): several _New taskpools, one start / wait.  Here
+    potrf + trtri + lauum on one matrix, then trsm, gemm and syrk that consume each other's results."""
+    N, nb, K = 378, 93, 200
+    lib = ctx.lib
+    A0 = oracle.plgsy(float(N), Lower, N, nb, SEED_A)
+    want = A0.copy(order="F")
+    assert oracle.poinv(Lower, want, nb) == 0
+    d = make_host(ctx, A0, nb, nb)
+    i1, i2 = C.c_int(-5), C.c_int(-5)
+    tps = [lib.dplasma_dpotrf_New(Lower, d.ref, C.byref(i1)), lib.dplasma_dtrtri_New(Lower, NonUnit, d.ref, C.byref(i2)),
+           lib.dplasma_dlauum_New(Lower, d.ref)]
+    assert all(tps) and i1.value == 0 and i2.value == 0
+    for tp in tps:
+        assert lib.parsec_context_add_taskpool(ctx.ptr, tp) == 0
+    assert lib.parsec_context_start(ctx.ptr) == 0
+    assert lib.parsec_context_wait(ctx.ptr) == 0
+    lib.dplasma_dpotrf_Destruct(tps[0]); lib.dplasma_dtrtri_Destruct(tps[1]); lib.dplasma_dlauum_Destruct(tps[2])
+    assert i1.value == 0 and i2.value == 0
+    assert lib.dplasma_b200_last_elapsed(ctx.ptr) > 0.0
+    got = read_host(d, N, N, nb, nb)
+    assert relerr(np.tril(got), np.tril(want)) < VTOL
+    d.free()
+    # one taskpool that does all three
+    d = make_host(ctx, A0, nb, nb)
+    tp = lib.dplasma_dpoinv_New(Lower, d.ref, C.byref(i1))
+    lib.parsec_context_add_taskpool(ctx.ptr, tp)
+    assert lib.parsec_context_start(ctx.ptr) == 0 and lib.parsec_context_wait(ctx.ptr) == 0
+    lib.dplasma_dpoinv_Destruct(tp)
+    assert i1.value == 0 and relerr(np.tril(read_host(d, N, N, nb, nb)), np.tril(want)) < VTOL
+    d.free()
+    # B <- L^-1 B ; G <- B^T B (gemm) ; S <- B^T B lower (syrk), in one queue
+    _, F = factor(oracle, Lower, N, nb)
+    B = oracle.plrnt(N, K, nb, nb, 7)
+    wB = B.copy(order="F")
+    assert oracle.trsm(Left, Lower, NoTrans, NonUnit, 1.0, F, wB, nb, nb) == 0
+    wG = np.zeros((K, K), order="F")
+    assert oracle.gemm(Trans, NoTrans, 1.0, wB, wB, 0.0, wG, nb, nb, nb) == 0
+    dF, dB = make_host(ctx, F, nb, nb), make_host(ctx, B, nb, nb)
+    dG, dS = make_host(ctx, np.full((K, K), np.nan, order="F"), nb, nb), make_host(ctx, np.zeros((K, K), order="F"), nb, nb)
+    tps = [lib.dplasma_dtrsm_New(Left, Lower, NoTrans, NonUnit, 1.0, dF.ref, dB.ref),
+           lib.dplasma_dgemm_New(Trans, NoTrans, 1.0, dB.ref, dB.ref, 0.0, dG.ref),
+           lib.dplasma_dsyrk_New(Lower, Trans, 1.0, dB.ref, 0.0, dS.ref)]
+    assert all(tps)
+    for tp in tps:
+        lib.parsec_context_add_taskpool(ctx.ptr, tp)
+    assert lib.parsec_context_start(ctx.ptr) == 0 and lib.parsec_context_wait(ctx.ptr) == 0
+    lib.dplasma_dtrsm_Destruct(tps[0]); lib.dplasma_dgemm_Destruct(tps[1]); lib.dplasma_dsyrk_Destruct(tps[2])
+    assert relerr(read_host(dB, N, K, nb, nb), wB) < 1e-10
+    assert relerr(read_host(dG, K, K, nb, nb), wG) < 1e-10
+    assert relerr(np.tril(read_host(dS, K, K, nb, nb)), np.tril(wG)) < 1e-10
+    for x in (dF, dB, dG, dS):
+        x.free()
+    # illegal arguments: NULL (src/ztrtri_wrapper.c:84-92, zgemm_wrapper.c:445-452)
+    assert lib.dplasma_dtrtri_New(7, NonUnit, dF.ref, C.byref(i1)) is None
+    assert lib.dplasma_dgemm_New(7, NoTrans, 1.0, dF.ref, dF.ref, 0.0, dF.ref) is None
