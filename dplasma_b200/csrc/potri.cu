@@ -23,6 +23,8 @@
 #include <algorithm>
 #include "internal.h"
 
+extern "C" int info_allreduce_max(parsec_context_s* ctx, int info);  // comm.cu
+
 namespace dpb {
 
 int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp);
@@ -206,15 +208,101 @@ static int lauum_lower_1gpu(parsec_context_s* ctx, cudaStream_t s, const DevMatr
     return 0;
 }
 
+// local tiles of a matrix distributed over a P x Q grid <- identity
+__global__ void identity_dist_kernel(DevMatrix A) {
+    const long long total = (long long)A.lmt * A.lnt * A.tileElems;
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+         e += (long long)gridDim.x * blockDim.x) {
+        const long long t = e / A.tileElems, r = e % A.tileElems;
+        const int il = (int)(t % A.lmt), jl = (int)(t / A.lmt);
+        const long long gi = (long long)(il * A.P + A.prow) * A.mb + (int)(r % A.mb);
+        const long long gj = (long long)(jl * A.Q + A.pcol) * A.nb + (int)(r / A.mb);
+        A.base[e] = (gi == gj && gi < A.M) ? 1.0 : 0.0;
+    }
+}
+
+// Process grid.  The inverse comes from the distributed triangular solves that dpotrs uses, applied to the
+// identity: op(T) X = I for trtri, and A X = I (two solves with the factor, src/zpotrs_wrapper.c:78-98) for
+// potri; the uplo triangle of X then replaces the factor.  Three times the flops of trtri + lauum, but built
+// only from the grid primitives the parity tests already pin; the panel-broadcast version of the two DAGs
+// replaces it next.  NonUnit only; lauum alone is not built on a grid.
+static int inverse_chain_grid(parsec_context_s* ctx, const char* name, int ops, int uplo, int diag,
+                              parsec_tiled_matrix_t* A, int* info_out) {
+    if (!(ops & OP_TRTRI) || diag != dplasmaNonUnit || A->mtype != PARSEC_MATRIX_DOUBLE) {
+        fprintf(stderr, "%s: on a process grid only the real NonUnit inversion (dtrtri / dpotri / dpoinv) is built\n", name);
+        return -2;
+    }
+    cudaSetDevice(ctx->device);
+    cudaStream_t s = ctx->sPanel;
+    DevMatrix dA, X;
+    for (cudaEvent_t e : ctx->evIn) cudaEventDestroy(e);
+    ctx->evIn.clear();
+    int rc = stage_in(ctx, A, &dA, true, uplo);
+    if (!rc && (dA.mb != dA.nb || dA.mt != dA.nt)) rc = -3;
+    if (!rc && cudaMemsetAsync(ctx->dInfo, 0, sizeof(int), s) != cudaSuccess) rc = -201;
+    if (!rc) *ctx->hInfo = 0;
+    if (!rc) rc = (int)cudaEventRecord(ctx->evStart, s);
+    int info = 0;
+    if (!rc && (ops & OP_POTRF)) {
+        parsec_taskpool_s tp{};
+        tp.kind = TP_POTRF;
+        tp.uplo = uplo;
+        tp.A = A;
+        tp.dA = dA;
+        tp.dA.owned = false;
+        ctx->curTp = nullptr;
+        ctx->earlyOut = -1;
+        rc = potrf_enqueue(ctx, &tp);
+        if (!rc && cudaMemcpyAsync(ctx->hInfo, ctx->dInfo, sizeof(int), cudaMemcpyDeviceToHost, s) != cudaSuccess) rc = -201;
+        if (!rc && cudaStreamSynchronize(s) != cudaSuccess) rc = -202;
+        if (!rc) info = info_allreduce_max(ctx, *ctx->hInfo);  // every rank takes the same branch below
+    }
+    if (!rc && info == 0) {
+        rc = alloc_like(dA, &X);
+        if (!rc) {
+            identity_dist_kernel<<<1184, 256, 0, s>>>(X);
+            ctx->launches++;
+            rc = (int)cudaGetLastError();
+        }
+        if (!rc && (ops & OP_LAUUM)) {
+            // Lower: L Y = I, L^T X = Y ; Upper: U^T Y = I, U X = Y
+            rc = trsm_left_multi(ctx, s, uplo, uplo == dplasmaLower ? dplasmaNoTrans : dplasmaTrans, dplasmaNonUnit, 1.0, dA, X);
+            if (!rc) rc = trsm_left_multi(ctx, s, uplo, uplo == dplasmaLower ? dplasmaTrans : dplasmaNoTrans, dplasmaNonUnit, 1.0, dA, X);
+        } else if (!rc) {
+            rc = trsm_left_multi(ctx, s, uplo, dplasmaNoTrans, dplasmaNonUnit, 1.0, dA, X);
+        }
+        // the uplo triangle of X replaces the factor; the other triangle of A is not touched
+        const int rowEnd = std::min(dA.firstLocalRowGE(dA.mt), dA.lmt), colEnd = std::min(dA.firstLocalColGE(dA.nt), dA.lnt);
+        for (int jl = 0; !rc && jl < colEnd; jl++)
+            for (int il = 0; !rc && il < rowEnd; il++) {
+                const int gm = il * dA.P + dA.prow, gn = jl * dA.Q + dA.pcol;
+                if (gm == gn) rc = launch_copy_tril(ctx, s, X.tile(il, jl), X.mb, dA.tile(il, jl), dA.mb, dA.rowsOfTile(gm), uplo, 2);
+                else if ((uplo == dplasmaLower) ? (gm > gn) : (gm < gn)) {
+                    if (cudaMemcpyAsync(dA.tile(il, jl), X.tile(il, jl), (size_t)dA.tileElems * sizeof(double),
+                                        cudaMemcpyDeviceToDevice, s) != cudaSuccess) rc = -201;
+                }
+            }
+    }
+    if (!rc) rc = (int)cudaEventRecord(ctx->evStop, s);
+    if (!rc) rc = stage_out(ctx, A, &dA, uplo);
+    cudaError_t e = cudaStreamSynchronize(s);
+    float ms = 0.f;
+    if (!rc && cudaEventElapsedTime(&ms, ctx->evStart, ctx->evStop) == cudaSuccess) ctx->lastElapsed = ms * 1e-3;
+    stage_free(&X);
+    stage_free(&dA);
+    if (rc) return rc < 0 ? rc : -1000 - rc;
+    if (e != cudaSuccess) return -1000 - (int)e;
+    *info_out = info;
+    return 0;
+}
+
 // stage A, run the requested chain of operations on the GPU, stage the triangle back
 int run_inverse_chain(parsec_context_s* ctx, const char* name, int ops, int uplo, int diag, parsec_tiled_matrix_t* A,
                       int* info_out) {
     *info_out = 0;
     if (!ctx) return -100;
-    if (A->super.nodes > 1) {
-        fprintf(stderr, "%s: not built for a process grid yet (single process only)\n", name);
-        return -2;
-    }
+    if (A->m == 0 || A->n == 0) return 0;  // LAPACK quick return
+    if (A->super.nodes > 1) return inverse_chain_grid(ctx, name, ops, uplo, diag, A, info_out);
     if (A->mtype != PARSEC_MATRIX_DOUBLE && (ops & (OP_TRTRI | OP_LAUUM))) {
         fprintf(stderr, "%s: only real double precision is built\n", name);
         return -3;
@@ -326,12 +414,13 @@ int dplasma_dpoinv_sync(parsec_context_t* parsec, dplasma_enum_t uplo, parsec_ti
     // src/zpoinv_wrapper.c:255-272: three blocking calls in a row (the reference overwrites the factorization's
     // info with the inversion's, :267-268; here a failed factorization stops the chain and is reported)
     if (uplo != dplasmaUpper && uplo != dplasmaLower) { fprintf(stderr, "dplasma_dpoinv_sync: illegal value of uplo\n"); return -1; }
+    // a process grid has no stand-alone lauum yet: the three steps run as the one chain of dplasma_dpoinv
+    if (A->super.nodes > 1) return dplasma_dpoinv(parsec, uplo, A);
     int info = dplasma_dpotrf(parsec, uplo, A);
     if (info != 0) return info;
     info = dplasma_dtrtri(parsec, uplo, dplasmaNonUnit, A);
     if (info != 0) return info;
-    dplasma_dlauum(parsec, uplo, A);
-    return info;
+    return dplasma_dlauum(parsec, uplo, A);
 }
 
 // ||Id - Ainv A||_1 / (||A||_1 ||Ainv||_1 N eps), Ainv stored in `uplo`, A read as a general matrix

@@ -301,3 +301,70 @@ def nccl_host_potrf_worker(rank, world, port, P, Q, N, nb, kind, q):
         ctx.close()
     finally:
         dist.destroy_process_group()
+
+
+def nccl_poinv_worker(rank, world, port, P, Q, N, nb, uplo_name, q):
+    """GPU: dplasma_dpoinv, dplasma_dpotrf + dplasma_dpotri and dplasma_dtrtri on a P x Q grid against the oracle."""
+    import torch
+    import dplasma_b200 as dp
+    from tests.util import full_to_local
+    torch.cuda.set_device(rank)
+    dist = _init(rank, world, port, "nccl")
+    try:
+        lib = dp.load()
+        ctx = dp.Context(lib)
+        ids = [ctx.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.comm_init(ids[0], rank, world)
+        uplo = dp.Lower if uplo_name == "L" else dp.Upper
+
+        def dev_desc():
+            d = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, where=1)
+            t = torch.zeros(max(d.elems, 1), dtype=torch.float64, device="cuda")
+            d.s.mat = t.data_ptr()
+            return d, t
+        from oracle.oracle import Oracle, NonUnit
+        orc = Oracle()
+        tri = np.tril if uplo == dp.Lower else np.triu
+        A0 = orc.plgsy(float(N), uplo, N, nb, 3872)
+        F = A0.copy(order="F")
+        assert orc.potrf(uplo, F, nb) == 0
+        T = F.copy(order="F")
+        assert orc.trtri(uplo, NonUnit, T, nb) == 0
+        Pw = F.copy(order="F")
+        assert orc.potri(uplo, Pw, nb) == 0
+
+        def local_err(t, d, want):
+            torch.cuda.synchronize()
+            got = t.cpu().numpy()[:d.elems]
+            w = full_to_local(want, nb, nb, P, Q, rank)
+            # compare the stored triangle only: rebuild the mask in the local layout
+            m = full_to_local(tri(np.ones((N, N))), nb, nb, P, Q, rank) != 0
+            o = (full_to_local(np.ones((N, N)), nb, nb, P, Q, rank) != 0) & ~m   # inside the matrix, other triangle
+            return float(np.abs(got[m] - w[m]).max() / np.abs(want).max()) if m.any() else 0.0, \
+                bool(np.array_equal(got[o], full_to_local(A0, nb, nb, P, Q, rank)[o]))
+        # (1) one call
+        dA, tA = dev_desc()
+        assert lib.dplasma_dplgsy(ctx.ptr, float(N), uplo, dA.ref, 3872) == 0
+        info1 = lib.dplasma_dpoinv(ctx.ptr, uplo, dA.ref)
+        e1, other1 = local_err(tA, dA, Pw)
+        # (2) factor, then potri
+        dB, tB = dev_desc()
+        assert lib.dplasma_dplgsy(ctx.ptr, float(N), uplo, dB.ref, 3872) == 0
+        info2 = lib.dplasma_dpotrf(ctx.ptr, uplo, dB.ref)
+        info2 = info2 or lib.dplasma_dpotri(ctx.ptr, uplo, dB.ref)
+        e2, other2 = local_err(tB, dB, Pw)
+        # (3) factor, then trtri alone
+        dC, tC = dev_desc()
+        assert lib.dplasma_dplgsy(ctx.ptr, float(N), uplo, dC.ref, 3872) == 0
+        info3 = lib.dplasma_dpotrf(ctx.ptr, uplo, dC.ref)
+        info3 = info3 or lib.dplasma_dtrtri(ctx.ptr, uplo, NonUnit, dC.ref)
+        e3, other3 = local_err(tC, dC, T)
+        # (4) not positive definite: the factorization's info, MAX-reduced, nothing inverted
+        dD, tD = dev_desc()
+        assert lib.dplasma_dplgsy(ctx.ptr, 0.0, uplo, dD.ref, 3872) == 0
+        info4 = lib.dplasma_dpoinv(ctx.ptr, uplo, dD.ref)
+        q.put((rank, info1, e1, other1, info2, e2, other2, info3, e3, other3, info4))
+        ctx.close()
+    finally:
+        dist.destroy_process_group()

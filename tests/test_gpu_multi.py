@@ -153,3 +153,30 @@ def test_dpotrf_grid_host_matrix(P, Q, kind):
         assert p.exitcode == 0
     for rank, info, err in res:
         assert info == 0 and err < 1e-11, (rank, info, err)
+
+
+@pytest.mark.parametrize("P,Q", [(1, 2), (2, 1), (2, 2), (2, 4)])
+@pytest.mark.parametrize("uplo", ["L", "U"])
+def test_dpoinv_dpotri_dtrtri_grid_match_oracle(P, Q, uplo):
+    """the inversion path on a process grid (ragged last tile): one-call dpoinv, dpotrf + dpotri, dpotrf + dtrtri"""
+    import torch
+    import torch.multiprocessing as mp
+    from tests.dist_workers import nccl_poinv_worker
+    world = P * Q
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=nccl_poinv_worker, args=(r, world, port, P, Q, 1000, 128, uplo, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for rank, info1, e1, o1, info2, e2, o2, info3, e3, o3, info4 in res:
+        assert info1 == 0 and info2 == 0 and info3 == 0, (rank, info1, info2, info3)
+        assert e1 < 1e-11 and e2 < 1e-11 and e3 < 1e-11, (rank, e1, e2, e3)
+        assert o1 and o2 and o3, (rank, o1, o2, o3)      # the other triangle is never touched
+        assert info4 == res[0][10] and info4 > 0           # MAX-reduced, identical on every rank
