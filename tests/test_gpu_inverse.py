@@ -295,3 +295,20 @@ def test_taskpool_composition_runs_in_queue_order(ctx, oracle):
     # illegal arguments: NULL (src/ztrtri_wrapper.c:84-92, zgemm_wrapper.c:445-452)
     assert lib.dplasma_dtrtri_New(7, NonUnit, dF.ref, C.byref(i1)) is None
     assert lib.dplasma_dgemm_New(7, NoTrans, 1.0, dF.ref, dF.ref, 0.0, dF.ref) is None
+
+
+def test_c_driver_with_the_four_checks_of_testing_zposv():
+    """tests/c/testing_dposv.c: plain C against include/dplasma_b200.h, the four checks of tests/testing_zposv.c
+    (posv; potrf + potrs; potrf + trsm + trsm; potrf + potri) for both triangles; exit code 0 iff all pass"""
+    import subprocess
+    exe = os.path.join(ROOT, "tests", "c", "testing_dposv")
+    subprocess.check_call(["gcc", "-std=c11", "-O2", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "c", "testing_dposv.c"), "-o", exe,
+                           "-L" + os.path.join(ROOT, "dplasma_b200", "lib"), "-ldplasma_b200",
+                           "-Wl,-rpath," + os.path.join(ROOT, "dplasma_b200", "lib")])
+    for args in (["378", "93", "367"], ["1700", "320", "400"]):   # tests/Testings.cmake:89-90,146-149
+        out = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stdout + out.stderr
+        assert out.stdout.count("PASSED !") == 8 and "FAILED" not in out.stdout, out.stdout
+        for what in ("DPOSV", "DPOTRF + DPOTRS", "DPOTRF + DTRSM + DTRSM", "DPOTRF + DPOTRI"):
+            assert f"TESTING {what} (Upper) ....... PASSED" in out.stdout and f"TESTING {what} (Lower) ....... PASSED" in out.stdout
