@@ -81,6 +81,31 @@ def test_dsyrk_vs_oracle(ctx, oracle, N, K, nb, kb, uplo, trans):
         dA.free(); dC.free()
 
 
+def test_dgemm_dsyrk_against_reference_fixtures(ctx, oracle):
+    """the CUDA path against outputs of the reference's own CORE_dgemm / CORE_dsyrk (tests/golden/make_golden_blas3.py)"""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_r01_blas3.npz"))
+    M, N, K, mb, nb, kb = 378, 300, 367, 93, 64, 80
+    for ta, na in ((NoTrans, "N"), (Trans, "T")):
+        for tb, nbn in ((NoTrans, "N"), (Trans, "T")):
+            A = oracle.plrnt(*((M, K, mb, kb) if ta == NoTrans else (K, M, kb, mb)), 11)
+            B = oracle.plrnt(*((K, N, kb, nb) if tb == NoTrans else (N, K, nb, kb)), 12)
+            dA = make_host(ctx, A, kb if ta != NoTrans else mb, mb if ta != NoTrans else kb)
+            dB = make_host(ctx, B, nb if tb != NoTrans else kb, kb if tb != NoTrans else nb)
+            dC = make_host(ctx, oracle.plrnt(M, N, mb, nb, 13), mb, nb)
+            assert ctx.lib.dplasma_dgemm(ctx.ptr, ta, tb, 0.75, dA.ref, dB.ref, -0.5, dC.ref) == 0
+            assert relerr(read_host(dC, M, N, mb, nb).ravel(order="F")[::17], g[f"dgemm_{na}{nbn}_s17"]) < VTOL
+            dA.free(); dB.free(); dC.free()
+    for uplo, nu in ((Lower, "L"), (Upper, "U")):
+        for tr, nt_ in ((NoTrans, "N"), (Trans, "T")):
+            A = oracle.plrnt(*((N, K, nb, kb) if tr == NoTrans else (K, N, kb, nb)), 21)
+            dA = make_host(ctx, A, kb if tr != NoTrans else nb, nb if tr != NoTrans else kb)
+            dC = make_host(ctx, oracle.plrnt(N, N, nb, nb, 22), nb, nb)
+            assert ctx.lib.dplasma_dsyrk(ctx.ptr, uplo, tr, 0.5, dA.ref, -0.25, dC.ref) == 0
+            assert relerr(read_host(dC, N, N, nb, nb).ravel(order="F")[::17], g[f"dsyrk_{nu}{nt_}_s17"]) < VTOL
+            dA.free(); dC.free()
+
+
 def test_blas3_argument_codes(ctx):
     def desc(m, n, mb, nb):
         s = dp.capi.BlockCyclicStruct()

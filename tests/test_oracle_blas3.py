@@ -50,6 +50,26 @@ def test_tiled_herk_against_numpy(oracle, p):
     assert oracle.herk(Lower, 7, 1.0, A, 0.0, C1, nb, kb, p) == -2
 
 
+def test_gemm_syrk_against_reference_fixtures(oracle):
+    """fixtures from the reference's CORE_dgemm / CORE_dsyrk (tests/golden/make_golden_blas3.py)"""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_r01_blas3.npz"))
+    M, N, K, mb, nb, kb = 378, 300, 367, 93, 64, 80
+    for ta, na in ((NoTrans, "N"), (Trans, "T")):
+        for tb, nbn in ((NoTrans, "N"), (Trans, "T")):
+            A = oracle.plrnt(*((M, K, mb, kb) if ta == NoTrans else (K, M, kb, mb)), 11)
+            B = oracle.plrnt(*((K, N, kb, nb) if tb == NoTrans else (N, K, nb, kb)), 12)
+            C = oracle.plrnt(M, N, mb, nb, 13)
+            assert oracle.gemm(ta, tb, 0.75, A, B, -0.5, C, mb, nb, kb) == 0
+            np.testing.assert_allclose(C.ravel(order="F")[::17], g[f"dgemm_{na}{nbn}_s17"], rtol=1e-12, atol=1e-13)
+    for uplo, nu in ((Lower, "L"), (Upper, "U")):
+        for tr, nt_ in ((NoTrans, "N"), (Trans, "T")):
+            A = oracle.plrnt(*((N, K, nb, kb) if tr == NoTrans else (K, N, kb, nb)), 21)
+            C = oracle.plrnt(N, N, nb, nb, 22)
+            assert oracle.herk(uplo, tr, 0.5, A, -0.25, C, nb, kb) == 0
+            np.testing.assert_allclose(C.ravel(order="F")[::17], g[f"dsyrk_{nu}{nt_}_s17"], rtol=1e-12, atol=1e-13)
+
+
 def test_reference_gemm_syrk_agree_when_present(oracle):
     try:
         from oracle.oracle import Reference
