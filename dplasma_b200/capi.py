@@ -80,6 +80,7 @@ class Lib:
         proto("parsec_tiled_matrix_destroy", None, [pBC])
         proto("dplasma_b200_rank_of", i, [pBC, i, i])
         proto("dplasma_b200_panel_plan", i, [pBC, i, i, C.POINTER(i), C.POINTER(i), C.POINTER(i)])
+        proto("dplasma_b200_rowpanel_plan", i, [pBC, i, C.POINTER(i), C.POINTER(i), C.POINTER(i)])
         proto("dplasma_dpotrf_New", vp, [i, pBC, C.POINTER(i)])
         proto("dplasma_dpotrf_Destruct", None, [vp])
         proto("dplasma_dpotrf_Destroy", None, [vp])

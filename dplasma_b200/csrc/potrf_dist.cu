@@ -503,3 +503,31 @@ extern "C" int dplasma_b200_panel_plan(const parsec_tiled_matrix_t* A, int k, in
     }
     return 0;
 }
+
+// Host-only plan of step k of the distributed inversion DAGs (src/ztrtri_L.jdf, src/zlauum_L.jdf): the operands of
+// a step are tile ROW k to the left of the diagonal (n < k), which the owners in grid row kp send down their grid
+// columns, and -- for the lauum products A(m,n) += A(k,m)^T A(k,n) -- the same tiles re-sent along the grid row of
+// their transposed position.  out[0..3] = kp, kq, ncolsBefore (local tile columns with global n < k),
+// nrowsBefore (local tile rows with global m < k); for each such local tile row il (global m): rowRootCol[il] =
+// the grid column m % Q that holds A(k,m) after the column broadcast, rowSrcJl[il] = m / Q, its local column there.
+extern "C" int dplasma_b200_rowpanel_plan(const parsec_tiled_matrix_t* A, int k, int* out, int* rowRootCol, int* rowSrcJl) {
+    using namespace dpb;
+    const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
+    DevMatrix dm;
+    dm.mb = A->mb; dm.nb = A->nb;
+    dm.M = A->m; dm.N = A->n; dm.mt = A->mt; dm.nt = A->nt;
+    dm.P = bc->grid.rows; dm.Q = bc->grid.cols;
+    dm.prow = (bc->grid.rrank - bc->grid.ip + dm.P) % dm.P;
+    dm.pcol = (bc->grid.crank - bc->grid.jq + dm.Q) % dm.Q;
+    dm.lmt = bc->nb_elem_r; dm.lnt = bc->nb_elem_c;
+    out[0] = k % dm.P;
+    out[1] = k % dm.Q;
+    out[2] = std::min(dm.firstLocalColGE(k), dm.lnt);
+    out[3] = std::min(dm.firstLocalRowGE(k), dm.lmt);
+    for (int il = 0; il < out[3]; il++) {
+        const int gm = il * dm.P + dm.prow;
+        rowRootCol[il] = gm % dm.Q;
+        rowSrcJl[il] = gm / dm.Q;
+    }
+    return 0;
+}

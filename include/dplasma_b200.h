@@ -135,6 +135,12 @@ void parsec_tiled_matrix_destroy(parsec_tiled_matrix_t *dc);
  * into messages.  Host arithmetic only.  out[6] = {kq, kp, il0, nrows, jl0, ncols}. */
 int dplasma_b200_panel_plan(const parsec_tiled_matrix_t *A, int k, int gmFirst, int *out, int *colRoot,
                             int *colSrcIl);
+/* The plan of step k of the distributed inversion DAGs (src/ztrtri_L.jdf:60-142, src/zlauum_L.jdf:38-130), whose
+ * operands are tile ROW k left of the diagonal: out[4] = {kp, kq, local tile columns with n < k, local tile rows
+ * with m < k}; per such local tile row (global m): the grid column m % Q that holds A(k,m) once the row has gone
+ * down the grid columns, and m / Q, its local column index there (the root and source of the broadcast along the
+ * grid row that the products A(m,n) += A(k,m)^T A(k,n) need).  Host arithmetic only. */
+int dplasma_b200_rowpanel_plan(const parsec_tiled_matrix_t *A, int k, int *out, int *rowRootCol, int *rowSrcJl);
 /* rank owning global tile (m,n): the data collection's rank_of (src/zpotrf_L.jdf:105) */
 int dplasma_b200_rank_of(const parsec_tiled_matrix_t *A, int m, int n);
 

@@ -368,3 +368,151 @@ def nccl_poinv_worker(rank, world, port, P, Q, N, nb, uplo_name, q):
         ctx.close()
     finally:
         dist.destroy_process_group()
+
+
+def gloo_potri_worker(rank, world, port, P, Q, N, nb, q):
+    """CPU: distributed tiled trtri + lauum (lower) with the ORACLE's tile kernels, driven by the library's own
+    per-step plans (dplasma_b200_panel_plan for the tile column below the diagonal, dplasma_b200_rowpanel_plan for
+    the tile row left of it) over gloo broadcasts.  Step bodies: src/ztrtri_L.jdf:21-187, src/zlauum_L.jdf:38-155."""
+    import torch
+    import dplasma_b200 as dp
+    from oracle.oracle import Oracle, Lower, NoTrans, ConjTrans, NonUnit, Left, Right
+    from tests.util import full_to_local, local_to_full
+    dist = _init(rank, world, port, "gloo")
+    try:
+        lib, orc = dp.load(), Oracle()
+        prow, pcol = rank // Q, rank % Q
+        row_groups = [dist.new_group([r * Q + c for c in range(Q)]) for r in range(P)]
+        col_groups = [dist.new_group([r * Q + c for r in range(P)]) for c in range(Q)]
+        A0 = orc.plgsy(float(N), Lower, N, nb, 3872)
+        F = A0.copy(order="F")
+        assert orc.potrf(Lower, F, nb) == 0
+        s = dp.capi.BlockCyclicStruct()
+        lib.parsec_matrix_block_cyclic_init(C.byref(s), dp.MATRIX_DOUBLE, dp.MATRIX_TILE, rank, nb, nb, N, N, 0, 0, N, N, P, Q, 1, 1, 0, 0)
+        lmt, lnt, mt = s.nb_elem_r, s.nb_elem_c, s.super.mt
+        flat = full_to_local(F, nb, nb, P, Q, rank)
+        tiles = flat.reshape(lnt, lmt, nb, nb) if flat.size else np.zeros((lnt, lmt, nb, nb))
+
+        def tile(il, jl):
+            return tiles[jl, il].reshape((nb, nb)).T
+
+        def tdim(g):
+            return N - g * nb if g == mt - 1 else nb
+
+        def bc(t, src, group):
+            x = torch.from_numpy(np.ascontiguousarray(t))
+            dist.broadcast(x, src=src, group=group)
+            return x.numpy()
+
+        def plans(k):
+            out = (C.c_int * 6)()
+            cr, cs = (C.c_int * max(lnt, 1))(), (C.c_int * max(lnt, 1))()
+            lib.dplasma_b200_panel_plan(C.byref(s), k, k + 1, out, cr, cs)
+            kq, kp, il0, nrows = out[0], out[1], out[2], out[3]
+            ro = (C.c_int * 4)()
+            rc, rj = (C.c_int * max(lmt, 1))(), (C.c_int * max(lmt, 1))()
+            lib.dplasma_b200_rowpanel_plan(C.byref(s), k, ro, rc, rj)
+            assert ro[0] == kp == k % P and ro[1] == kq == k % Q
+            return kp, kq, il0, nrows, ro[2], ro[3], list(rc), list(rj)
+
+        def diag_tile_everywhere_it_is_needed(k, kp, kq, down_column, along_row):
+            """A(k,k) from its owner down grid column kq and / or along grid row kp (ztrsm_in_A, readA)"""
+            t = np.zeros((nb, nb))
+            if prow == kp and pcol == kq:
+                t = np.array(tile(k // P, k // Q))
+            if down_column and pcol == kq:
+                t = bc(t, kp * Q + kq, col_groups[kq])
+            if along_row and prow == kp:
+                t = bc(t, kp * Q + kq, row_groups[kp])
+            return t
+
+        def row_k_down_the_columns(k, kp, ncb):
+            """tile row k, n < k: every rank of grid row kp sends its tiles down its grid column"""
+            return {jl: bc(np.array(tile(k // P, jl)) if prow == kp else np.zeros((nb, nb)), kp * Q + pcol, col_groups[pcol])
+                    for jl in range(ncb)}
+
+        # ---------------- trtri ----------------
+        for k in range(mt):
+            kp, kq, il0, nrows, ncb, nrb, rootc, srcj = plans(k)
+            tk, ilk, jlk = tdim(k), k // P, k // Q
+            Akk = np.asfortranarray(diag_tile_everywhere_it_is_needed(k, kp, kq, True, True)[:tk, :tk])
+            # trtri_ztrsmR: A(m,k) = -A(m,k) inv(A(k,k)), my rows m > k of tile column k
+            if pcol == kq:
+                for il in range(il0, il0 + nrows):
+                    gm = il * P + prow
+                    B = np.asfortranarray(tile(il, jlk)[:tdim(gm), :tk])
+                    orc.trsm_tile(Right, Lower, NoTrans, NonUnit, -1.0, Akk, B)
+                    tile(il, jlk)[:tdim(gm), :tk] = B
+            # the new column slab along the grid rows (root kq), tile row k down the grid columns (root kp)
+            rowp = {}
+            if nrows > 0:
+                slab = np.stack([np.array(tile(il, jlk)) for il in range(il0, il0 + nrows)]) if pcol == kq else np.zeros((nrows, nb, nb))
+                slab = bc(slab, prow * Q + kq, row_groups[prow])
+                rowp = {il0 + i: slab[i] for i in range(nrows)}
+            colp = row_k_down_the_columns(k, kp, ncb)
+            # trtri_zgemm: A(m,n) += A(m,k) A(k,n), m > k > n
+            for jl in range(ncb):
+                for il in range(il0, il0 + nrows):
+                    gm = il * P + prow
+                    Am = np.asfortranarray(rowp[il][:tdim(gm), :tk])
+                    Bn = np.asfortranarray(colp[jl][:tk, :nb])
+                    Cmn = np.asfortranarray(tile(il, jl)[:tdim(gm), :nb])
+                    orc.gemm_tile(NoTrans, NoTrans, 1.0, Am, Bn, 1.0, Cmn)
+                    tile(il, jl)[:tdim(gm), :nb] = Cmn
+            if prow == kp:
+                # trtri_ztrsmL: A(k,n) = inv(A(k,k)) A(k,n), n < k
+                for jl in range(ncb):
+                    B = np.asfortranarray(tile(ilk, jl)[:tk, :nb])
+                    orc.trsm_tile(Left, Lower, NoTrans, NonUnit, 1.0, Akk, B)
+                    tile(ilk, jl)[:tk, :nb] = B
+                if pcol == kq:
+                    T = np.asfortranarray(tile(ilk, jlk)[:tk, :tk])
+                    assert orc.trtri_tile(Lower, NonUnit, T) == 0
+                    tile(ilk, jlk)[:tk, :tk] = T
+        # ---------------- lauum ----------------
+        for k in range(mt):
+            kp, kq, il0, nrows, ncb, nrb, rootc, srcj = plans(k)
+            tk, ilk, jlk = tdim(k), k // P, k // Q
+            colp = row_k_down_the_columns(k, kp, ncb)
+            # A(k,m) for my tile rows m < k: along my grid row from the grid column that received it
+            rowt = {il: bc(colp[srcj[il]] if pcol == rootc[il] else np.zeros((nb, nb)), prow * Q + rootc[il], row_groups[prow])
+                    for il in range(nrb)}
+            for jl in range(ncb):
+                gn = jl * Q + pcol
+                An = np.asfortranarray(colp[jl][:tk, :nb])
+                for il in range(nrb):
+                    gm = il * P + prow
+                    if gm < gn:
+                        continue
+                    Cmn = np.asfortranarray(tile(il, jl))
+                    if gm == gn:  # lauum_zherk
+                        orc.herk_tile(Lower, ConjTrans, 1.0, An, 1.0, Cmn)
+                    else:         # lauum_zgemm
+                        orc.gemm_tile(ConjTrans, NoTrans, 1.0, np.asfortranarray(rowt[il][:tk, :nb]), An, 1.0, Cmn)
+                    tile(il, jl)[:, :] = Cmn
+            Akk = np.asfortranarray(diag_tile_everywhere_it_is_needed(k, kp, kq, False, True)[:tk, :tk])
+            if prow == kp:
+                for jl in range(ncb):  # lauum_ztrmm
+                    B = np.asfortranarray(tile(ilk, jl)[:tk, :nb])
+                    orc.trmm_tile(Left, Lower, ConjTrans, NonUnit, 1.0, Akk, B)
+                    tile(ilk, jl)[:tk, :nb] = B
+                if pcol == kq:         # lauum_zlauum
+                    T = np.asfortranarray(tile(ilk, jlk)[:tk, :tk])
+                    orc.lauum_tile(Lower, T)
+                    tile(ilk, jlk)[:tk, :tk] = T
+        want = F.copy(order="F")
+        assert orc.potri(Lower, want, nb) == 0
+        got = local_to_full(tiles.reshape(-1), N, N, nb, nb, P, Q, rank)
+        mask = np.zeros((N, N), dtype=bool)
+        for jl in range(lnt):
+            for il in range(lmt):
+                gm, gn = il * P + prow, jl * Q + pcol
+                if gm >= gn:
+                    mask[gm * nb:gm * nb + tdim(gm), gn * nb:gn * nb + tdim(gn)] = True
+        low = mask & np.tril(np.ones((N, N), dtype=bool))
+        up = mask & ~np.tril(np.ones((N, N), dtype=bool))          # strict upper parts of my diagonal tiles
+        err = float(np.abs(got - want)[low].max() / np.abs(want).max()) if low.any() else 0.0
+        untouched = bool(np.array_equal(got[up], F[up]))
+        q.put((rank, err, untouched))
+    finally:
+        dist.destroy_process_group()

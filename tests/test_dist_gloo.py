@@ -32,3 +32,26 @@ def test_distributed_cholesky_plan_over_gloo(P, Q, N, nb):
     for rank, err, info, winfo in res:
         assert err < 1e-12, (rank, err)
         assert info == winfo == 0
+
+
+@pytest.mark.parametrize("P,Q,N,nb", [(1, 2, 200, 32), (2, 1, 200, 32), (2, 2, 232, 24), (2, 3, 250, 24)])
+def test_distributed_trtri_lauum_plan_over_gloo(P, Q, N, nb):
+    """the communication pattern of the inversion DAGs on a grid (tile column below the diagonal along the grid
+    rows, tile row left of it down the grid columns and, for lauum, on along the grid row of its transposed
+    position) with the library's plans and the oracle's tile kernels; result == single-process oracle potri"""
+    import torch.multiprocessing as mp
+    from tests.dist_workers import gloo_potri_worker
+    world = P * Q
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=gloo_potri_worker, args=(r, world, port, P, Q, N, nb, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err, untouched in res:
+        assert err < 1e-12, (rank, err)
+        assert untouched, rank
