@@ -516,3 +516,127 @@ def gloo_potri_worker(rank, world, port, P, Q, N, nb, q):
         q.put((rank, err, untouched))
     finally:
         dist.destroy_process_group()
+
+
+def gloo_gemm_syrk_worker(rank, world, port, P, Q, M, N, K, nb, q):
+    """CPU: distributed C = alpha A B^T + beta C (dgemm NT) and C = alpha A A^T + beta C (dsyrk Lower NoTrans) on a
+    P x Q grid with the ORACLE's tile kernels, driven by dplasma_b200_panel_plan with gmFirst = 0: at step k tile
+    column k of A goes along the grid rows; tile column k of B (of A for syrk) goes along the grid rows too and
+    then, from the rank on the diagonal of the grid pattern, down the grid column of its transposed position --
+    the three broadcasts of the factorization (src/zpotrf_L.jdf:112,213-215) without the solves."""
+    import torch
+    import dplasma_b200 as dp
+    from oracle.oracle import Oracle, Lower, NoTrans, ConjTrans
+    from tests.util import full_to_local, local_to_full
+    dist = _init(rank, world, port, "gloo")
+    try:
+        lib, orc = dp.load(), Oracle()
+        prow, pcol = rank // Q, rank % Q
+        row_groups = [dist.new_group([r * Q + c for c in range(Q)]) for r in range(P)]
+        col_groups = [dist.new_group([r * Q + c for r in range(P)]) for c in range(Q)]
+        alpha, beta = 0.75, -0.5
+
+        def desc(m, n):
+            s = dp.capi.BlockCyclicStruct()
+            lib.parsec_matrix_block_cyclic_init(C.byref(s), dp.MATRIX_DOUBLE, dp.MATRIX_TILE, rank, nb, nb, m, n, 0, 0, m, n, P, Q, 1, 1, 0, 0)
+            return s
+
+        class Local:
+            def __init__(self, X):
+                self.m, self.n = X.shape
+                self.s = desc(self.m, self.n)
+                self.lmt, self.lnt, self.mt, self.nt = self.s.nb_elem_r, self.s.nb_elem_c, self.s.super.mt, self.s.super.nt
+                flat = full_to_local(X, nb, nb, P, Q, rank)
+                self.t = flat.reshape(self.lnt, self.lmt, nb, nb) if flat.size else np.zeros((self.lnt, self.lmt, nb, nb))
+
+            def tile(self, il, jl):
+                return self.t[jl, il].reshape((nb, nb)).T
+
+            def rows(self, g):
+                return self.m - g * nb if g == self.mt - 1 else nb
+
+            def cols(self, g):
+                return self.n - g * nb if g == self.nt - 1 else nb
+
+            def full(self):
+                return local_to_full(self.t.reshape(-1), self.m, self.n, nb, nb, P, Q, rank)
+
+        def bc(t, src, group):
+            x = torch.from_numpy(np.ascontiguousarray(t))
+            dist.broadcast(x, src=src, group=group)
+            return x.numpy()
+
+        def row_panel(X, k):
+            """tile column k of X, all rows: my grid row's tiles of it, from the rank in grid column k % Q"""
+            out = (C.c_int * 6)()
+            cr, cs = (C.c_int * max(X.lnt, 1))(), (C.c_int * max(X.lnt, 1))()
+            lib.dplasma_b200_panel_plan(C.byref(X.s), k, 0, out, cr, cs)
+            kq, il0, nrows = out[0], out[2], out[3]
+            assert il0 == 0 and nrows == X.lmt
+            if nrows == 0:
+                return {}
+            slab = np.stack([np.array(X.tile(il, k // Q)) for il in range(nrows)]) if pcol == kq else np.zeros((nrows, nb, nb))
+            slab = bc(slab, prow * Q + kq, row_groups[prow])
+            return {il: slab[il] for il in range(nrows)}
+
+        def col_panel(X, k, rowp, ncols_c, owner_desc):
+            """X(n,k) for my local tile columns n of C: down my grid column from grid row n % P, which holds it in rowp"""
+            out = (C.c_int * 6)()
+            cr, cs = (C.c_int * max(ncols_c, 1))(), (C.c_int * max(ncols_c, 1))()
+            lib.dplasma_b200_panel_plan(C.byref(owner_desc), k, 0, out, cr, cs)
+            assert out[4] == 0 and out[5] == ncols_c
+            return {jl: bc(rowp[cs[jl]] if cr[jl] == prow else np.zeros((nb, nb)), cr[jl] * Q + pcol, col_groups[pcol])
+                    for jl in range(ncols_c)}
+
+        # ---------------- dgemm NT: C (M x N) = alpha A (M x K) B (N x K)^T + beta C ----------------
+        A = Local(orc.plrnt(M, K, nb, nb, 11))
+        B = Local(orc.plrnt(N, K, nb, nb, 12))
+        Cfull = orc.plrnt(M, N, nb, nb, 13)
+        Cm = Local(Cfull)
+        # the plan of the transposed broadcast is the one of an N x N matrix with C's column distribution
+        sq = desc(N, N)
+        for k in range(A.nt):
+            tk = A.cols(k)
+            ap = row_panel(A, k)
+            bp = col_panel(B, k, row_panel(B, k), Cm.lnt, sq)
+            for jl in range(Cm.lnt):
+                gn = jl * Q + pcol
+                Bn = np.asfortranarray(bp[jl][:Cm.cols(gn), :tk])
+                for il in range(Cm.lmt):
+                    gm = il * P + prow
+                    T = np.asfortranarray(Cm.tile(il, jl)[:Cm.rows(gm), :Cm.cols(gn)])
+                    orc.gemm_tile(NoTrans, ConjTrans, alpha, np.asfortranarray(ap[il][:Cm.rows(gm), :tk]), Bn, beta if k == 0 else 1.0, T)
+                    Cm.tile(il, jl)[:Cm.rows(gm), :Cm.cols(gn)] = T
+        want = Cfull.copy(order="F")
+        assert orc.gemm(NoTrans, ConjTrans, alpha, orc.plrnt(M, K, nb, nb, 11), orc.plrnt(N, K, nb, nb, 12), beta, want, nb, nb, nb) == 0
+        mask = local_to_full(full_to_local(np.ones((M, N)), nb, nb, P, Q, rank), M, N, nb, nb, P, Q, rank) != 0
+        err_gemm = float(np.abs(Cm.full() - want)[mask].max() / np.abs(want).max()) if mask.any() else 0.0
+        # ---------------- dsyrk Lower NoTrans: S (M x M) = alpha A A^T + beta S ----------------
+        Sfull = orc.plrnt(M, M, nb, nb, 22)
+        S = Local(Sfull)
+        for k in range(A.nt):
+            tk = A.cols(k)
+            ap = row_panel(A, k)
+            cp = col_panel(A, k, ap, S.lnt, S.s)
+            for jl in range(S.lnt):
+                gn = jl * Q + pcol
+                An = np.asfortranarray(cp[jl][:S.cols(gn), :tk])
+                for il in range(S.lmt):
+                    gm = il * P + prow
+                    if gm < gn:
+                        continue
+                    T = np.asfortranarray(S.tile(il, jl)[:S.rows(gm), :S.cols(gn)])
+                    zb = beta if k == 0 else 1.0
+                    if gm == gn:
+                        orc.herk_tile(Lower, NoTrans, alpha, An, zb, T)
+                    else:
+                        orc.gemm_tile(NoTrans, ConjTrans, alpha, np.asfortranarray(ap[il][:S.rows(gm), :tk]), An, zb, T)
+                    S.tile(il, jl)[:S.rows(gm), :S.cols(gn)] = T
+        wantS = Sfull.copy(order="F")
+        assert orc.herk(Lower, NoTrans, alpha, orc.plrnt(M, K, nb, nb, 11), beta, wantS, nb, nb) == 0
+        maskS = local_to_full(full_to_local(np.ones((M, M)), nb, nb, P, Q, rank), M, M, nb, nb, P, Q, rank) != 0
+        d = np.abs(S.full() - wantS)   # the upper triangle must still be the input: wantS keeps it too
+        err_syrk = float(d[maskS].max() / np.abs(wantS).max()) if maskS.any() else 0.0
+        q.put((rank, err_gemm, err_syrk))
+    finally:
+        dist.destroy_process_group()

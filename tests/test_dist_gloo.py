@@ -55,3 +55,24 @@ def test_distributed_trtri_lauum_plan_over_gloo(P, Q, N, nb):
     for rank, err, untouched in res:
         assert err < 1e-12, (rank, err)
         assert untouched, rank
+
+
+@pytest.mark.parametrize("P,Q,M,N,K,nb", [(1, 2, 150, 130, 170, 32), (2, 1, 150, 130, 170, 32), (2, 2, 140, 100, 90, 24), (2, 3, 160, 150, 100, 24)])
+def test_distributed_gemm_syrk_plan_over_gloo(P, Q, M, N, K, nb):
+    """dgemm (NT) and dsyrk (Lower, NoTrans) on a grid are the factorization's panel exchange with gmFirst = 0:
+    the library's plan + the oracle's tile kernels over gloo reproduce the single-process oracle"""
+    import torch.multiprocessing as mp
+    from tests.dist_workers import gloo_gemm_syrk_worker
+    world = P * Q
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=gloo_gemm_syrk_worker, args=(r, world, port, P, Q, M, N, K, nb, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err_gemm, err_syrk in res:
+        assert err_gemm < 1e-12 and err_syrk < 1e-12, (rank, err_gemm, err_syrk)
