@@ -129,6 +129,7 @@ class Lib:
         proto("dplasma_b200_kernel_launches", C.c_longlong, [vp])
         proto("dplasma_b200_profile", None, [vp, i])
         proto("dplasma_b200_profile_read", i, [vp, C.POINTER(d), C.POINTER(d), C.POINTER(i), C.POINTER(d)])
+        proto("dplasma_b200_profile_read_stream", i, [vp, i, C.POINTER(d), C.POINTER(d), C.POINTER(i), C.POINTER(d)])
         proto("dplasma_b200_dpotrf_tile", i, [vp, vp, i, i, vp, i, vp, i])
         proto("dplasma_b200_dpotrf_tile_noalloc", i, [vp, i, i, vp, i, vp, i])
         proto("dplasma_b200_dtrsm_tile", i, [vp, vp, i, i, i, i, i, i, d, vp, i, vp, i])

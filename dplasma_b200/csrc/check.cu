@@ -184,7 +184,7 @@ int check_dpotrf(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec
     if (!rc && uplo == dplasmaUpper && multi) {
         // grid: bring both the factor and A0 to lower form through the distributed transpose
         DevMatrix Lt, Rt;
-        rc = ensure_grid_comms(parsec, dA.P, dA.Q);
+        rc = ensure_grid_comms(parsec, dA.P, dA.Q, dA.ip, dA.jq);
         if (!rc) rc = alloc_like(dA, &Lt);
         if (!rc) rc = alloc_like(dA, &Rt);
         if (!rc) rc = dist_transpose_tri(parsec, s, dA, dplasmaUpper, Lt);

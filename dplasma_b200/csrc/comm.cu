@@ -83,18 +83,22 @@ int p2p_recv(parsec_context_s* ctx, double* buf, size_t count, int peer, cudaStr
 int group_start(parsec_context_s* ctx) { return ctx->nccl->GroupStart(); }
 int group_end(parsec_context_s* ctx) { return ctx->nccl->GroupEnd(); }
 
-// row / column communicators of a P x Q grid are split lazily, once per grid shape
-int ensure_grid_comms(parsec_context_s* ctx, int P, int Q) {
-    if (ctx->gridP == P && ctx->gridQ == Q && ctx->commRow && ctx->commCol) return 0;
+// row / column communicators of a P x Q grid are split lazily, once per grid shape.
+// Ranks inside the row / column communicators are the LOGICAL grid coordinates of the distribution (the
+// process that owns tile (0,0) is rank 0 of both), so that the broadcast roots k % Q, n % P of the step plan
+// are communicator ranks as they stand, whatever RSRC / CSRC (grid.ip / grid.jq) the descriptor carries.
+int ensure_grid_comms(parsec_context_s* ctx, int P, int Q, int ip, int jq) {
+    if (ctx->gridP == P && ctx->gridQ == Q && ctx->gridIp == ip && ctx->gridJq == jq && ctx->commRow && ctx->commCol) return 0;
     if (!ctx->commWorld) { fprintf(stderr, "dplasma_b200: dplasma_b200_comm_init was not called\n"); return -302; }
     if (P * Q != ctx->nranks) { fprintf(stderr, "dplasma_b200: grid %dx%d does not match %d ranks\n", P, Q, ctx->nranks); return -303; }
     if (ctx->commRow) ctx->nccl->CommDestroy(ctx->commRow);
     if (ctx->commCol) ctx->nccl->CommDestroy(ctx->commCol);
     const int prow = ctx->rank / Q, pcol = ctx->rank % Q;
-    int rc = ctx->nccl->CommSplit(ctx->commWorld, prow, pcol, &ctx->commRow, nullptr);  // ranks of my grid row, keyed by column
-    if (!rc) rc = ctx->nccl->CommSplit(ctx->commWorld, pcol, prow, &ctx->commCol, nullptr);  // my grid column, keyed by row
+    const int lrow = (prow - ip % P + P) % P, lcol = (pcol - jq % Q + Q) % Q;
+    int rc = ctx->nccl->CommSplit(ctx->commWorld, prow, lcol, &ctx->commRow, nullptr);  // ranks of my grid row, keyed by logical column
+    if (!rc) rc = ctx->nccl->CommSplit(ctx->commWorld, pcol, lrow, &ctx->commCol, nullptr);  // my grid column, keyed by logical row
     if (rc) { fprintf(stderr, "dplasma_b200: ncclCommSplit failed: %s\n", ctx->nccl->GetErrorString(rc)); return -304; }
-    ctx->gridP = P; ctx->gridQ = Q;
+    ctx->gridP = P; ctx->gridQ = Q; ctx->gridIp = ip; ctx->gridJq = jq;
     return 0;
 }
 

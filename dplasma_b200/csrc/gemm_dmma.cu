@@ -2,6 +2,7 @@
 #include "gemm_dmma.cuh"
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 
 namespace dpb {
 
@@ -11,8 +12,6 @@ int gemm_init_attributes() {
     e = cudaFuncSetAttribute(gemm_dmma_kernel<CFG, AK, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                              (int)CFG::smem(AK, BK));                                                    \
     if (e != cudaSuccess) return (int)e;
-    DPB_ATTR(CfgBig, false, false)
-    DPB_ATTR(CfgWide, false, false)
     DPB_ATTR(CfgSmall, false, false)
     DPB_ATTR(CfgSmall, true, false)
     DPB_ATTR(CfgSmall, false, true)
@@ -22,48 +21,95 @@ int gemm_init_attributes() {
 }
 
 void gemm_cfg_dims(int cfg, int* bm, int* bn) {
-    if (cfg == CFG_BIG) { *bm = CfgBig::BM; *bn = CfgBig::BN; }
-    else if (cfg == CFG_WIDE) { *bm = CfgWide::BM; *bn = CfgWide::BN; }
-    else { *bm = CfgSmall::BM; *bn = CfgSmall::BN; }
+    (void)cfg;
+    *bm = CfgSmall::BM;
+    *bn = CfgSmall::BN;
 }
 
-// Tile configuration for a problem that would be `bigItems` CTA tiles of 128x128.
-// DPB_GEMM_CFG=big|wide|small overrides (profiling).
+// One tile configuration: 64x64 CTA tiles at 3 CTAs/SM (measured in round 1 against 128x128 and 128x64:
+// co-resident CTAs hide each other's prologue and epilogue, which one resident CTA cannot).
 int gemm_pick_cfg(long long bigItems) {
-    static int forced = -2;
-    if (forced == -2) {
-        const char* e = getenv("DPB_GEMM_CFG");
-        forced = -1;
-        if (e) {
-            if (e[0] == 'b') forced = CFG_BIG;
-            else if (e[0] == 'w') forced = CFG_WIDE;
-            else if (e[0] == 's') forced = CFG_SMALL;
-        }
-    }
-    if (forced >= 0) return forced;
-    // Measured on B200 (profiles/): the 64x64 tile at 3 CTAs/SM beats the larger tiles at every
-    // size (34.9 vs 32.6 / 32.3 TFLOP/s on 16384^2 x 512): co-resident CTAs hide each other's
-    // prologue and epilogue, which a single resident CTA cannot.
     (void)bigItems;
     return CFG_SMALL;
 }
 
-int gemm_launch(const GemmDesc& d, int nItems, int cfg, cudaStream_t stream) {
-    if (nItems <= 0) return 0;
-    // operands stored K-major (transposed forms) exist for the 64x64 tile only
-    if (d.a_kmajor || d.b_kmajor) {
-        if (d.a_kmajor && d.b_kmajor)
-            gemm_dmma_kernel<CfgSmall, true, true><<<nItems, CfgSmall::THREADS, CfgSmall::smem(true, true), stream>>>(d);
-        else if (d.a_kmajor)
-            gemm_dmma_kernel<CfgSmall, true, false><<<nItems, CfgSmall::THREADS, CfgSmall::smem(true, false), stream>>>(d);
+// ---- tensor maps of the M-major operands ----
+// cuTensorMapEncodeTiled is host arithmetic inside the driver library; it is resolved through the runtime so
+// that the library keeps linking against nothing but cudart.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encoder() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
         else
-            gemm_dmma_kernel<CfgSmall, false, true><<<nItems, CfgSmall::THREADS, CfgSmall::smem(false, true), stream>>>(d);
-    } else if (cfg == CFG_SMALL)
-        gemm_dmma_kernel<CfgSmall, false, false><<<nItems, CfgSmall::THREADS, CfgSmall::SMEM, stream>>>(d);
-    else if (cfg == CFG_WIDE)
-        gemm_dmma_kernel<CfgWide, false, false><<<nItems, CfgWide::THREADS, CfgWide::SMEM, stream>>>(d);
+            fprintf(stderr, "dplasma_b200: cuTensorMapEncodeTiled is not available from this driver\n");
+    }
+    return fn;
+}
+
+// A 4-D view {rows, k, tile, k-tile} of an operand stored M-major: element (r, kk) of tile t, k-tile q at
+// base + r + kk*ld + t*tileStride + q*kTileStride (doubles).  Box = {16 rows, BK}, 128-byte swizzle.
+static bool encode_operand(CUtensorMap* tm, const double* base, long long rows, long long kdim, long long ld,
+                           long long tiles, long long tileStride, long long ktiles, long long kTileStride) {
+    EncodeTiledFn enc = encoder();
+    if (!enc) return false;
+    if (rows <= 0 || kdim <= 0) return false;
+    if (tiles < 1) tiles = 1;
+    if (ktiles < 1) ktiles = 1;
+    // strides of dimensions that have extent 1 are never used, but must still be legal (non-zero multiples of 16 B)
+    if (tiles == 1 || tileStride <= 0) tileStride = ld * kdim + (ld * kdim) % 2;
+    if (ktiles == 1 || kTileStride <= 0) kTileStride = tileStride;
+    if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld & 1) || (tileStride & 1) || (kTileStride & 1)) return false;
+    const cuuint64_t dims[4] = {(cuuint64_t)rows, (cuuint64_t)kdim, (cuuint64_t)tiles, (cuuint64_t)ktiles};
+    const cuuint64_t strides[3] = {(cuuint64_t)ld * 8, (cuuint64_t)tileStride * 8, (cuuint64_t)kTileStride * 8};
+    const cuuint32_t box[4] = {(cuuint32_t)CfgSmall::MBLK, (cuuint32_t)CfgSmall::BK, 1, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, const_cast<double*>(base), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS;
+}
+
+// fills d.tmA / d.tmB for the operands stored M-major; false: this launch has to use the element-wise producer
+static bool prepare_tensor_maps(GemmDesc& d) {
+    const bool multiK = d.kTile < (1 << 30);
+    const long long kdim = multiK ? d.kTile : d.K;
+    const long long ktiles = multiK ? (d.K + d.kTile - 1) / d.kTile : 1;
+    if (d.mode == GEMM_SINGLE) {
+        if (!d.a_kmajor && !encode_operand(&d.tmA, d.A, d.M, kdim, d.lda, d.batchStrideA != 0 ? d.batch : 1, d.batchStrideA,
+                                           ktiles, d.aKTileStride))
+            return false;
+        if (!d.b_kmajor && !encode_operand(&d.tmB, d.B, d.N, kdim, d.ldb, d.batchStrideB != 0 ? d.batch : 1,
+                                           d.batchStrideB, ktiles, d.bKTileStride))
+            return false;
+        return true;
+    }
+    if (!encode_operand(&d.tmA, d.rowPanel, d.nb, kdim, d.nb, d.rowEnd, d.rowPanelStride, ktiles, d.aKTileStride)) return false;
+    return encode_operand(&d.tmB, d.colPanel, d.nb, kdim, d.nb, d.colFirst + d.ncols, d.colPanelStride, ktiles,
+                          d.bKTileStride);
+}
+
+int gemm_launch(const GemmDesc& din, int nItems, int cfg, cudaStream_t stream) {
+    (void)cfg;
+    if (nItems <= 0) return 0;
+    GemmDesc d = din;
+    if (d.fast && !(d.a_kmajor && d.b_kmajor) && !prepare_tensor_maps(d)) d.fast = 0;
+    if (d.a_kmajor && d.b_kmajor)
+        gemm_dmma_kernel<CfgSmall, true, true><<<nItems, CfgSmall::THREADS, CfgSmall::smem(true, true), stream>>>(d);
+    else if (d.a_kmajor)
+        gemm_dmma_kernel<CfgSmall, true, false><<<nItems, CfgSmall::THREADS, CfgSmall::smem(true, false), stream>>>(d);
+    else if (d.b_kmajor)
+        gemm_dmma_kernel<CfgSmall, false, true><<<nItems, CfgSmall::THREADS, CfgSmall::smem(false, true), stream>>>(d);
     else
-        gemm_dmma_kernel<CfgBig, false, false><<<nItems, CfgBig::THREADS, CfgBig::SMEM, stream>>>(d);
+        gemm_dmma_kernel<CfgSmall, false, false><<<nItems, CfgSmall::THREADS, CfgSmall::SMEM, stream>>>(d);
     return (int)cudaGetLastError();
 }
 

@@ -9,9 +9,12 @@
 // FP64 has no tcgen05 / TMEM kind on sm_100a: the FP64 tensor path is the warp-level
 // mma.sync.m8n8k4.f64 (SASS DMMA.8x8x4) with register accumulators.  The kernel is therefore
 // an Ampere-style register-tiled GEMM fed by a Blackwell-style pipeline: one producer warp
-// stages operand panels into shared memory with cp.async.bulk (SASS UBLKCP, the non-tensor
-// TMA path) completing on mbarriers; consumer warps wait on the full barrier, run DMMA from
-// conflict-free padded shared-memory rows, and release stages through empty barriers.
+// stages operand panels into shared memory with the TMA engine -- tensor-map tile copies
+// (cp.async.bulk.tensor.4d, SASS UTMALDG) for operands stored M-major, 1-D bulk copies
+// (cp.async.bulk, SASS UBLKCP) for operands stored K-major -- completing on mbarriers; consumer
+// warps wait on the full barrier, run DMMA from conflict-free shared-memory layouts with
+// register-double-buffered fragments (the loads of the next k-step, and of the next stage, are
+// in flight while the current DMMAs issue), and release stages through empty barriers.
 //
 // Operand form is "NT": C[i][j] (+)= sum_k A[i][k] * B[j][k], A and B column-major with the
 // contraction index as the slow dimension (a column of A is contiguous) -- exactly the
@@ -19,6 +22,7 @@
 // i.e. A^T stored column-major) are supported by a transposing producer for the upper /
 // solve variants.
 #pragma once
+#include <cuda.h>  // CUtensorMap (types only: the encoder is resolved through cudaGetDriverEntryPoint)
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -36,7 +40,8 @@ struct GemmDesc {
     // common
     double alpha, beta;  // C = beta*C + alpha*A*B^T
     int K;               // contraction length
-    int fast;            // 1: 16B-aligned bulk-copy producer; 0: element-wise producer
+    int fast;            // 1: TMA producer (operands 16 B aligned, even leading dimensions / strides; K-major
+                         //    operands additionally K % 16 == 0); 0: element-wise producer
     int preload;         // 1: accumulators start as (beta/alpha)*C (hides the C read; sums into |C|-sized
                          //    accumulators, so only for tiles whose entries are of the size of the products);
                          // 0: BLAS order: product accumulated on its own, C = beta*C + alpha*acc in the epilogue
@@ -73,6 +78,9 @@ struct GemmDesc {
     int rowFirst[kMaxCols];   // per column: first local tile row with global m >= global n
     int rowEnd;               // local tile rows end (exclusive)
     int itemStart[kMaxCols + 1];  // prefix sum of work items (CTA tiles) per column
+    // ---- tensor maps of the M-major operands (fast mode): 4-D views {rows, k, tile | batch, k-tile}
+    alignas(64) CUtensorMap tmA;
+    alignas(64) CUtensorMap tmB;
 };
 
 // ---------------------------------------------------------------------------------------
@@ -113,6 +121,27 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
         "l"(src), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
 }
+// 4-D tensor-map tile copy global -> shared (SASS UTMALDG); out-of-bounds parts of the box arrive as zeros
+__device__ __forceinline__ void tma_g2s_4d(void* dst, const CUtensorMap* tm, int c0, int c1, int c2, int c3,
+                                           uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+// 16-byte shared-memory load.  volatile: the consumer loop is software-pipelined by hand and the order of
+// loads, DMMAs and barrier operations written in the source is the order that must reach the SASS.
+__device__ __forceinline__ void lds128(double& x, double& y, uint32_t addr) {
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(addr));
+}
+__device__ __forceinline__ void lds64(double& x, uint32_t addr) {
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x) : "r"(addr));
+}
+// s * x for s = +1 / -1 without the FP64 pipe (which the DMMAs of the co-resident CTAs keep busy): sign-bit flip
+__device__ __forceinline__ double flip_sign(double x, unsigned flip) {
+    return __hiloint2double(__double2hiint(x) ^ (int)flip, __double2loint(x));
+}
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
     // volatile: keeps every DMMA ordered against the (volatile) mbarrier waits/arrives, see the
     // stage-release note in the consumer loop
@@ -124,40 +153,50 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
 // ---------------------------------------------------------------------------------------
 // Tile configuration
 // ---------------------------------------------------------------------------------------
-template <int BM_, int BN_, int WM_, int STAGES_, int MINB_>
+template <int BM_, int BN_, int STAGES_, int MINB_>
 struct GemmCfg {
-    static constexpr int BM = BM_, BN = BN_, BK = 16, WM = WM_, WN = 32, STAGES = STAGES_, MINB = MINB_;
+    static constexpr int BM = BM_, BN = BN_, BK = 16, WM = 32, WN = 32, STAGES = STAGES_, MINB = MINB_;
     static constexpr int MF = WM / 8, NF = WN / 8;  // 8x8 fragments per warp tile
     static constexpr int WARPS_M = BM / WM, WARPS_N = BN / WN;
     static constexpr int CONSUMER_WARPS = WARPS_M * WARPS_N;
     static constexpr int THREADS = (CONSUMER_WARPS + 1) * 32;
-    // Padded shared-memory row strides (doubles), chosen so the fragment loads below are
-    // bank-conflict free: LDS.128 of 8 contiguous doubles/thread needs stride = 2 (mod 16);
-    // the paired 2+2 layout needs stride = 4 (mod 16).
-    static constexpr int LDA_S = (WM == 64) ? BM + 2 : BM + 4;
-    static constexpr int LDB_S = BN + 4;
+    // M-major operands are staged in blocks of 16 rows: [rows / 16][BK][16 doubles], one TMA box {16 rows, BK}
+    // per block, written with the 128-byte swizzle (the 16-byte chunk j of k-row r lands at chunk j ^ (r & 7)).
+    // A fragment load is one LDS.128 per lane -- two adjacent rows at one k -- and with the row-pair
+    // permutation pair_of() below the 8 lanes of every quarter-warp hit 8 different 16-byte bank groups.
+    static constexpr int MBLK = 16;
+    static constexpr int MBLK_BYTES = MBLK * BK * 8;  // 2048: a multiple of the 1024-byte swizzle period
     // K-major operands are staged as [row][LDK]: one 128 B bulk copy per operand row, natural
     // fragment rows (8f + g), LDS.64 conflict-free for LDK = 4 (mod 16)
     static constexpr int LDK = BK + 4;
-    __host__ __device__ static constexpr int a_stage(bool ak) { return ak ? BM * LDK : BK * LDA_S; }  // doubles
-    __host__ __device__ static constexpr int b_stage(bool bk) { return bk ? BN * LDK : BK * LDB_S; }
+    __host__ __device__ static constexpr int a_stage(bool ak) { return ak ? BM * LDK : BM * BK; }  // doubles
+    __host__ __device__ static constexpr int b_stage(bool bk) { return bk ? BN * LDK : BN * BK; }
+    // + 1024: the kernel rounds the dynamic shared-memory base up to the swizzle period
     __host__ __device__ static constexpr size_t smem(bool ak, bool bk) {
-        return (size_t)STAGES * (a_stage(ak) + b_stage(bk)) * 8 + 2 * STAGES * 8 + 16;
+        return (size_t)STAGES * (a_stage(ak) + b_stage(bk)) * 8 + 2 * STAGES * 8 + 16 + 1024;
     }
     static constexpr size_t SMEM = smem(false, false);
+    static_assert((BM * BK * 8) % 1024 == 0 && (BM * LDK * 8) % 1024 == 0 && (BN * BK * 8) % 1024 == 0 &&
+                      (BN * LDK * 8) % 1024 == 0, "stage bases must keep the 1024-byte swizzle alignment");
 };
-using CfgBig = GemmCfg<128, 128, 64, 4, 1>;   // 8 consumer warps, 64x32 warp tiles, 134 KB smem, 1 CTA/SM
-using CfgWide = GemmCfg<128, 64, 64, 4, 2>;   // 4 consumer warps, 64x32 warp tiles, 101 KB smem, 2 CTAs/SM
-using CfgSmall = GemmCfg<64, 64, 32, 4, 3>;   // 4 consumer warps, 32x32 warp tiles, 70 KB smem, 3 CTAs/SM
-enum GemmCfgId : int { CFG_BIG = 0, CFG_WIDE = 1, CFG_SMALL = 2 };
+// 4 consumer warps, 32x32 warp tiles, 66 KB smem, 3 CTAs/SM: co-resident CTAs hide each other's prologue and
+// epilogue (measured in round 1 against 128x128 and 128x64 CTA tiles at 1-2 CTAs/SM: 34.9 vs 32.6 / 32.3 TFLOP/s)
+using CfgSmall = GemmCfg<64, 64, 4, 3>;
+enum GemmCfgId : int { CFG_SMALL = 2 };
 
-// row (within the warp tile) of fragment f, fragment-row g
+// Row pair (rows 2p, 2p+1 of a 16-row block) that fragment-row g of an m8n8k4 operand stands for.  Any
+// permutation is legal as long as A, B and C agree; this one sends the two fragment rows that share a
+// quarter-warp (g = 2q, 2q+1) to pairs 4 apart, which the swizzle then keeps on different bank groups
+// for all four k-rows of a k-step.
+__host__ __device__ __forceinline__ constexpr int pair_of(int g) { return (g >> 1) | ((g & 1) << 2); }
+// row (within the warp tile) of M-major fragment f for fragment-row g: 2 adjacent rows, 16 apart per pair
+__device__ __forceinline__ int mrow(int g, int f) { return 2 * pair_of(g) + (f & 1) + 16 * (f >> 1); }
+// fragment maps of the kernels that keep their own padded staging (kernels.cu)
 template <int WM>
 __device__ __forceinline__ int frag_row(int g, int f) {
     if (WM == 64) return 8 * g + f;               // thread owns 8 contiguous rows
     return 2 * g + (f & 1) + 16 * (f >> 1);       // thread owns 2+2 rows, 16 apart
 }
-// column (within the 32-wide warp tile) for B fragment f and fragment-col g
 __device__ __forceinline__ int frag_col(int g, int f) { return 2 * g + (f & 1) + 16 * (f >> 1); }
 
 struct BlockWork {
@@ -168,6 +207,7 @@ struct BlockWork {
     int lda, ldb, ldc;
     int lower;       // mask: write only gi >= gj
     int gi0, gj0;    // global (within-problem) offsets of this CTA tile for the mask
+    int aRow, aTile, bRow, bTile;  // tensor-map coordinates of the operand blocks: first row, tile | batch index
     bool valid;
 };
 
@@ -193,6 +233,8 @@ __device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
         w.C = d.C + (size_t)bt * d.batchStrideC + i0 + (size_t)j0 * d.ldc;
         w.lower = d.lower;
         w.gi0 = d.rowOff + i0; w.gj0 = d.colOff + j0;
+        w.aRow = i0; w.aTile = (d.batchStrideA != 0) ? bt : 0;  // stride 0: one operand shared by the whole batch
+        w.bRow = j0; w.bTile = (d.batchStrideB != 0) ? bt : 0;
         if (d.lower == 1 && (w.gi0 + w.M - 1 < w.gj0)) w.valid = false;  // entirely above diagonal
         if (d.lower == 2 && (w.gj0 + w.N - 1 < w.gi0)) w.valid = false;  // entirely below diagonal
         return w;
@@ -224,6 +266,7 @@ __device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
     w.C = d.Cbase + ((size_t)i + (size_t)j * d.tileLdT) * d.tileElems + i0 + (size_t)j0 * d.nb;
     w.lower = (gm == gn);
     w.gi0 = i0; w.gj0 = j0;
+    w.aRow = i0; w.aTile = i; w.bRow = j0; w.bTile = j;
     if (w.lower && (i0 + w.M - 1 < j0)) w.valid = false;
     return w;
 }
@@ -234,9 +277,11 @@ __device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
 template <class Cfg, bool AK, bool BKM>
 __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(const __grid_constant__ GemmDesc d) {
     constexpr int BM = Cfg::BM, BN = Cfg::BN, BK = Cfg::BK, STAGES = Cfg::STAGES;
-    constexpr int LDA_S = Cfg::LDA_S, LDB_S = Cfg::LDB_S, MF = Cfg::MF, NF = Cfg::NF, LDK = Cfg::LDK;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int MF = Cfg::MF, NF = Cfg::NF, LDK = Cfg::LDK, MBB = Cfg::MBLK_BYTES;
+    extern __shared__ unsigned char smem_dyn[];
     constexpr int A_STAGE = Cfg::a_stage(AK), B_STAGE = Cfg::b_stage(BKM);
+    // the swizzle of the TMA engine is a function of the shared-memory address bits: 1024-byte aligned stages
+    unsigned char* smem_raw = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
     double* sA = reinterpret_cast<double*>(smem_raw);
     double* sB = sA + (size_t)STAGES * A_STAGE;
     uint64_t* full = reinterpret_cast<uint64_t*>(sB + (size_t)STAGES * B_STAGE);
@@ -259,10 +304,12 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
 
     if (warp == Cfg::CONSUMER_WARPS) {
         // ============================ producer warp ============================
-        // bulk (TMA) producer needs 16 B alignment: host-checked strides/pointers, K % 16 == 0, and an
-        // even row count for M-major operands (their rows are copied as one contiguous run)
-        const bool fast = d.fast && (AK || !(w.M & 1)) && (BKM || !(w.N & 1));
-        const int nA = AK ? w.M : BK, nB = BKM ? w.N : BK;  // bulk copies per stage
+        const bool fast = d.fast != 0;
+        const int nBoxA = (w.M + Cfg::MBLK - 1) / Cfg::MBLK, nBoxB = (w.N + Cfg::MBLK - 1) / Cfg::MBLK;
+        // what one stage brings in: whole boxes for the tensor-map copies (out-of-bounds parts count, they
+        // arrive as zeros), 128-byte rows for the K-major bulk copies
+        const uint32_t txBytes = (uint32_t)((AK ? w.M * BK * 8 : nBoxA * MBB) + (BKM ? w.N * BK * 8 : nBoxB * MBB));
+        const int nA = AK ? w.M : nBoxA, nB = BKM ? w.N : nBoxB;  // copies per stage
         for (int c = 0; c < nChunks; c++) {
             const int s = c % STAGES;
             const uint32_t ph = (c / STAGES) & 1;
@@ -272,23 +319,24 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
             const int kk0 = c * BK;
             const int kt = kk0 / d.kTile, kin = kk0 - kt * d.kTile;
             if (fast) {
-                // K % 16 == 0 and kTile % 16 == 0 are guaranteed by the host in fast mode.
-                if (lane == 0) mbar_expect_tx(&full[s], (uint32_t)((w.M + w.N) * BK * 8));
+                if (lane == 0) mbar_expect_tx(&full[s], txBytes);
                 __syncwarp();
                 const double* Ab = w.A + (size_t)kt * d.aKTileStride;
                 const double* Bb = w.B + (size_t)kt * d.bKTileStride;
                 for (int q = lane; q < nA + nB; q += 32) {
                     if (q < nA) {
                         if (AK) bulk_g2s(dA + q * LDK, Ab + kin + (size_t)q * w.lda, BK * 8, &full[s]);
-                        else bulk_g2s(dA + q * LDA_S, Ab + (size_t)(kin + q) * w.lda, (uint32_t)w.M * 8, &full[s]);
+                        else tma_g2s_4d(reinterpret_cast<unsigned char*>(dA) + q * MBB, &d.tmA, w.aRow + q * Cfg::MBLK, kin,
+                                        w.aTile, kt, &full[s]);
                     } else {
                         const int r = q - nA;
                         if (BKM) bulk_g2s(dB + r * LDK, Bb + kin + (size_t)r * w.ldb, BK * 8, &full[s]);
-                        else bulk_g2s(dB + r * LDB_S, Bb + (size_t)(kin + r) * w.ldb, (uint32_t)w.N * 8, &full[s]);
+                        else tma_g2s_4d(reinterpret_cast<unsigned char*>(dB) + r * MBB, &d.tmB, w.bRow + r * Cfg::MBLK, kin,
+                                        w.bTile, kt, &full[s]);
                     }
                 }
             } else {
-                // generic producer: element loads with zero fill (odd sizes, unaligned operands)
+                // generic producer: element loads with zero fill (unaligned operands), same shared-memory layouts
                 for (int r = 0; r < BK; r++) {
                     const int kk = kk0 + r;
                     const bool kin_range = kk < d.K;
@@ -298,14 +346,14 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
                         if (kin_range && i < w.M)
                             v = AK ? w.A[(size_t)kt2 * d.aKTileStride + kin2 + (size_t)i * w.lda]
                                    : w.A[(size_t)kt2 * d.aKTileStride + (size_t)kin2 * w.lda + i];
-                        dA[AK ? i * LDK + r : r * LDA_S + i] = v;
+                        dA[AK ? i * LDK + r : ((i >> 4) * BK + r) * 16 + ((((i & 15) >> 1) ^ (r & 7)) << 1) + (i & 1)] = v;
                     }
                     for (int j = lane; j < BN; j += 32) {
                         double v = 0.0;
                         if (kin_range && j < w.N)
                             v = BKM ? w.B[(size_t)kt2 * d.bKTileStride + kin2 + (size_t)j * w.ldb]
                                     : w.B[(size_t)kt2 * d.bKTileStride + (size_t)kin2 * w.ldb + j];
-                        dB[BKM ? j * LDK + r : r * LDB_S + j] = v;
+                        dB[BKM ? j * LDK + r : ((j >> 4) * BK + r) * 16 + ((((j & 15) >> 1) ^ (r & 7)) << 1) + (j & 1)] = v;
                     }
                 }
                 __syncwarp();
@@ -322,19 +370,22 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
 
     // Accumulators start as (beta/alpha)*C: the read of C overlaps the pipeline fill instead of
     // sitting, un-overlapped, in the epilogue; the epilogue only stores alpha*acc.
-    // thread holds, for fragment (i,j): rows wm0+frag_row(g,i); columns wn0+frag_col(2t,j) and
-    // wn0+frag_col(2t+1,j)   (the C fragment's column index plays the role of B's g)
+    // thread holds, for fragment (i,j): row crow(i); columns ccol(2t, j) and ccol(2t+1, j)
+    // (the C fragment's column index plays the role of B's fragment row g)
     const double alpha = d.alpha, beta = d.beta;
     // diagonal (SYRK) tiles carry the large diagonal entries of the matrix: never preload those
     const bool pre = d.preload && (w.lower == 0);
     const double cscale = (beta == 0.0 || !pre) ? 0.0 : beta / alpha;
     const double ebeta = pre ? 0.0 : beta;  // what the epilogue still has to add
-    constexpr int RUN = (Cfg::WM == 64) ? 8 : 2;  // contiguous rows a thread owns per fragment group
+    // the trailing update has alpha = -1, beta = 1: scaling by +-1 is a sign flip on the integer pipe, so the
+    // prologue and epilogue of this CTA do not queue FP64 instructions behind the DMMAs of its neighbours
+    const bool unitScale = (alpha == 1.0 || alpha == -1.0) && (cscale == 1.0 || cscale == -1.0 || cscale == 0.0);
+    const unsigned preFlip = (cscale < 0.0) ? 0x80000000u : 0u, postFlip = (alpha < 0.0) ? 0x80000000u : 0u;
     const bool vec = !AK && (w.M == BM) && (w.N == BN) && (w.lower == 0) && ((w.ldc & 1) == 0) &&
                      ((reinterpret_cast<uintptr_t>(w.C) & 15) == 0);
     // fragment -> tile coordinates (K-major operands use the natural 8f+g fragment rows)
-    auto crow = [&](int i) { return wm0 + (AK ? 8 * i + g : frag_row<Cfg::WM>(g, i)); };
-    auto ccol = [&](int c, int j) { return wn0 + (BKM ? 8 * j + c : frag_col(c, j)); };
+    auto crow = [&](int i) { return wm0 + (AK ? 8 * i + g : mrow(g, i)); };
+    auto ccol = [&](int c, int j) { return wn0 + (BKM ? 8 * j + c : mrow(c, j)); };
     double acc[MF][NF][2];
     if (cscale == 0.0) {
 #pragma unroll
@@ -349,9 +400,14 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
                 const double* cp = w.C + (size_t)ccol(2 * t + h, j) * w.ldc + wm0;
 #pragma unroll
                 for (int i = 0; i < MF; i += 2) {
-                    const double2 x = *reinterpret_cast<const double2*>(cp + frag_row<Cfg::WM>(g, i));
-                    acc[i][j][h] = cscale * x.x;
-                    acc[i + 1][j][h] = cscale * x.y;
+                    const double2 x = *reinterpret_cast<const double2*>(cp + mrow(g, i));
+                    if (unitScale) {
+                        acc[i][j][h] = flip_sign(x.x, preFlip);
+                        acc[i + 1][j][h] = flip_sign(x.y, preFlip);
+                    } else {
+                        acc[i][j][h] = cscale * x.x;
+                        acc[i + 1][j][h] = cscale * x.y;
+                    }
                 }
             }
     } else {
@@ -372,58 +428,74 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
                 }
             }
     }
-    (void)RUN;
 
-    // per-thread fragment base offsets inside a stage
-    const int aoff = AK ? (wm0 + g) * LDK + t : ((Cfg::WM == 64) ? (wm0 + 8 * g) : (wm0 + 2 * g));
-    const int boff = BKM ? (wn0 + g) * LDK + t : wn0 + 2 * g;
-
-    for (int c = 0; c < nChunks; c++) {
-        const int s = c % STAGES;
-        mbar_wait(&full[s], (c / STAGES) & 1);
-        // Release the PREVIOUS stage only now.  An arrive issued straight after the last LDS of a
-        // chunk can overtake that load (the arrive does not wait for the LDS scoreboard) and let
-        // the producer's bulk copy overwrite the stage under it.  Behind the spin-wait above, every
-        // DMMA of chunk c-1 -- and therefore every LDS feeding it -- has been issued and completed.
-        if (c > 0 && lane == 0) mbar_arrive(&empty[(c - 1) % STAGES]);
-        const double* pA = sA + (size_t)s * A_STAGE + aoff;
-        const double* pB = sB + (size_t)s * B_STAGE + boff;
+    // ---- fragment loads: per-thread byte offsets inside a stage, everything else is an immediate ----
+    // M-major (swizzled blocks): k-row 4ks+t, chunk pair_of(g) ^ ((4ks+t) & 7); the chunk of odd ks differs from the
+    // chunk of even ks in bit 2 only.  K-major: row 8v+g, k = 4ks+t.
+    const uint32_t aE = AK ? (uint32_t)((wm0 + g) * LDK + t) * 8u
+                           : (uint32_t)((wm0 / Cfg::MBLK) * MBB + t * 128 + ((pair_of(g) ^ t) << 4));
+    const uint32_t bE = BKM ? (uint32_t)((wn0 + g) * LDK + t) * 8u
+                            : (uint32_t)((wn0 / Cfg::MBLK) * MBB + t * 128 + ((pair_of(g) ^ t) << 4));
+    const uint32_t aO = AK ? aE : (aE ^ 64u), bO = BKM ? bE : (bE ^ 64u);
+    auto load_frags = [&](double (&a)[MF], double (&b)[NF], uint32_t stA, uint32_t stB, int ks) {
+        const uint32_t pa = stA + ((ks & 1) ? aO : aE), pb = stB + ((ks & 1) ? bO : bE);
+        if (AK) {
 #pragma unroll
-        for (int ks = 0; ks < BK / 4; ks++) {
-            double a[MF], b[NF];
-            const double* ra = AK ? pA + ks * 4 : pA + (ks * 4 + t) * LDA_S;
-            const double* rb = BKM ? pB + ks * 4 : pB + (ks * 4 + t) * LDB_S;
-            if (AK) {
+            for (int v = 0; v < MF; v++) lds64(a[v], pa + (uint32_t)(v * 8 * LDK + ks * 4) * 8u);
+        } else {
 #pragma unroll
-                for (int v = 0; v < MF; v++) a[v] = ra[v * 8 * LDK];
-            } else if (Cfg::WM == 64) {
-#pragma unroll
-                for (int v = 0; v < 4; v++) {
-                    double2 x = *reinterpret_cast<const double2*>(ra + 2 * v);
-                    a[2 * v] = x.x; a[2 * v + 1] = x.y;
-                }
-            } else {
-#pragma unroll
-                for (int v = 0; v < MF / 2; v++) {
-                    double2 x = *reinterpret_cast<const double2*>(ra + 16 * v);
-                    a[2 * v] = x.x; a[2 * v + 1] = x.y;
-                }
-            }
-            if (BKM) {
-#pragma unroll
-                for (int v = 0; v < NF; v++) b[v] = rb[v * 8 * LDK];
-            } else {
-#pragma unroll
-                for (int v = 0; v < NF / 2; v++) {
-                    double2 x = *reinterpret_cast<const double2*>(rb + 16 * v);
-                    b[2 * v] = x.x; b[2 * v + 1] = x.y;
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < MF; i++)
-#pragma unroll
-                for (int j = 0; j < NF; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+            for (int v = 0; v < MF / 2; v++) lds128(a[2 * v], a[2 * v + 1], pa + (uint32_t)(v * MBB + ks * 512));
         }
+        if (BKM) {
+#pragma unroll
+            for (int v = 0; v < NF; v++) lds64(b[v], pb + (uint32_t)(v * 8 * LDK + ks * 4) * 8u);
+        } else {
+#pragma unroll
+            for (int v = 0; v < NF / 2; v++) lds128(b[2 * v], b[2 * v + 1], pb + (uint32_t)(v * MBB + ks * 512));
+        }
+    };
+    auto mma_all = [&](const double (&a)[MF], const double (&b)[NF]) {
+#pragma unroll
+        for (int i = 0; i < MF; i++)
+#pragma unroll
+            for (int j = 0; j < NF; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+    };
+
+    // ---- main loop, software-pipelined by hand: while the DMMAs of one k-step issue, the fragments of the next
+    // k-step -- across the stage boundary too -- are already on their way from shared memory, so a warp never sits
+    // at the top of a stage with an empty DMMA queue (with three warps per scheduler marching in step, that idle
+    // gap was the 8 % the first version of this kernel lost) ----
+    constexpr uint32_t A_BYTES = A_STAGE * 8, B_BYTES = B_STAGE * 8;
+    const uint32_t sA0 = smem_u32(sA), sB0 = smem_u32(sB);
+    uint32_t stA = sA0, stB = sB0;
+    int s = 0;
+    uint32_t ph = 0;
+    double a0[MF], b0[NF], a1[MF], b1[NF];
+    if (nChunks > 0) {
+        mbar_wait(&full[0], 0);
+        load_frags(a0, b0, stA, stB, 0);
+    }
+    for (int c = 0; c < nChunks; c++) {
+        int ns = s + 1;
+        uint32_t nA = stA + A_BYTES, nB = stB + B_BYTES, nph = ph;
+        if (ns == STAGES) { ns = 0; nA = sA0; nB = sB0; nph ^= 1; }
+#pragma unroll
+        for (int ks = 0; ks < BK / 4; ks += 2) {
+            load_frags(a1, b1, stA, stB, ks + 1);
+            mma_all(a0, b0);
+            if (ks + 2 < BK / 4) {
+                load_frags(a0, b0, stA, stB, ks + 2);
+            } else if (c + 1 < nChunks) {
+                mbar_wait(&full[ns], nph);
+                load_frags(a0, b0, nA, nB, 0);
+            }
+            mma_all(a1, b1);
+        }
+        // Every LDS of this stage has fed a DMMA that has been issued (in-order issue, and all of these are
+        // volatile asm: the compiler keeps the order written here), so the stage can go back to the producer.
+        // An arrive placed right after the last LDS instead could overtake that load (round-1 finding).
+        if (lane == 0) mbar_arrive(&empty[s]);
+        s = ns; stA = nA; stB = nB; ph = nph;
     }
 
     // ================================ epilogue ================================
@@ -436,14 +508,19 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
 #pragma unroll
                 for (int i = 0; i < MF; i += 2) {
                     double2 x;
-                    x.x = alpha * acc[i][j][h];
-                    x.y = alpha * acc[i + 1][j][h];
+                    if (unitScale) {
+                        x.x = flip_sign(acc[i][j][h], postFlip);
+                        x.y = flip_sign(acc[i + 1][j][h], postFlip);
+                    } else {
+                        x.x = alpha * acc[i][j][h];
+                        x.y = alpha * acc[i + 1][j][h];
+                    }
                     if (ebeta != 0.0) {
-                        const double2 c0 = *reinterpret_cast<const double2*>(cp + frag_row<Cfg::WM>(g, i));
+                        const double2 c0 = *reinterpret_cast<const double2*>(cp + mrow(g, i));
                         x.x += ebeta * c0.x;
                         x.y += ebeta * c0.y;
                     }
-                    *reinterpret_cast<double2*>(cp + frag_row<Cfg::WM>(g, i)) = x;
+                    *reinterpret_cast<double2*>(cp + mrow(g, i)) = x;
                 }
             }
         return;

@@ -21,6 +21,19 @@ constexpr int IB = 64;  // leaf block of the in-tile recursion (diagonal blocks 
         }                                                                                    \
     } while (0)
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-DEVICE setting: a process that drives several
+// GPUs (one context per device, or the allocation-free tile entry called on each) needs it once per device.
+#define DPB_SMEM_OPT_IN(kernel, bytes)                                                                        \
+    do {                                                                                                      \
+        static bool done__[64] = {false};                                                                     \
+        int dev__ = 0;                                                                                        \
+        DPB_CUDA(cudaGetDevice(&dev__));                                                                      \
+        if (!done__[dev__ & 63]) {                                                                            \
+            DPB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            done__[dev__ & 63] = true;                                                                        \
+        }                                                                                                     \
+    } while (0)
+
 // Working layout in HBM: the regular local tile grid of a 2D block-cyclic matrix.
 // Local tile (il, jl) <-> global tile (il*P + prow, jl*Q + pcol); tile at
 // base + (il + jl*lmt) * tileElems, column-major, leading dimension mb.
@@ -32,8 +45,13 @@ struct DevMatrix {
     int lmt = 0, lnt = 0;  // local tile rows / cols
     int M = 0, N = 0;      // global size
     int mt = 0, nt = 0;    // global tile counts
-    int P = 1, Q = 1, prow = 0, pcol = 0;
+    int P = 1, Q = 1, prow = 0, pcol = 0;  // prow / pcol are LOGICAL grid coordinates: tile (0,0) lives on (0,0)
+    int ip = 0, jq = 0;    // physical grid coordinates owning tile (0,0) (ScaLAPACK RSRC / CSRC)
     bool owned = false;    // staged copy allocated by the library
+    // host-side only: where the (sub)matrix sits inside the caller's local array.  A tile-aligned submatrix
+    // A(i:i+m, j:j+n) of a block-cyclic parent is itself block-cyclic with the source process shifted by
+    // (i/mb, j/nb); its local tile (il, jl) is the parent's local tile (il + offR, jl + offC).
+    int offR = 0, offC = 0, userLmt = 0;
     __host__ __device__ double* tile(int il, int jl) const { return base + ((size_t)il + (size_t)jl * lmt) * tileElems; }
     __host__ __device__ int rowsOfTile(int gm) const { return gm == mt - 1 ? M - gm * mb : mb; }
     __host__ __device__ int colsOfTile(int gn) const { return gn == nt - 1 ? N - gn * nb : nb; }
@@ -86,7 +104,7 @@ struct parsec_context_s {
     void* commWorld = nullptr;
     void* commRow = nullptr;
     void* commCol = nullptr;
-    int gridP = 0, gridQ = 0;
+    int gridP = 0, gridQ = 0, gridIp = 0, gridJq = 0;
     parsec_taskpool_s* curTp = nullptr;  // taskpool being enqueued (for early write-back of finished columns)
     int earlyOut = 0;                    // columns of curTp already written back by the copy stream
     std::vector<cudaEvent_t> evIn;       // per local tile column: its host-to-device copy has landed (pipelined stage-in)
@@ -97,6 +115,7 @@ struct parsec_context_s {
     int profile = 0;
     std::vector<cudaEvent_t> profEv;   // pairs (start, stop)
     std::vector<double> profFlops;
+    std::vector<int> profStream;       // 1: launched on the update stream (bulk), 0: panel stream
 };
 
 namespace dpb {
@@ -125,6 +144,7 @@ int launch_absmax(parsec_context_s* ctx, cudaStream_t s, const double* v, long l
 int launch_copy_tril(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst, int ldd,
                      int n, int uplo, int symmetrize);
 int launch_fill(parsec_context_s* ctx, cudaStream_t s, double* p, long long n, double v);
+int launch_scale_tile(parsec_context_s* ctx, cudaStream_t s, double* C, int ldc, int m, int n, double beta, int part);
 int launch_trtri_leaf(parsec_context_s* ctx, cudaStream_t s, const double* A, int lda, int n, int uplo, int unit,
                       double* winv);
 int launch_trtri_blocks(parsec_context_s* ctx, cudaStream_t s, const double* T, int ldt, int n, int uplo, int unit,
@@ -169,7 +189,9 @@ int p2p_send(parsec_context_s* ctx, const double* buf, size_t count, int peer, c
 int p2p_recv(parsec_context_s* ctx, double* buf, size_t count, int peer, cudaStream_t s);
 int group_start(parsec_context_s* ctx);
 int group_end(parsec_context_s* ctx);
-int ensure_grid_comms(parsec_context_s* ctx, int P, int Q);
+int ensure_grid_comms(parsec_context_s* ctx, int P, int Q, int ip = 0, int jq = 0);
+// world rank of the process at LOGICAL grid coordinates (lr, lc) of A's distribution
+inline int world_rank_of(const DevMatrix& A, int lr, int lc) { return ((lr + A.ip) % A.P) * A.Q + (lc + A.jq) % A.Q; }
 void comm_destroy(parsec_context_s* ctx);
 // potrf_dist.cu
 int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T, int uplo, const DevMatrix& Tt);

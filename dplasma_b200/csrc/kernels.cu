@@ -282,12 +282,8 @@ __global__ void __launch_bounds__(256) trtri_blocks_kernel(const double* __restr
 int launch_trtri_blocks(parsec_context_s* ctx, cudaStream_t s, const double* T, int ldt, int n, int uplo, int unit,
                         double* winv) {
     if (n <= 0) return 0;
-    static bool attr = false;
     const int smem = 2 * IB * LEAF_LD * (int)sizeof(double);
-    if (!attr) {
-        DPB_CUDA(cudaFuncSetAttribute(trtri_blocks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr = true;
-    }
+    DPB_SMEM_OPT_IN(trtri_blocks_kernel, smem);
     trtri_blocks_kernel<<<(n + IB - 1) / IB, 256, smem, s>>>(T, ldt, n, uplo, unit, winv);
     ctx->launches++;
     return (int)cudaGetLastError();
@@ -295,12 +291,8 @@ int launch_trtri_blocks(parsec_context_s* ctx, cudaStream_t s, const double* T, 
 
 int launch_trtri_leaf(parsec_context_s* ctx, cudaStream_t s, const double* A, int lda, int n, int uplo, int unit,
                       double* winv) {
-    static bool attr = false;
     const int smem = 2 * IB * LEAF_LD * (int)sizeof(double);
-    if (!attr) {
-        DPB_CUDA(cudaFuncSetAttribute(trtri_leaf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr = true;
-    }
+    DPB_SMEM_OPT_IN(trtri_leaf_kernel, smem);
     trtri_leaf_kernel<<<1, 256, smem, s>>>(A, lda, n, uplo, unit, winv);
     ctx->launches++;
     return (int)cudaGetLastError();
@@ -531,11 +523,7 @@ int launch_potrf_diag_writeback(parsec_context_s* ctx, cudaStream_t s, double* A
 
 int launch_potrf_colblock(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, int j0, double* winv,
                           double* wdiag, int* dInfo, int infoBase) {
-    static bool attr = false;
-    if (!attr) {
-        DPB_CUDA(cudaFuncSetAttribute(potrf_colblock_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PC_SMEM));
-        attr = true;
-    }
+    DPB_SMEM_OPT_IN(potrf_colblock_kernel, PC_SMEM);
     const int nblk = (n - j0 + IB - 1) / IB;
     potrf_colblock_kernel<<<nblk, 256, PC_SMEM, s>>>(A, lda, n, j0, winv, wdiag, dInfo, infoBase);
     ctx->launches++;
@@ -712,12 +700,8 @@ __global__ void __launch_bounds__(256) ztrtri_blocks_kernel(const double* __rest
 int launch_ztrtri_blocks(parsec_context_s* ctx, cudaStream_t s, const double* T, int ldt, int n, double* winv,
                          double* winvT) {
     if (n <= 0) return 0;
-    static bool attr = false;
     const int smem = 4 * IB * LEAF_LD * (int)sizeof(double);
-    if (!attr) {
-        DPB_CUDA(cudaFuncSetAttribute(ztrtri_blocks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr = true;
-    }
+    DPB_SMEM_OPT_IN(ztrtri_blocks_kernel, smem);
     ztrtri_blocks_kernel<<<(n + IB - 1) / IB, 256, smem, s>>>(T, ldt, n, winv, winvT);
     ctx->launches++;
     return (int)cudaGetLastError();
@@ -725,12 +709,8 @@ int launch_ztrtri_blocks(parsec_context_s* ctx, cudaStream_t s, const double* T,
 
 int launch_zpotrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv, int* dInfo,
                        int infoBase) {
-    static bool attr = false;
     const int smem = 4 * IB * LEAF_LD * (int)sizeof(double);
-    if (!attr) {
-        DPB_CUDA(cudaFuncSetAttribute(zpotrf_leaf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr = true;
-    }
+    DPB_SMEM_OPT_IN(zpotrf_leaf_kernel, smem);
     zpotrf_leaf_kernel<<<1, 256, smem, s>>>(A, lda, n, winv, dInfo, infoBase);
     ctx->launches++;
     return (int)cudaGetLastError();
@@ -884,11 +864,7 @@ __global__ void __launch_bounds__(256) trsm_panel_fused_kernel(const double* __r
 int launch_trsm_panel_fused(parsec_context_s* ctx, cudaStream_t s, const double* L, int ldl, int n, const double* winv,
                             double* B, int ldb, long long tileStride, int rowsPerTile, int lastTileRows, int ntiles) {
     if (ntiles <= 0 || n <= 0) return 0;
-    static bool attr = false;
-    if (!attr) {
-        DPB_CUDA(cudaFuncSetAttribute(trsm_panel_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM));
-        attr = true;
-    }
+    DPB_SMEM_OPT_IN(trsm_panel_fused_kernel, TP_SMEM);
     const int spt = (rowsPerTile + IB - 1) / IB;
     trsm_panel_fused_kernel<<<ntiles * spt, 256, TP_SMEM, s>>>(L, ldl, n, winv, B, ldb, tileStride, rowsPerTile,
                                                                 lastTileRows, ntiles);
@@ -898,12 +874,8 @@ int launch_trsm_panel_fused(parsec_context_s* ctx, cudaStream_t s, const double*
 
 int launch_potrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
                       int* dInfo, int infoBase) {
-    static bool attr = false;
     const int smem = 2 * IB * LEAF_LD * (int)sizeof(double);
-    if (!attr) {
-        DPB_CUDA(cudaFuncSetAttribute(potrf_leaf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        attr = true;
-    }
+    DPB_SMEM_OPT_IN(potrf_leaf_kernel, smem);
     potrf_leaf_kernel<<<1, 256, smem, s>>>(A, lda, n, winv, dInfo, infoBase);
     ctx->launches++;
     return (int)cudaGetLastError();
@@ -1188,13 +1160,16 @@ int launch_transpose(parsec_context_s* ctx, cudaStream_t s, const double* src, i
 // tile (m,n) <-> tile (n,m)^T.  One CTA per 32x32 block pair.
 __global__ void __launch_bounds__(256) transpose_grid_kernel(DevMatrix A) {
     __shared__ double ta[32][33], tb[32][33];
-    // blockIdx.z enumerates tile pairs m >= n; x,y the 32x32 blocks of tile (m,n)
-    int pz = blockIdx.z, m = 0;
-    while ((m + 1) * (m + 2) / 2 <= pz) m++;
-    const int n = pz - m * (m + 1) / 2;
-    if (m >= A.mt || n >= A.nt) return;
+    // blockIdx.z walks the tile pairs m >= n (grid-stride: gridDim.z is capped at 65535); x,y the 32x32 blocks of tile (m,n)
+    const long long pairs = (long long)A.mt * (A.mt + 1) / 2;
     const int bi = blockIdx.x * 32, bj = blockIdx.y * 32;
-    if (m == n && bi < bj) return;
+    for (long long pz = blockIdx.z; pz < pairs; pz += gridDim.z) {
+    int m = (int)((sqrt(8.0 * (double)pz + 1.0) - 1.0) * 0.5);
+    while ((long long)(m + 1) * (m + 2) / 2 <= pz) m++;
+    while ((long long)m * (m + 1) / 2 > pz) m--;
+    const int n = (int)(pz - (long long)m * (m + 1) / 2);
+    if (m == n && bi < bj) continue;
+    __syncthreads();  // the shared tiles of the previous pair have been consumed
     double* Ta = A.tile(m, n);
     double* Tb = A.tile(n, m);
     const int ld = A.mb, nb = A.mb;
@@ -1209,16 +1184,20 @@ __global__ void __launch_bounds__(256) transpose_grid_kernel(DevMatrix A) {
         if (bj + tx < nb && bi + j < nb) Tb[(bj + tx) + (size_t)(bi + j) * ld] = ta[tx][j];
         if (bi + tx < nb && bj + j < nb) Ta[(bi + tx) + (size_t)(bj + j) * ld] = tb[tx][j];
     }
+    }
 }
 // complex variant: tile (m,n) <-> tile (n,m)^H (conjugate transpose), interleaved (re,im)
 __global__ void __launch_bounds__(256) ztranspose_grid_kernel(DevMatrix A) {
     __shared__ double2 ta[32][33], tb[32][33];
-    int pz = blockIdx.z, m = 0;
-    while ((m + 1) * (m + 2) / 2 <= pz) m++;
-    const int n = pz - m * (m + 1) / 2;
-    if (m >= A.mt || n >= A.nt) return;
+    const long long pairs = (long long)A.mt * (A.mt + 1) / 2;
     const int bi = blockIdx.x * 32, bj = blockIdx.y * 32;
-    if (m == n && bi < bj) return;
+    for (long long pz = blockIdx.z; pz < pairs; pz += gridDim.z) {
+    int m = (int)((sqrt(8.0 * (double)pz + 1.0) - 1.0) * 0.5);
+    while ((long long)(m + 1) * (m + 2) / 2 <= pz) m++;
+    while ((long long)m * (m + 1) / 2 > pz) m--;
+    const int n = (int)(pz - (long long)m * (m + 1) / 2);
+    if (m == n && bi < bj) continue;
+    __syncthreads();
     double2* Ta = reinterpret_cast<double2*>(A.tile(m, n));
     double2* Tb = reinterpret_cast<double2*>(A.tile(n, m));
     const int ld = A.mb, nb = A.mb;
@@ -1232,15 +1211,34 @@ __global__ void __launch_bounds__(256) ztranspose_grid_kernel(DevMatrix A) {
         if (bj + tx < nb && bi + j < nb) { double2 v = ta[tx][j]; v.y = -v.y; Tb[(bj + tx) + (size_t)(bi + j) * ld] = v; }
         if (bi + tx < nb && bj + j < nb) { double2 v = tb[tx][j]; v.y = -v.y; Ta[(bi + tx) + (size_t)(bj + j) * ld] = v; }
     }
+    }
 }
 int launch_transpose_grid(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A) {
     if (A.P * A.Q != 1 || A.mb != A.nb || A.mt != A.nt) return -3;
     const int nblk = (A.mb + 31) / 32;
     const long long pairs = (long long)A.mt * (A.mt + 1) / 2;
-    if (pairs > 65535) return -4;
-    dim3 grid(nblk, nblk, (unsigned)pairs);
+    dim3 grid(nblk, nblk, (unsigned)(pairs > 65535 ? 65535 : pairs));
     if (A.esz == 2) ztranspose_grid_kernel<<<grid, 256, 0, s>>>(A);
     else transpose_grid_kernel<<<grid, 256, 0, s>>>(A);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
+// C <- beta C on an m x n column-major tile (part: 0 all, 1 lower, 2 upper); beta == 0 stores zeros
+__global__ void scale_tile_kernel(double* __restrict__ C, int ldc, int m, int n, double beta, int part) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < (long long)m * n;
+         e += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(e % m), j = (int)(e / m);
+        if ((part == 1 && i < j) || (part == 2 && i > j)) continue;
+        double* c = C + i + (size_t)j * ldc;
+        *c = (beta == 0.0) ? 0.0 : beta * *c;
+    }
+}
+int launch_scale_tile(parsec_context_s* ctx, cudaStream_t s, double* C, int ldc, int m, int n, double beta, int part) {
+    if (m <= 0 || n <= 0 || beta == 1.0) return 0;
+    long long blocks = ((long long)m * n + 255) / 256;
+    if (blocks > 1184) blocks = 1184;
+    scale_tile_kernel<<<(int)blocks, 256, 0, s>>>(C, ldc, m, n, beta, part);
     ctx->launches++;
     return (int)cudaGetLastError();
 }

@@ -51,7 +51,7 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
         d.mtGlobal = C.mt; d.ntGlobal = C.nt;
         d.rowEnd = rowEnd;
         if (ctx->cplx) d.fast = (K % 8 == 0) ? 1 : 0;
-        else d.fast = ((C.nb % 2 == 0) && (K % 16 == 0) && (kTile % 16 == 0) && (kTileStride % 2 == 0) && ((reinterpret_cast<uintptr_t>(rowPanel) & 15) == 0) &&
+        else d.fast = ((C.nb % 2 == 0) && (kTile % 16 == 0) && (kTileStride % 2 == 0) && ((reinterpret_cast<uintptr_t>(rowPanel) & 15) == 0) &&
                   ((reinterpret_cast<uintptr_t>(colPanel) & 15) == 0) && (rowStride % 2 == 0) &&
                   (colStride % 2 == 0))
                      ? 1 : 0;
@@ -100,6 +100,7 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
             ctx->profEv.push_back(pe0);
             ctx->profEv.push_back(pe1);
             ctx->profFlops.push_back(fl);
+            ctx->profStream.push_back(s == ctx->sUpdate ? 1 : 0);
         }
         if (rc) return rc;
     }
@@ -262,7 +263,7 @@ int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp) {
     if (A.P * A.Q != 1) {
         // grid: factor the distributed transpose as a lower problem, transpose the factor back
         if (A.P * A.Q != ctx->nranks) return -303;
-        int rc = ensure_grid_comms(ctx, A.P, A.Q);
+        int rc = ensure_grid_comms(ctx, A.P, A.Q, A.ip, A.jq);
         DevMatrix W;
         if (!rc) rc = alloc_like(A, &W);
         if (!rc) rc = dist_transpose_tri(ctx, ctx->sPanel, A, dplasmaUpper, W);
@@ -410,15 +411,22 @@ int dplasma_dpotrf(parsec_context_t* parsec, dplasma_enum_t uplo, parsec_tiled_m
     if (!parsec) return -1;
     int info = 0;
     parsec_taskpool_t* tp = dplasma_dpotrf_New(uplo, A, &info);
-    if (!tp) return -101;  // src/zpotrf_wrapper.c:318-319 region: New failed
+    // illegal uplo: New has printed the message and returned NULL; the reference's blocking wrapper then
+    // skips the run and returns info == 0 (src/zpotrf_wrapper.c:318-335)
+    if (!tp) return 0;
     int rc = parsec_context_add_taskpool(parsec, tp);
     if (!rc) rc = parsec_context_start(parsec);
     int rc2 = parsec_context_wait(parsec);
     dplasma_dpotrf_Destruct(tp);
-    if (rc) return rc < 0 ? rc : -rc - 1000;
-    if (rc2) return rc2 < 0 ? rc2 : -rc2 - 1000;
-    if (A->super.nodes > 1) info = info_allreduce_max(parsec, info);  // src/zpotrf_wrapper.c:331-332
-    return info;
+    const int err = rc ? (rc < 0 ? rc : -rc - 1000) : (rc2 ? (rc2 < 0 ? rc2 : -rc2 - 1000) : 0);
+    if (A->super.nodes > 1) {
+        // src/zpotrf_wrapper.c:331-332.  A rank whose run failed still takes part, with INT_MAX, so that
+        // the others neither wait for it forever nor report success.
+        const int g = info_allreduce_max(parsec, err ? 0x7fffffff : info);
+        if (err) return err;
+        return g == 0x7fffffff ? -102 : g;
+    }
+    return err ? err : info;
 }
 
 // profile of the grouped trailing-update launches (the dominant kernel): mode 1 starts
@@ -428,26 +436,37 @@ void dplasma_b200_profile(parsec_context_t* ctx, int on) {
     for (cudaEvent_t e : ctx->profEv) cudaEventDestroy(e);
     ctx->profEv.clear();
     ctx->profFlops.clear();
+    ctx->profStream.clear();
     ctx->profile = on;
 }
-int dplasma_b200_profile_read(parsec_context_t* ctx, double* seconds, double* flops, int* launches,
-                              double* best_tflops) {
+// which: -1 every launch; 1 the bulk updates on the update stream (launches on one stream never overlap each
+// other, so their summed duration is a share of the step <= 1); 0 the look-ahead / left-looking launches on
+// the panel stream, which run concurrently with the bulk update of the previous step
+int dplasma_b200_profile_read_stream(parsec_context_t* ctx, int which, double* seconds, double* flops, int* launches,
+                                     double* best_tflops) {
     if (!ctx) return -1;
     cudaDeviceSynchronize();
     double t = 0.0, f = 0.0, best = 0.0;
+    int cnt = 0;
     const size_t n = ctx->profFlops.size();
     for (size_t i = 0; i < n; i++) {
+        if (which >= 0 && ctx->profStream[i] != which) continue;
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, ctx->profEv[2 * i], ctx->profEv[2 * i + 1]) != cudaSuccess) continue;
         t += ms * 1e-3;
         f += ctx->profFlops[i];
+        cnt++;
         if (ms > 0.5f) best = std::max(best, ctx->profFlops[i] / (ms * 1e-3) / 1e12);
     }
     if (seconds) *seconds = t;
     if (flops) *flops = f;
-    if (launches) *launches = (int)n;
+    if (launches) *launches = cnt;
     if (best_tflops) *best_tflops = best;
     return 0;
+}
+int dplasma_b200_profile_read(parsec_context_t* ctx, double* seconds, double* flops, int* launches,
+                              double* best_tflops) {
+    return dplasma_b200_profile_read_stream(ctx, -1, seconds, flops, launches, best_tflops);
 }
 
 // complex double: same driver, interleaved complex tiles (src/zpotrf_wrapper.c is the source all

@@ -142,7 +142,7 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
                 ctx->nranks);
         return -303;
     }
-    int rc = ensure_grid_comms(ctx, A.P, A.Q);
+    int rc = ensure_grid_comms(ctx, A.P, A.Q, A.ip, A.jq);
     if (!rc) rc = ensure_winv(ctx, A.nb);
     if (!rc) rc = ensure_panel_bufs(ctx, A);
     if (rc) return rc;
@@ -231,7 +231,7 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
 // R <- R - L L^T on the lower tiles (the residual of check_dpotrf, src/dplasma_zcheck.c:89-99) for
 // a matrix distributed over the grid: the factorization's own panel exchange, minus the solves.
 int check_update_multi(parsec_context_s* ctx, const DevMatrix& L, const DevMatrix& R) {
-    int rc = ensure_grid_comms(ctx, L.P, L.Q);
+    int rc = ensure_grid_comms(ctx, L.P, L.Q, L.ip, L.jq);
     if (!rc) rc = ensure_panel_bufs(ctx, L);
     if (rc) return rc;
     cudaStream_t s = ctx->sPanel;
@@ -303,9 +303,9 @@ int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T
             }
             if (src != me && dst != me) continue;
             if (!grouped) { group_start(ctx); grouped = true; }
-            if (src == me) rc = p2p_send(ctx, T.tile(m / T.P, n / T.Q), te, dst, s);
+            if (src == me) rc = p2p_send(ctx, T.tile(m / T.P, n / T.Q), te, world_rank_of(T, dst / T.Q, dst % T.Q), s);
             else {
-                rc = p2p_recv(ctx, tmp + recvM.size() * te, te, src, s);
+                rc = p2p_recv(ctx, tmp + recvM.size() * te, te, world_rank_of(T, src / T.Q, src % T.Q), s);
                 recvM.push_back(m);
             }
         }
@@ -330,7 +330,7 @@ int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T
 // ---------------------------------------------------------------------------------------
 static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower, int diag, double alpha,
                               const DevMatrix& Tm, const DevMatrix& B) {
-    int rc = ensure_grid_comms(ctx, Tm.P, Tm.Q);
+    int rc = ensure_grid_comms(ctx, Tm.P, Tm.Q, Tm.ip, Tm.jq);
     if (!rc) rc = ensure_winv(ctx, Tm.nb);
     if (!rc) rc = ensure_panel_bufs(ctx, Tm);
     if (rc) return rc;
@@ -400,12 +400,12 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
 
 int trsm_left_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, int diag, double alpha,
                     const DevMatrix& A, const DevMatrix& B) {
-    if (A.P != B.P || A.Q != B.Q || A.mb != B.mb) {
+    if (A.P != B.P || A.Q != B.Q || A.mb != B.mb || A.ip != B.ip || A.jq != B.jq) {
         fprintf(stderr, "dplasma_dtrsm: A and B must share the process grid and the row tiling\n");
         return -102;
     }
     if (A.P * A.Q != ctx->nranks) return -303;
-    int rc = ensure_grid_comms(ctx, A.P, A.Q);
+    int rc = ensure_grid_comms(ctx, A.P, A.Q, A.ip, A.jq);
     if (rc) return rc;
     if (trans == dplasmaNoTrans) return solve_panels_multi(ctx, s, uplo == dplasmaLower, diag, alpha, A, B);
     // op(A) = A^T: solve with the transposed factor, which is triangular the other way round
@@ -423,7 +423,7 @@ int trsm_left_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, 
 int symm_residual_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, const DevMatrix& A, const DevMatrix& X,
                         const DevMatrix& B) {
     if (A.P * A.Q != ctx->nranks) return -303;
-    int rc = ensure_grid_comms(ctx, A.P, A.Q);
+    int rc = ensure_grid_comms(ctx, A.P, A.Q, A.ip, A.jq);
     if (!rc) rc = ensure_panel_bufs(ctx, A);
     if (rc) return rc;
     DevMatrix At;

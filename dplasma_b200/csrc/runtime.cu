@@ -193,13 +193,32 @@ static int describe(const parsec_tiled_matrix_t* A, DevMatrix* dm) {
     if (A->mtype != PARSEC_MATRIX_DOUBLE && A->mtype != PARSEC_MATRIX_COMPLEX_DOUBLE) return -1;
     dm->esz = (A->mtype == PARSEC_MATRIX_COMPLEX_DOUBLE) ? 2 : 1;
     if (bc->grid.krows != 1 || bc->grid.kcols != 1) return -2;
-    if (A->i != 0 || A->j != 0 || A->m != A->lm || A->n != A->ln) return -3;  // whole-matrix descriptors only
     dm->mb = A->mb; dm->nb = A->nb; dm->tileElems = (long long)A->mb * A->nb * dm->esz;
     dm->M = A->m; dm->N = A->n; dm->mt = A->mt; dm->nt = A->nt;
     dm->P = bc->grid.rows; dm->Q = bc->grid.cols;
-    dm->prow = (bc->grid.rrank - bc->grid.ip + dm->P) % dm->P;
-    dm->pcol = (bc->grid.crank - bc->grid.jq + dm->Q) % dm->Q;
-    dm->lmt = bc->nb_elem_r; dm->lnt = bc->nb_elem_c;
+    const bool whole = A->i == 0 && A->j == 0 && A->m == A->lm && A->n == A->ln;
+    if (whole) {
+        dm->prow = (bc->grid.rrank - bc->grid.ip + dm->P) % dm->P;
+        dm->pcol = (bc->grid.crank - bc->grid.jq + dm->Q) % dm->Q;
+        dm->ip = bc->grid.ip % dm->P; dm->jq = bc->grid.jq % dm->Q;
+        dm->lmt = bc->nb_elem_r; dm->lnt = bc->nb_elem_c;
+        dm->offR = dm->offC = 0; dm->userLmt = bc->nb_elem_r;
+        return 0;
+    }
+    // Submatrix A(i:i+m, j:j+n): tile-aligned offsets only, like the reference's pdpotrf wrapper
+    // (src/scalapack_wrappers/dplasma_wrapper_pdpotrf.c:209-211); not for sym-packed storage.
+    if (A->i < 0 || A->j < 0 || A->i % A->mb != 0 || A->j % A->nb != 0 || A->i + A->m > A->lm || A->j + A->n > A->ln) return -3;
+    if (bc->uplo != dplasmaUpperLower) return -3;
+    if (A->i + A->m < A->lm && A->m % A->mb != 0) return -3;  // an interior submatrix must end on a tile boundary
+    if (A->j + A->n < A->ln && A->n % A->nb != 0) return -3;
+    const int i0 = A->i / A->mb, j0 = A->j / A->nb;
+    dm->ip = (bc->grid.ip + i0) % dm->P; dm->jq = (bc->grid.jq + j0) % dm->Q;
+    dm->prow = (bc->grid.rrank - dm->ip + dm->P) % dm->P;
+    dm->pcol = (bc->grid.crank - dm->jq + dm->Q) % dm->Q;
+    dm->lmt = local_tiles(dm->mt, dm->P, dm->prow);
+    dm->lnt = local_tiles(dm->nt, dm->Q, dm->pcol);
+    dm->offR = (dm->prow + i0) / dm->P; dm->offC = (dm->pcol + j0) / dm->Q;
+    dm->userLmt = bc->nb_elem_r;
     return 0;
 }
 
@@ -227,7 +246,8 @@ static int copy_column(const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, in
             }
         const size_t cnt = (size_t)(i1 - i0) * dm->tileElems;
         double* dev = dm->tile(i0, jl);
-        double* usr = sym ? user + packed * dm->tileElems : user + ((size_t)i0 + (size_t)jl * dm->lmt) * dm->tileElems;
+        double* usr = sym ? user + packed * dm->tileElems
+                          : user + ((size_t)(i0 + dm->offR) + (size_t)(jl + dm->offC) * dm->userLmt) * dm->tileElems;
         if (dir == 0) DPB_CUDA(cudaMemcpyAsync(dev, usr, cnt * sizeof(double), cudaMemcpyDefault, s));
         else DPB_CUDA(cudaMemcpyAsync(usr, dev, cnt * sizeof(double), cudaMemcpyDefault, s));
         return 0;
@@ -239,7 +259,7 @@ static int copy_column(const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, in
         const int gm = il * dm->P + dm->prow;
         const int tm = dm->rowsOfTile(gm);
         double* dev = dm->tile(il, jl);
-        double* usr = user + ((size_t)il * dm->mb + (size_t)jl * dm->nb * lld) * dm->esz;
+        double* usr = user + ((size_t)(il + dm->offR) * dm->mb + (size_t)(jl + dm->offC) * dm->nb * lld) * dm->esz;
         if (dir == 0)
             DPB_CUDA(cudaMemcpy2DAsync(dev, (size_t)dm->mb * eb, usr, lld * eb, (size_t)tm * eb, tn, cudaMemcpyDefault, s));
         else
@@ -277,7 +297,9 @@ int stage_in(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* d
     }
     const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
     if (!bc->mat) return -110;
-    const bool regular = A->storage == PARSEC_MATRIX_TILE && bc->uplo == dplasmaUpperLower;
+    // in place only for whole matrices: a submatrix is staged (its local tiles are not a dense tile grid)
+    const bool regular = A->storage == PARSEC_MATRIX_TILE && bc->uplo == dplasmaUpperLower && dm->offR == 0 &&
+                         dm->offC == 0 && dm->userLmt == dm->lmt;
     if (regular && is_device_ptr(bc->mat)) {
         dm->base = (double*)bc->mat;
         dm->owned = false;

@@ -5,6 +5,7 @@
 // is built and the blocking dplasma_dpotrf stages it through the GPU tile grid.
 #include <cstdio>
 #include <cstdlib>
+#include <dlfcn.h>
 #include <map>
 #include "internal.h"
 
@@ -13,6 +14,41 @@ struct GridInfo { int nprow, npcol, myrow, mycol; };
 std::map<int, GridInfo> g_grids;
 parsec_context_t* g_wrapper_ctx = nullptr;
 bool g_wrapper_owned = false;
+
+// The process grid of a BLACS context.  The reference binds Cblacs_gridinfo / Cblacs_get / numroc_ at link time
+// (src/scalapack_wrappers/common.h:235-263,298-301).  This library must also load into processes that have no
+// BLACS at all (the Python tests, a C driver without ScaLAPACK), so the same symbols are looked up in the
+// running process: an application linked with ScaLAPACK/BLACS (tools/cscalapack/pdpotrf.c) is served by its own
+// BLACS exactly as with the reference; otherwise the grid registered with dplasma_b200_blacs_gridinit is used.
+typedef void (*blacs_gridinfo_fn)(int, int*, int*, int*, int*);
+typedef int (*numroc_fn)(int*, int*, int*, int*, int*);
+bool grid_of_context(int ictxt, GridInfo* g) {
+    blacs_gridinfo_fn gridinfo = (blacs_gridinfo_fn)dlsym(RTLD_DEFAULT, "Cblacs_gridinfo");
+    if (gridinfo) {
+        int P = -1, Q = -1, r = -1, c = -1;
+        gridinfo(ictxt, &P, &Q, &r, &c);
+        if (P > 0 && Q > 0 && r >= 0 && c >= 0) {  // BLACS answers -1 for a process outside the grid
+            *g = GridInfo{P, Q, r, c};
+            return true;
+        }
+    }
+    auto it = g_grids.find(ictxt);
+    if (it != g_grids.end()) { *g = it->second; return true; }
+    *g = GridInfo{1, 1, 0, 0};
+    return false;
+}
+// NUMROC: rows / columns of a block-cyclic dimension that land on process iproc (ScaLAPACK TOOLS/numroc.f);
+// the application's own numroc_ when it has one
+int local_count(int n, int nb, int iproc, int isrc, int nprocs) {
+    numroc_fn ext = (numroc_fn)dlsym(RTLD_DEFAULT, "numroc_");
+    if (ext) return ext(&n, &nb, &iproc, &isrc, &nprocs);
+    const int mydist = (nprocs + iproc - isrc) % nprocs, nblocks = n / nb;
+    int cnt = (nblocks / nprocs) * nb;
+    const int extra = nblocks % nprocs;
+    if (mydist < extra) cnt += nb;
+    else if (mydist == extra) cnt += n % nb;
+    return cnt;
+}
 }  // namespace
 
 extern "C" {
@@ -44,17 +80,22 @@ void pdpotrf_(char* UPLO, int* N, double* A, int* IA, int* JA, int* DESCA, int* 
     const int ictxt = DESCA[1], gM = DESCA[2], gN = DESCA[3], MB = DESCA[4], NB = DESCA[5];
     const int RSRC = DESCA[6], CSRC = DESCA[7], LLD = DESCA[8];  // common.h:283-292
     GridInfo g{1, 1, 0, 0};
-    auto it = g_grids.find(ictxt);
-    if (it != g_grids.end()) g = it->second;
+    grid_of_context(ictxt, &g);  // PASTE_SETUP: Cblacs_gridinfo (common.h:250)
     if (MB != NB) {
         fprintf(stderr, "pdpotrf_: square blocks required (MB=%d NB=%d)\n", MB, NB);  // :83
         *info = -606;
         return;
     }
-    if ((*IA - 1) % MB != 0 || (*JA - 1) % NB != 0 || *IA != 1 || *JA != 1 || *N != gM || *N != gN) {
-        // the reference asserts tile-aligned offsets (:209-211); sub-matrix views are not built here
-        fprintf(stderr, "pdpotrf_: only IA=JA=1 and N equal to the global size are supported\n");
+    const int cIA = *IA - 1, cJA = *JA - 1;
+    if (cIA < 0 || cJA < 0 || cIA % MB != 0 || cJA % NB != 0) {
+        // the reference asserts tile-aligned offsets (:209-211)
+        fprintf(stderr, "pdpotrf_: IA and JA must address the first row / column of a block (IA=%d JA=%d MB=%d)\n", *IA, *JA, MB);
         *info = -4;
+        return;
+    }
+    if (cIA + *N > gM || cJA + *N > gN || (cIA + *N < gM && *N % MB != 0) || (cJA + *N < gN && *N % NB != 0)) {
+        fprintf(stderr, "pdpotrf_: sub( A ) must lie inside A and, unless it reaches the last row / column, end on a block boundary\n");
+        *info = -2;
         return;
     }
     const char u = *UPLO;
@@ -63,10 +104,10 @@ void pdpotrf_(char* UPLO, int* N, double* A, int* IA, int* JA, int* DESCA, int* 
     if (!g_wrapper_ctx) { *info = -1000; return; }
     const int rank = g.myrow * g.npcol + g.mycol;
     parsec_matrix_block_cyclic_t dcA;
-    // numroc for the local column count (common.h:235-263)
-    parsec_matrix_block_cyclic_lapack_init(&dcA, PARSEC_MATRIX_DOUBLE, PARSEC_MATRIX_LAPACK, rank, MB, NB, gM, gN, 0, 0,
-                                           *N, *N, g.nprow, g.npcol, 1, 1, RSRC, CSRC, LLD, 0);
-    dcA.super.lln = dcA.super.sln;
+    // :177-188: the caller's local array, zero-copy, as a LAPACK-storage block-cyclic descriptor of sub( A )
+    const int nloc = local_count(gN, NB, g.mycol, CSRC, g.npcol);  // numroc_ (common.h:252)
+    parsec_matrix_block_cyclic_lapack_init(&dcA, PARSEC_MATRIX_DOUBLE, PARSEC_MATRIX_LAPACK, rank, MB, NB, gM, gN, cIA, cJA,
+                                           *N, *N, g.nprow, g.npcol, 1, 1, RSRC, CSRC, LLD, nloc);
     dcA.mat = A;
     // NB: like the reference wrapper (:219-222) the local info is returned without a MAX-reduce
     int rc = dplasma_dpotrf(g_wrapper_ctx, uplo, (parsec_tiled_matrix_t*)&dcA);
@@ -97,8 +138,7 @@ void pdtrsm_(char* SIDE, char* UPLO, char* TRANS, char* DIAG, int* M, int* N, do
         return;
     }
     GridInfo g{1, 1, 0, 0};
-    auto it = g_grids.find(ictxt);
-    if (it != g_grids.end()) g = it->second;
+    grid_of_context(ictxt, &g);
     if (!g_wrapper_ctx) parsec_init_wrapper_();
     if (!g_wrapper_ctx) return;
     const int rank = g.myrow * g.npcol + g.mycol, nb = DESCA[4];
@@ -137,8 +177,7 @@ void pdgemm_(char* TRANSA, char* TRANSB, int* M, int* N, int* K, double* ALPHA, 
         return;
     }
     GridInfo g{1, 1, 0, 0};
-    auto it = g_grids.find(ictxt);
-    if (it != g_grids.end()) g = it->second;
+    grid_of_context(ictxt, &g);
     if (!g_wrapper_ctx) parsec_init_wrapper_();
     if (!g_wrapper_ctx) return;
     const int rank = g.myrow * g.npcol + g.mycol;

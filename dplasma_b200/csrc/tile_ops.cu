@@ -49,7 +49,9 @@ int gemm_single(parsec_context_s* ctx, cudaStream_t s, int M, int N, int K, doub
     d.preload = ctx->gemmPreload;
     d.batch = batch; d.batchStrideA = sA; d.batchStrideB = sB; d.batchStrideC = sC;
     d.lastBatchM = lastBatchM;
-    d.fast = ((K % 16 == 0) && (lda % 2 == 0) && (ldb % 2 == 0) && aligned16(A) && aligned16(B) &&
+    // TMA producer: tensor-map copies for M-major operands (any K: the part of a box beyond K arrives as zeros),
+    // 128-byte bulk rows for K-major ones (whole 16-deep chunks only)
+    d.fast = ((!(aK || bK) || K % 16 == 0) && (lda % 2 == 0) && (ldb % 2 == 0) && aligned16(A) && aligned16(B) &&
               (sA % 2 == 0) && (sB % 2 == 0))
                  ? 1 : 0;
     // tile configuration: the large CTA tiles only when they still fill the machine
@@ -218,6 +220,8 @@ int dplasma_b200_dsyrk_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t 
     if (uplo != dplasmaLower && uplo != dplasmaUpper) return -3;
     cudaStream_t s = (cudaStream_t)stream;
     const bool aK = trans != dplasmaNoTrans;  // C = alpha A^T A + beta C : op(A)(i,kk) = A[kk + i*lda]
+    if (alpha == 0.0 || k == 0)  // BLAS: A is not referenced, C = beta C on the uplo triangle
+        return launch_scale_tile(ctx, s, C, ldc, n, n, beta, uplo == dplasmaLower ? 1 : 2);
     ctx->gemmPreload = 0;  // library-call semantics: product first, then beta*C
     int rc = gemm_single(ctx, s, n, n, k, alpha, A, lda, aK, A, lda, aK, beta, C, ldc, uplo == dplasmaLower ? 1 : 2);
     ctx->gemmPreload = 1;
@@ -233,6 +237,7 @@ int dplasma_b200_dgemm_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t 
     // B'[j][kk] = op(B)[kk][j]: NoTrans -> B[kk + j*ldb] (K-major), Trans -> B[j + kk*ldb] (M-major).
     const bool aK = transA != dplasmaNoTrans;
     const bool bK = transB == dplasmaNoTrans;
+    if (alpha == 0.0 || k == 0) return launch_scale_tile(ctx, s, C, ldc, m, n, beta, 0);  // BLAS: C = beta C
     ctx->gemmPreload = getenv("DPB_GEMM_PRELOAD") ? 1 : 0;  // library-call semantics unless overridden (profiling)
     int rc = gemm_single(ctx, s, m, n, k, alpha, A, lda, aK, B, ldb, bK, beta, C, ldc, 0);
     ctx->gemmPreload = 1;

@@ -266,6 +266,10 @@ double dplasma_b200_last_elapsed(parsec_context_t *parsec);
 void dplasma_b200_profile(parsec_context_t *parsec, int on);
 int dplasma_b200_profile_read(parsec_context_t *parsec, double *seconds, double *flops, int *launches,
                               double *best_tflops);
+/* the same sums restricted to one stream: which = 1 the bulk updates (update stream; launches on one stream do
+ * not overlap each other), 0 the look-ahead launches on the panel stream, -1 all */
+int dplasma_b200_profile_read_stream(parsec_context_t *parsec, int which, double *seconds, double *flops,
+                                     int *launches, double *best_tflops);
 /* number of kernels this library launched since the context was created */
 long long dplasma_b200_kernel_launches(parsec_context_t *parsec);
 

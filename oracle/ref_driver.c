@@ -48,6 +48,7 @@ void ref_dplgsy(double bump, int uplo, int M, int N, int mb, int nb, double *A, 
                 unsigned long long seed)
 {
     int mt = (M + mb - 1) / mb, nt = (N + nb - 1) / nb;
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
     for (int n = 0; n < nt; n++)
         for (int m = 0; m < mt; m++) {
             if (uplo == PlasmaLower && m < n) continue;
@@ -61,6 +62,7 @@ void ref_zplghe(double bump, int uplo, int M, int N, int mb, int nb, double _Com
                 unsigned long long seed)
 {
     int mt = (M + mb - 1) / mb, nt = (N + nb - 1) / nb;
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
     for (int n = 0; n < nt; n++)
         for (int m = 0; m < mt; m++) {
             if (uplo == PlasmaLower && m < n) continue;
@@ -73,6 +75,7 @@ void ref_zplghe(double bump, int uplo, int M, int N, int mb, int nb, double _Com
 void ref_dplrnt(int M, int N, int mb, int nb, double *A, int lda, unsigned long long seed)
 {
     int mt = (M + mb - 1) / mb, nt = (N + nb - 1) / nb;
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
     for (int n = 0; n < nt; n++)
         for (int m = 0; m < mt; m++) {
             int tm = (m == mt - 1) ? M - m * mb : mb, tn = (n == nt - 1) ? N - n * nb : nb;
@@ -83,6 +86,7 @@ void ref_dplrnt(int M, int N, int mb, int nb, double *A, int lda, unsigned long 
 void ref_zplrnt(int M, int N, int mb, int nb, double _Complex *A, int lda, unsigned long long seed)
 {
     int mt = (M + mb - 1) / mb, nt = (N + nb - 1) / nb;
+#pragma omp parallel for collapse(2) schedule(dynamic, 1)
     for (int n = 0; n < nt; n++)
         for (int m = 0; m < mt; m++) {
             int tm = (m == mt - 1) ? M - m * mb : mb, tn = (n == nt - 1) ? N - n * nb : nb;
@@ -482,6 +486,26 @@ double ref_time_dpotrf(int uplo, int N, int nb, unsigned long long seed, int *in
     double t0 = omp_get_wtime();
     int info = ref_dpotrf(uplo, N, nb, A, (int)lda);
     double t1 = omp_get_wtime();
+    if (info_out) *info_out = info;
+    free(A);
+    return t1 - t0;
+}
+
+/* Second CPU line of BASELINE.md section 5: the same matrix factored by ONE monolithic, internally
+ * multithreaded LAPACKE_dpotrf call (what a user without a tile runtime would run).  Returns seconds. */
+extern int LAPACKE_dpotrf_work(int layout, char uplo, int n, double *a, int lda);
+double ref_time_lapacke_dpotrf(int uplo, int N, int nb, unsigned long long seed, int threads, int *info_out)
+{
+    size_t lda = (size_t)N;
+    double *A = (double *)malloc(lda * N * sizeof(double));
+    if (!A) return -1.0;
+    openblas_set_num_threads(1);
+    ref_dplgsy((double)N, uplo, N, N, nb, nb, A, (int)lda, seed);
+    openblas_set_num_threads(threads > 0 ? threads : omp_get_max_threads());
+    double t0 = omp_get_wtime();
+    int info = LAPACKE_dpotrf_work(102 /* LAPACK_COL_MAJOR */, uplo == PlasmaLower ? 'L' : 'U', N, A, (int)lda);
+    double t1 = omp_get_wtime();
+    openblas_set_num_threads(1);
     if (info_out) *info_out = info;
     free(A);
     return t1 - t0;

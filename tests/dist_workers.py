@@ -228,10 +228,12 @@ def nccl_posv_worker(rank, world, port, P, Q, N, nb, K, nbr, uplo_name, q, check
         dist.destroy_process_group()
 
 
-def nccl_pdpotrf_worker(rank, world, port, P, Q, N, nb, uplo_name, q):
+def nccl_pdpotrf_worker(rank, world, port, P, Q, N, nb, uplo_name, q, rsrc=0, csrc=0, ia=1, blacs=False):
     """GPU: the ScaLAPACK-compatible pdpotrf_ on a P x Q grid: each rank passes its own
     column-major local array (LLD = local rows) and the 9-int array descriptor, like
-    tools/cscalapack/pdpotrf.c:94."""
+    tools/cscalapack/pdpotrf.c:94.  rsrc / csrc: the process row / column that owns block (0,0) (DESCA[6..7]);
+    ia: sub( A ) starts at global row and column ia of a larger matrix; blacs: the grid comes from the
+    process's "BLACS" (tests/c/fake_blacs.c) instead of dplasma_b200_blacs_gridinit."""
     import torch
     import dplasma_b200 as dp
     from tests.util import lapack_local
@@ -247,20 +249,35 @@ def nccl_pdpotrf_worker(rank, world, port, P, Q, N, nb, uplo_name, q):
         from oracle.oracle import Oracle
         orc = Oracle()
         uplo = dp.Lower if uplo_name == "L" else dp.Upper
-        A0 = orc.plgsy(float(N), dp.UpperLower, N, nb, 3872)
-        loc, ri, ci = lapack_local(A0, nb, nb, P, Q, rank)
+        S0 = orc.plgsy(float(N), dp.UpperLower, N, nb, 3872)
+        o = ia - 1
+        gN = o + N
+        A0 = np.asfortranarray(np.random.default_rng(11).standard_normal((gN, gN)))
+        A0[o:, o:] = S0
+        # the process at physical (r, c) holds what the process at logical ((r - rsrc) % P, (c - csrc) % Q) would
+        lrank = ((rank // Q - rsrc) % P) * Q + (rank % Q - csrc) % Q
+        loc, ri, ci = lapack_local(A0, nb, nb, P, Q, lrank)
+        loc0 = loc.copy()
         lld = max(1, loc.shape[0])
-        lib.dplasma_b200_blacs_gridinit(7, P, Q, rank // Q, rank % Q)
-        desc = (C.c_int * 9)(1, 7, N, N, nb, nb, 0, 0, lld)
-        n, one, info = C.c_int(N), C.c_int(1), C.c_int(-7)
+        if blacs:
+            from tests.util import load_fake_blacs
+            load_fake_blacs().fake_blacs_set(7, P, Q, rank // Q, rank % Q)
+        else:
+            lib.dplasma_b200_blacs_gridinit(7, P, Q, rank // Q, rank % Q)
+        desc = (C.c_int * 9)(1, 7, gN, gN, nb, nb, rsrc, csrc, lld)
+        n, one, info = C.c_int(N), C.c_int(ia), C.c_int(-7)
         lib.pdpotrf_(uplo_name.encode(), C.byref(n), loc.ctypes.data_as(C.c_void_p), C.byref(one), C.byref(one), desc, C.byref(info))
         want = A0.copy(order="F")
-        assert orc.potrf(uplo, want, nb) == 0
+        sub = S0.copy(order="F")
+        assert orc.potrf(uplo, sub, nb) == 0
         tri = np.tril if uplo == dp.Lower else np.triu
-        mask = tri(np.ones((N, N), dtype=bool))[np.ix_(ri, ci)]
-        err = float(np.abs(loc - want[np.ix_(ri, ci)])[mask].max() / np.abs(want).max()) if mask.any() else 0.0
-        # the other triangle of the caller's array is left alone
-        untouched = bool(np.array_equal(loc[~mask], A0[np.ix_(ri, ci)][~mask]))
+        full = np.zeros((gN, gN), dtype=bool)
+        full[o:, o:] = tri(np.ones((N, N), dtype=bool))
+        want[o:, o:] = sub
+        mask = full[np.ix_(ri, ci)]
+        err = float(np.abs(loc - want[np.ix_(ri, ci)])[mask].max() / np.abs(sub).max()) if mask.any() else 0.0
+        # everything but the uplo triangle of sub( A ) is left alone in the caller's array
+        untouched = bool(np.array_equal(loc[~mask], loc0[~mask]))
         q.put((rank, info.value, err, untouched))
         lib.dplasma_b200_wrapper_set_context(None)
         ctx.close()

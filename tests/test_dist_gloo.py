@@ -7,11 +7,21 @@ import pytest
 
 
 def free_port():
-    s = socket.socket()
-    s.bind(("127.0.0.1", 0))
-    p = s.getsockname()[1]
-    s.close()
-    return p
+    """outside the kernel's ephemeral range, see tests/test_gpu_multi.py"""
+    import os
+    import random
+    rng = random.Random(os.getpid() * 104729 + int.from_bytes(os.urandom(4), "little"))
+    for _ in range(200):
+        p = rng.randrange(20000, 32000)
+        s = socket.socket()
+        try:
+            s.bind(("127.0.0.1", p))
+        except OSError:
+            continue
+        finally:
+            s.close()
+        return p
+    raise RuntimeError("no free rendezvous port")
 
 
 @pytest.mark.parametrize("P,Q,N,nb", [(1, 2, 200, 32), (2, 1, 200, 32), (2, 2, 232, 24)])

@@ -8,11 +8,22 @@ pytestmark = pytest.mark.gpu
 
 
 def free_port():
-    s = socket.socket()
-    s.bind(("127.0.0.1", 0))
-    p = s.getsockname()[1]
-    s.close()
-    return p
+    """a rendezvous port OUTSIDE the kernel's ephemeral range (32768-60999): a port handed out by bind(0) can be
+    taken by any outgoing connection between the moment it is released here and the moment the workers listen on it"""
+    import os
+    import random
+    rng = random.Random(os.getpid() * 7919 + int.from_bytes(os.urandom(4), "little"))
+    for _ in range(200):
+        p = rng.randrange(20000, 32000)
+        s = socket.socket()
+        try:
+            s.bind(("127.0.0.1", p))
+        except OSError:
+            continue
+        finally:
+            s.close()
+        return p
+    raise RuntimeError("no free rendezvous port")
 
 
 def run_grid(P, Q, N, nb, check_values, cplx=False):
@@ -28,7 +39,7 @@ def run_grid(P, Q, N, nb, check_values, cplx=False):
     procs = [ctx.Process(target=nccl_potrf_worker, args=(r, world, port, P, Q, N, nb, q, check_values, cplx)) for r in range(world)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=600) for _ in range(world)]
+    res = [q.get(timeout=240) for _ in range(world)]
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
@@ -45,8 +56,9 @@ def test_dpotrf_grid_matches_oracle(P, Q, N, nb):
         assert info_bad == res[0][6] and info_bad > 0     # MAX-reduced, identical on every rank
 
 
-@pytest.mark.parametrize("P,Q,N,nb", [(1, 2, 32768, 1024), (2, 2, 49152, 1024), (2, 4, 65536, 1024)])
+@pytest.mark.parametrize("P,Q,N,nb", [(1, 2, 32768, 1024), (2, 2, 49152, 1024), (2, 4, 65536, 1024), (2, 4, 131072, 1024)])
 def test_dpotrf_grid_large_residual(P, Q, N, nb):
+    """the last case is BASELINE.json configs[2] (the north-star run) through the reference's residual check"""
     res = run_grid(P, Q, N, nb, False)
     for rank, info, bad, resid, err, t, info_bad in res:
         assert info == 0 and bad == 0 and 0.0 <= resid < 60.0, (rank, info, bad, resid)
@@ -65,7 +77,7 @@ def run_posv(P, Q, N, nb, K, nbr, uplo, check_values):
     procs = [ctx.Process(target=nccl_posv_worker, args=(r, world, port, P, Q, N, nb, K, nbr, uplo, q, check_values)) for r in range(world)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=900) for _ in range(world)]
+    res = [q.get(timeout=420) for _ in range(world)]
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
@@ -107,12 +119,38 @@ def test_pdpotrf_grid(P, Q, uplo):
     procs = [ctx.Process(target=nccl_pdpotrf_worker, args=(r, world, port, P, Q, 1100, 128, uplo, q)) for r in range(world)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=600) for _ in range(world)]
+    res = [q.get(timeout=240) for _ in range(world)]
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
     for rank, info, err, untouched in res:
         assert info == 0 and err < 1e-11 and untouched, (rank, info, err, untouched)
+
+
+@pytest.mark.parametrize("P,Q,rsrc,csrc,ia", [(1, 2, 0, 1, 1), (2, 1, 1, 0, 129), (1, 2, 0, 1, 257), (2, 2, 1, 1, 129), (2, 4, 1, 3, 385)])
+def test_pdpotrf_grid_rsrc_csrc_and_submatrix(P, Q, rsrc, csrc, ia):
+    """block (0,0) on a process other than (0,0) (DESCA RSRC / CSRC) and a block-aligned sub( A ); the grid comes from
+    the process's BLACS symbols like in an application linked with ScaLAPACK"""
+    import torch
+    import torch.multiprocessing as mp
+    from tests.dist_workers import nccl_pdpotrf_worker
+    world = P * Q
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    for uplo in ("L", "U"):
+        port = free_port()
+        procs = [ctx.Process(target=nccl_pdpotrf_worker, args=(r, world, port, P, Q, 1100, 128, uplo, q, rsrc, csrc, ia, True))
+                 for r in range(world)]
+        for p in procs:
+            p.start()
+        res = [q.get(timeout=240) for _ in range(world)]
+        for p in procs:
+            p.join(timeout=120)
+            assert p.exitcode == 0
+        for rank, info, err, untouched in res:
+            assert info == 0 and err < 1e-11 and untouched, (rank, uplo, info, err, untouched)
 
 
 @pytest.mark.parametrize("P,Q", [(1, 2), (2, 2)])
@@ -147,7 +185,7 @@ def test_dpotrf_grid_host_matrix(P, Q, kind):
     procs = [ctx.Process(target=nccl_host_potrf_worker, args=(r, world, port, P, Q, 1500, 128, kind, q)) for r in range(world)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=600) for _ in range(world)]
+    res = [q.get(timeout=240) for _ in range(world)]
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
@@ -171,7 +209,7 @@ def test_dpoinv_dpotri_dtrtri_grid_match_oracle(P, Q, uplo):
     procs = [ctx.Process(target=nccl_poinv_worker, args=(r, world, port, P, Q, 1000, 128, uplo, q)) for r in range(world)]
     for p in procs:
         p.start()
-    res = [q.get(timeout=600) for _ in range(world)]
+    res = [q.get(timeout=240) for _ in range(world)]
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0

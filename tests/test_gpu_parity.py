@@ -279,9 +279,9 @@ def test_info_semantics(ctx, oracle, golden):
     d = make_host(ctx, A, nb, nb)
     assert ctx.lib.dplasma_dpotrf(ctx.ptr, Lower, d.ref) == 151 == int(golden["d200_pivot150_info_L"][0])
     d.free()
-    # bad uplo: New fails -> -101 like the reference's blocking wrappers
+    # bad uplo: New prints and returns NULL, the blocking wrapper returns info == 0 (src/zpotrf_wrapper.c:318-335)
     d = make_host(ctx, A, nb, nb)
-    assert ctx.lib.dplasma_dpotrf(ctx.ptr, 999, d.ref) == -101
+    assert ctx.lib.dplasma_dpotrf(ctx.ptr, 999, d.ref) == 0
     d.free()
 
 
@@ -365,6 +365,44 @@ def test_pdpotrf_single_process(ctx, oracle):
         oracle.potrf(uplo, want, nb)
         tri = np.tril if uplo == Lower else np.triu
         assert relerr(tri(A), tri(want)) < VTOL
+
+
+@pytest.mark.parametrize("gN,ia,N", [(700, 129, 572), (700, 65, 256), (640, 1, 640)])
+def test_pdpotrf_blacs_symbols_and_submatrix(ctx, oracle, gN, ia, N):
+    """The reference's wrapper asks BLACS for the grid (Cblacs_gridinfo, common.h:250) and accepts sub( A ) =
+    A(IA:IA+N-1, JA:JA+N-1) with block-aligned IA, JA (dplasma_wrapper_pdpotrf.c:209-211): a process that has those
+    symbols is served by them, and only the uplo triangle of sub( A ) changes in the caller's array."""
+    from tests.util import load_fake_blacs
+    nb = 64
+    fb = load_fake_blacs()
+    fb.fake_blacs_set(42, 1, 1, 0, 0)
+    calls0 = C.c_int.in_dll(fb, "g_fake_blacs_calls").value
+    rng = np.random.default_rng(gN + ia)
+    G0 = np.asfortranarray(rng.standard_normal((gN, gN)))
+    S0 = oracle.plgsy(float(N), UpperLower, N, nb, SEED_A)
+    o = ia - 1
+    G0[o:o + N, o:o + N] = S0
+    for u, uplo in ((b"L", Lower), (b"U", Upper)):
+        G = G0.copy(order="F")
+        desc = (C.c_int * 9)(1, 42, gN, gN, nb, nb, 0, 0, gN)
+        n, i1, info = C.c_int(N), C.c_int(ia), C.c_int(-7)
+        ctx.lib.pdpotrf_(u, C.byref(n), G.ctypes.data_as(C.c_void_p), C.byref(i1), C.byref(i1), desc, C.byref(info))
+        assert info.value == 0
+        want = S0.copy(order="F")
+        assert oracle.potrf(uplo, want, nb) == 0
+        tri = np.tril if uplo == Lower else np.triu
+        sub = G[o:o + N, o:o + N]
+        assert relerr(tri(sub), tri(want)) < VTOL
+        changed = G != G0
+        allowed = np.zeros_like(changed)
+        allowed[o:o + N, o:o + N] = tri(np.ones((N, N), dtype=bool))
+        assert not (changed & ~allowed).any()
+    assert C.c_int.in_dll(fb, "g_fake_blacs_calls").value > calls0   # the grid came from "BLACS"
+    # offsets that do not address the first row of a block are refused like the reference's assert
+    n, bad, info = C.c_int(64), C.c_int(3), C.c_int(0)
+    G = G0.copy(order="F")
+    ctx.lib.pdpotrf_(b"L", C.byref(n), G.ctypes.data_as(C.c_void_p), C.byref(bad), C.byref(bad), desc, C.byref(info))
+    assert info.value == -4 and np.array_equal(G, G0)
 
 
 # ------------------------------------------------------------------ BASELINE sizes through properties
@@ -602,3 +640,42 @@ def test_zposv_lower_vs_oracle(ctx, oracle, N, nb, K, nbr):
     assert ctx.lib.dplasma_zlange(ctx.ptr, dp.InfNorm, dB.ref) == pytest.approx(oracle.lange_inf(np.asfortranarray(X), "z"), rel=1e-12)
     for d in (dA, dB, dA0, dB0):
         d.free()
+
+
+def test_tile_seam_alpha_zero_scales_c(ctx):
+    """cuBLAS / BLAS rule at the kernel seam: alpha == 0 (or k == 0) never reads A or B, C = beta C
+    (beta == 0 stores zeros even over NaN); dsyrk touches only its triangle"""
+    import torch
+    m, n = 93, 70
+    rng = np.random.default_rng(5)
+    C0 = np.asfortranarray(rng.standard_normal((m, n)))
+    junk = torch.full((8,), float("nan"), dtype=torch.float64, device="cuda")
+    for beta in (2.5, 0.0):
+        C1 = C0.copy()
+        if beta == 0.0:
+            C1[3, 4] = np.nan
+        tC = torch.from_numpy(C1.T.copy()).cuda()
+        assert ctx.lib.dplasma_b200_dgemm_tile(ctx.ptr, None, NoTrans, Trans, m, n, 64, 0.0, dev(junk), m, dev(junk), n, beta, dev(tC), m) == 0
+        torch.cuda.synchronize()
+        assert np.array_equal(tC.cpu().numpy().T, beta * C0 if beta else np.zeros_like(C0))
+    S0 = np.asfortranarray(rng.standard_normal((n, n)))
+    tS = torch.from_numpy(S0.T.copy()).cuda()
+    assert ctx.lib.dplasma_b200_dsyrk_tile(ctx.ptr, None, Lower, NoTrans, n, 0, 1.0, dev(junk), n, 3.0, dev(tS), n) == 0
+    torch.cuda.synchronize()
+    got = tS.cpu().numpy().T
+    assert np.array_equal(np.tril(got), np.tril(3.0 * S0)) and np.array_equal(np.triu(got, 1), np.triu(S0, 1))
+
+
+def test_dpotrf_upper_more_than_65535_tile_pairs(ctx, oracle):
+    """dplasmaUpper on one GPU transposes the tile grid in place: nt = 364 gives 66430 tile pairs, more than one
+    grid dimension holds (the reference's own testing_zpotrf.c:21 is Upper-only)"""
+    N, nb = 2906, 8
+    A0 = oracle.plgsy(float(N), Upper, N, nb, SEED_A)
+    d = make_host(ctx, A0, nb, nb)
+    assert ctx.lib.dplasma_dpotrf(ctx.ptr, Upper, d.ref) == 0
+    F = read_host(d, N, N, nb, nb)
+    want = A0.copy(order="F")
+    assert oracle.potrf(Upper, want, nb) == 0
+    assert relerr(np.triu(F), np.triu(want)) < VTOL
+    assert np.array_equal(np.tril(F, -1), np.tril(A0, -1))
+    d.free()

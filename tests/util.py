@@ -59,3 +59,19 @@ def lapack_local(A, mb, nb, P, Q, rank):
     ri = np.concatenate([np.arange(g * mb, min(M, (g + 1) * mb)) for g in range(prow, mt, P)] or [np.zeros(0, int)])
     ci = np.concatenate([np.arange(g * nb, min(N, (g + 1) * nb)) for g in range(pcol, nt, Q)] or [np.zeros(0, int)])
     return np.asfortranarray(A[np.ix_(ri.astype(int), ci.astype(int))]), ri.astype(int), ci.astype(int)
+
+
+def load_fake_blacs():
+    """compile tests/c/fake_blacs.c and load it RTLD_GLOBAL: the process now 'has a BLACS' (Cblacs_gridinfo,
+    Cblacs_get, numroc_) for libdplasma_b200 to find, like an application linked with ScaLAPACK"""
+    import ctypes
+    import os
+    import subprocess
+    import tempfile
+    here = os.path.dirname(os.path.abspath(__file__))
+    so = os.path.join(tempfile.gettempdir(), f"libfakeblacs_{os.getuid()}.so")
+    if not os.path.exists(so):
+        tmp = so + f".{os.getpid()}"
+        subprocess.check_call(["gcc", "-O1", "-shared", "-fPIC", "-o", tmp, os.path.join(here, "c", "fake_blacs.c")])
+        os.replace(tmp, so)
+    return ctypes.CDLL(so, mode=ctypes.RTLD_GLOBAL)
