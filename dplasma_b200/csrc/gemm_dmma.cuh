@@ -138,10 +138,6 @@ __device__ __forceinline__ void lds128(double& x, double& y, uint32_t addr) {
 __device__ __forceinline__ void lds64(double& x, uint32_t addr) {
     asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x) : "r"(addr));
 }
-// s * x for s = +1 / -1 without the FP64 pipe (which the DMMAs of the co-resident CTAs keep busy): sign-bit flip
-__device__ __forceinline__ double flip_sign(double x, unsigned flip) {
-    return __hiloint2double(__double2hiint(x) ^ (int)flip, __double2loint(x));
-}
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
     // volatile: keeps every DMMA ordered against the (volatile) mbarrier waits/arrives, see the
     // stage-release note in the consumer loop
@@ -377,10 +373,6 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
     const bool pre = d.preload && (w.lower == 0);
     const double cscale = (beta == 0.0 || !pre) ? 0.0 : beta / alpha;
     const double ebeta = pre ? 0.0 : beta;  // what the epilogue still has to add
-    // the trailing update has alpha = -1, beta = 1: scaling by +-1 is a sign flip on the integer pipe, so the
-    // prologue and epilogue of this CTA do not queue FP64 instructions behind the DMMAs of its neighbours
-    const bool unitScale = (alpha == 1.0 || alpha == -1.0) && (cscale == 1.0 || cscale == -1.0 || cscale == 0.0);
-    const unsigned preFlip = (cscale < 0.0) ? 0x80000000u : 0u, postFlip = (alpha < 0.0) ? 0x80000000u : 0u;
     const bool vec = !AK && (w.M == BM) && (w.N == BN) && (w.lower == 0) && ((w.ldc & 1) == 0) &&
                      ((reinterpret_cast<uintptr_t>(w.C) & 15) == 0);
     // fragment -> tile coordinates (K-major operands use the natural 8f+g fragment rows)
@@ -401,13 +393,8 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
 #pragma unroll
                 for (int i = 0; i < MF; i += 2) {
                     const double2 x = *reinterpret_cast<const double2*>(cp + mrow(g, i));
-                    if (unitScale) {
-                        acc[i][j][h] = flip_sign(x.x, preFlip);
-                        acc[i + 1][j][h] = flip_sign(x.y, preFlip);
-                    } else {
-                        acc[i][j][h] = cscale * x.x;
-                        acc[i + 1][j][h] = cscale * x.y;
-                    }
+                    acc[i][j][h] = cscale * x.x;
+                    acc[i + 1][j][h] = cscale * x.y;
                 }
             }
     } else {
@@ -508,13 +495,8 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
 #pragma unroll
                 for (int i = 0; i < MF; i += 2) {
                     double2 x;
-                    if (unitScale) {
-                        x.x = flip_sign(acc[i][j][h], postFlip);
-                        x.y = flip_sign(acc[i + 1][j][h], postFlip);
-                    } else {
-                        x.x = alpha * acc[i][j][h];
-                        x.y = alpha * acc[i + 1][j][h];
-                    }
+                    x.x = alpha * acc[i][j][h];
+                    x.y = alpha * acc[i + 1][j][h];
                     if (ebeta != 0.0) {
                         const double2 c0 = *reinterpret_cast<const double2*>(cp + mrow(g, i));
                         x.x += ebeta * c0.x;

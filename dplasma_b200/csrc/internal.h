@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <cstdio>
+#include <cstdlib>
+#include <algorithm>
 #include <vector>
 #include "../../include/dplasma_b200.h"
 #include "gemm_dmma.cuh"
@@ -94,8 +96,16 @@ struct parsec_context_s {
     size_t wInvSlot = 0;
     double* wNorm = nullptr;    // row-sum scratch for norms
     size_t wNormLen = 0;
-    double* panelBuf[2] = {nullptr, nullptr};  // multi-GPU panel workspaces
-    size_t panelBufElems = 0;
+    // multi-GPU panel workspaces: panelSets sets of panelSetElems doubles in one allocation (two alternate in
+    // steady state; more are kept alive while a host matrix is still arriving, see potrf_dist.cu)
+    double* panelBase = nullptr;
+    size_t panelSetElems = 0;
+    int panelSets = 0;
+    // host -> device staging rate seen by the last pipelined stage-in (bytes/s, 0: not measured yet): the
+    // schedule uses it to guess which tile columns will have landed by the time a step runs
+    double h2dBw = 0.0;
+    double h2dBytes = 0.0;
+    cudaEvent_t evH2d[2] = {nullptr, nullptr};
     double lastElapsed = 0.0;
     double lastCheck = 0.0;
     long long launches = 0;
@@ -119,6 +129,49 @@ struct parsec_context_s {
 };
 
 namespace dpb {
+// ---------------------------------------------------------------------------------------
+// Arrival model of a pipelined stage-in (host matrix still on its way, tile column by tile column, while the
+// factorization runs).  All of it is a GUESS used to decide how much work to enqueue behind which copy event;
+// correctness rests on the events alone (every stream waits for the copy of a column before touching it).
+// A pessimistic guess only postpones the update of late columns (they are caught up later in one launch);
+// an optimistic one makes a stream wait for data -- so the rate is discounted.
+// ---------------------------------------------------------------------------------------
+struct ArrivalModel {
+    std::vector<double> landed;  // landed[jl]: modelled time at which local tile column jl is in HBM
+    double now = 0.0;            // modelled GPU time consumed by the steps enqueued so far
+    double rate = 28e12;         // sustained flop/s of the update kernel used for `now`
+    void init(const DevMatrix& A, double bytesPerSecond) {
+        if (const char* e = getenv("DPB_H2D_GBS")) bytesPerSecond = atof(e) * 1e9 / 0.85;  // tests: force a rate
+        const double bw = 0.85 * (bytesPerSecond > 1e6 ? bytesPerSecond : 20e9);
+        landed.assign(A.lnt, 0.0);
+        double t = 0.0;
+        for (int jl = 0; jl < A.lnt; jl++) {
+            const int gn = jl * A.Q + A.pcol;
+            const int rows = std::max(0, std::min(A.firstLocalRowGE(A.mt), A.lmt) - A.firstLocalRowGE(gn));
+            t += (double)rows * A.tileElems * 8.0 / bw;
+            landed[jl] = t;
+        }
+    }
+    // local flops of the trailing update of step k (my share of the (nt-k-1)(nt-k)/2 tiles) plus the panel
+    void step(const DevMatrix& A, int k) {
+        const double tiles = 0.5 * (double)(A.nt - k - 1) * (A.nt - k) / (A.P * A.Q);
+        now += 2.0 * tiles * A.nb * (double)A.nb * A.nb / rate + 0.8e-3;
+    }
+    // number of local columns modelled as landed by `now` (a prefix: copies are issued left to right)
+    int arrived() const {
+        int n = 0;
+        while (n < (int)landed.size() && landed[n] <= now) n++;
+        return n;
+    }
+    // steps needed before everything has landed (the window during which earlier panels must stay available)
+    int window(const DevMatrix& A, int cap) const {
+        ArrivalModel m = *this;
+        int w = 0;
+        while (w < cap && w < A.nt && m.arrived() < (int)landed.size()) { m.step(A, w); w++; }
+        return w;
+    }
+};
+
 // kernels.cu
 int launch_potrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv,
                       int* dInfo, int infoBase);
@@ -217,5 +270,6 @@ int inf_norm_public(parsec_context_s* ctx, const DevMatrix& A, bool sym, int upl
 int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp);
 int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,
                     long long rowStride, const double* colPanel, long long colStride, int gnFirst,
-                    int gnEnd, double alpha, int K, int kTile = 0, long long kTileStride = 0, int rowFirstFixed = -1);
+                    int gnEnd, double alpha, int K, int kTile = 0, long long kTileStride = 0, int rowFirstFixed = -1,
+                    int jlMin = 0, int jlMax = 1 << 30);
 }  // namespace dpb

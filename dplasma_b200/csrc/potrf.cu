@@ -27,8 +27,9 @@ static cudaEvent_t get_event(parsec_context_s* ctx, size_t idx) {
 // gnFirst <= gn < gnEnd and gm >= gn; diagonal tiles only in their lower part (SYRK).
 int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,
                     long long rowStride, const double* colPanel, long long colStride, int gnFirst, int gnEnd,
-                    double alpha, int K, int kTile, long long kTileStride, int rowFirstFixed) {
-    const int jl0 = C.firstLocalColGE(gnFirst), jl1 = std::min(C.firstLocalColGE(gnEnd), C.lnt);
+                    double alpha, int K, int kTile, long long kTileStride, int rowFirstFixed, int jlMin, int jlMax) {
+    // [jlMin, jlMax): additional clamp on the LOCAL tile columns (columns of a host matrix that have landed)
+    const int jl0 = std::max(C.firstLocalColGE(gnFirst), jlMin), jl1 = std::min(std::min(C.firstLocalColGE(gnEnd), C.lnt), jlMax);
     const int rowEnd = std::min(C.firstLocalRowGE(C.mt), C.lmt);
     for (int c0 = jl0; c0 < jl1; c0 += kMaxCols) {
         const int ncols = std::min(kMaxCols, jl1 - c0);
@@ -151,52 +152,36 @@ static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
     DPB_CUDA(cudaStreamWaitEvent(su, ev0, 0));
     size_t evi = 1;
     cudaEvent_t evUpdPrev = nullptr;
-    int kStart = 0;
-    if (!ctx->evIn.empty() && (int)ctx->evIn.size() == nt && nt >= 8 && !ctx->cplx) {
-        // ---- pipelined stage-in: the host matrix is still arriving, tile column by tile column.
-        // Start LEFT-looking on the columns that are here (column j needs only columns <= j):
-        //   A(j.., j) -= A(j.., 0:j) A(j, 0:j)^T ; POTRF(j,j) ; TRSM(j+1.., j)
-        // then bring the rest of the matrix up to date in one grouped launch and go on right-looking.
-        const int cstar = nt / 4;
-        const long long kts = (long long)A.lmt * A.tileElems;
-        for (int j = 0; j < cstar; j++) {
-            DPB_CUDA(cudaStreamWaitEvent(sp, ctx->evIn[j], 0));
-            if (j > 0) {
-                rc = trailing_update(ctx, sp, A, A.tile(0, 0), A.tileElems, A.tile(0, 0), A.tileElems, j, j + 1, -1.0,
-                                     j * nb, nb, kts);
-                if (rc) return rc;
-            }
-            double* winv = ctx->wInv + (size_t)(j & 1) * ctx->wInvSlot;
-            rc = potrf_tile_fused(ctx, sp, A.tile(j, j), A.mb, nb, winv, ctx->dInfo, j * nb);
-            if (rc) return rc;
-            rc = trsm_panel_lower(ctx, sp, A.tile(j, j), A.mb, nb, winv, A.tile(j + 1, j), A.mb, A.mb, nt - j - 1,
-                                  A.tileElems, A.rowsOfTile(nt - 1));
-            if (rc) return rc;
-            cudaEvent_t evCol = get_event(ctx, evi++);
-            DPB_CUDA(cudaEventRecord(evCol, sp));
-            if (ctx->curTp && ctx->earlyOut >= 0) {
-                rc = stage_out_column(ctx, ctx->curTp->A, &ctx->curTp->dA, j, dplasmaLower, evCol);
-                if (rc) return rc;
-                ctx->earlyOut = j + 1;
-            }
-        }
-        DPB_CUDA(cudaStreamWaitEvent(sp, ctx->evIn[nt - 1], 0));  // copies are in order: everything has landed
-        rc = trailing_update(ctx, sp, A, A.tile(0, 0), A.tileElems, A.tile(0, 0), A.tileElems, cstar, nt, -1.0,
-                             cstar * nb, nb, kts);
-        if (rc) return rc;
-        cudaEvent_t evCatch = get_event(ctx, evi++);
-        DPB_CUDA(cudaEventRecord(evCatch, sp));
-        DPB_CUDA(cudaStreamWaitEvent(su, evCatch, 0));
-        kStart = cstar;
-    } else if (!ctx->evIn.empty()) {
-        // not eligible for the left-looking start: wait for the whole matrix
+    // A host matrix that is still arriving tile column by tile column (pipelined stage-in): step k updates only the
+    // columns [.., avail) that have landed; later arrivals are caught up with ALL panels factored so far in one
+    // grouped launch (K spans the finished tile columns, read in place) and join the regular update from then on.
+    const bool arriving = !ctx->evIn.empty() && (int)ctx->evIn.size() == nt && !ctx->cplx;
+    if (!ctx->evIn.empty() && !arriving) {
         DPB_CUDA(cudaStreamWaitEvent(sp, ctx->evIn.back(), 0));
         DPB_CUDA(cudaStreamWaitEvent(su, ctx->evIn.back(), 0));
     }
-    for (int k = kStart; k < nt; k++) {
+    ArrivalModel model;
+    if (arriving) model.init(A, ctx->h2dBw);
+    int avail = arriving ? 0 : nt;
+    const long long kts = (long long)A.lmt * A.tileElems;
+    // columns [avail, upto) <- updates of panels 0 .. panels-1, on stream s, behind the copy of column upto-1
+    auto catch_up = [&](cudaStream_t s, int upto, int panels) -> int {
+        upto = std::min(upto, nt);
+        if (upto <= avail) return 0;
+        DPB_CUDA(cudaStreamWaitEvent(s, ctx->evIn[upto - 1], 0));  // copies are issued left to right
+        if (panels <= 0) return 0;
+        return trailing_update(ctx, s, A, A.tile(0, 0), A.tileElems, A.tile(0, 0), A.tileElems, panels, nt, -1.0, panels * nb,
+                               nb, kts, -1, avail, upto);
+    };
+    for (int k = 0; k < nt; k++) {
         const int tk = A.rowsOfTile(k);
         double* winv = ctx->wInv + (size_t)(k & 1) * ctx->wInvSlot;
         double* Akk = A.tile(k, k);
+        if (k >= avail) {  // first step, or a column that landed late: bring it up to date before factoring it
+            rc = catch_up(sp, k + 1, k);
+            if (rc) return rc;
+            avail = k + 1;
+        }
         rc = potrf_tile_fused(ctx, sp, Akk, A.mb, tk, winv, ctx->dInfo, k * nb);
         if (rc) return rc;
         trace_mark(sp, k, 0);
@@ -215,17 +200,40 @@ static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
             ctx->earlyOut = k + 1;
         }
         const double* panel = A.tile(0, k);  // tile (i,k) at panel + i*tileElems
+        const int availOld = avail;
         // look-ahead: tile column k+1 on the panel stream (after the previous bulk update wrote it)
         if (evUpdPrev) DPB_CUDA(cudaStreamWaitEvent(sp, evUpdPrev, 0));
-        rc = trailing_update(ctx, sp, A, panel, A.tileElems, panel, A.tileElems, k + 1, k + 2, -1.0, nb);
+        if (k + 1 >= avail) {
+            rc = catch_up(sp, k + 2, k + 1);  // not touched yet: panels 0 .. k at once
+            avail = k + 2;
+        } else {
+            rc = trailing_update(ctx, sp, A, panel, A.tileElems, panel, A.tileElems, k + 1, k + 2, -1.0, nb);
+        }
         if (rc) return rc;
         trace_mark(sp, k, 2);
-        // bulk: tile columns k+2.. on the update stream
-        if (k + 2 < nt) {
+        // bulk: the tile columns k+2.. that had landed before this step, on the update stream
+        bool bulk = false;
+        if (k + 2 < std::min(nt, availOld)) {
             DPB_CUDA(cudaStreamWaitEvent(su, evPanel, 0));
-            rc = trailing_update(ctx, su, A, panel, A.tileElems, panel, A.tileElems, k + 2, nt, -1.0, nb);
+            rc = trailing_update(ctx, su, A, panel, A.tileElems, panel, A.tileElems, k + 2, nt, -1.0, nb, 0, 0, -1, 0, availOld);
             if (rc) return rc;
             trace_mark(su, k, 3);
+            bulk = true;
+        }
+        if (avail < nt) {
+            // the columns expected to have landed by now: panels 0 .. k in one launch, behind their copy event
+            model.step(A, k);
+            int target = std::max(avail, model.arrived());
+            if (k + 3 >= nt) target = nt;
+            if (target > avail) {
+                DPB_CUDA(cudaStreamWaitEvent(su, evPanel, 0));
+                rc = catch_up(su, target, k + 1);
+                if (rc) return rc;
+                avail = target;
+                bulk = true;
+            }
+        }
+        if (bulk) {
             cudaEvent_t evUpd = get_event(ctx, evi++);
             DPB_CUDA(cudaEventRecord(evUpd, su));
             evUpdPrev = evUpd;
@@ -338,16 +346,17 @@ int parsec_context_start(parsec_context_t* ctx) {
     ctx->evIn.clear();
     for (parsec_taskpool_s* tp : ctx->queue) {
         if (tp->kind != TP_POTRF) continue;
-        // A single queued lower factorization of a host matrix in TILE storage, one process: pipeline the
-        // stage-in with a left-looking start.  Everything else: plain stage-in.
+        // A single queued lower factorization of a host matrix (tile or LAPACK storage, one process or a grid):
+        // the stage-in is pipelined, the schedule follows the arrival of the tile columns.  Everything else:
+        // plain stage-in.
         const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)tp->A;
         cudaPointerAttributes at;
         bool onDevice = cudaPointerGetAttributes(&at, bc->mat) == cudaSuccess &&
                         (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged);
         cudaGetLastError();
-        const bool pipe = ctx->queue.size() == 1 && tp->uplo == dplasmaLower && tp->A->super.nodes == 1 &&
-                          tp->A->storage == PARSEC_MATRIX_TILE && tp->A->mtype == PARSEC_MATRIX_DOUBLE && !onDevice &&
-                          tp->A->m % tp->A->mb == 0 && !getenv("DPB_NO_PIPELINE");
+        const bool pipe = ctx->queue.size() == 1 && tp->uplo == dplasmaLower && tp->A->mtype == PARSEC_MATRIX_DOUBLE &&
+                          !onDevice && tp->A->mb == tp->A->nb && tp->A->nb % 16 == 0 && tp->A->nt >= 4 &&
+                          !getenv("DPB_NO_PIPELINE");
         int rc = pipe ? stage_in_pipelined(ctx, tp->A, &tp->dA, tp->uplo) : stage_in(ctx, tp->A, &tp->dA, true, tp->uplo);
         if (rc) return rc;
         tp->staged = true;
@@ -396,7 +405,18 @@ int parsec_context_wait(parsec_context_t* ctx) {
     if (ctx->seqElapsed >= 0.0) ctx->lastElapsed = ctx->seqElapsed;
     else if (cudaEventElapsedTime(&ms, ctx->evStart, ctx->evStop) == cudaSuccess) ctx->lastElapsed = ms * 1e-3;
     ctx->seqElapsed = -1.0;
+    if (ctx->h2dBytes > 0.0 && ctx->evH2d[0] && ctx->evH2d[1]) {
+        float hms = 0.f;
+        if (cudaEventElapsedTime(&hms, ctx->evH2d[0], ctx->evH2d[1]) == cudaSuccess && hms > 0.f) {
+            const double bw = ctx->h2dBytes / (hms * 1e-3);
+            ctx->h2dBw = ctx->h2dBw > 0.0 ? 0.5 * (ctx->h2dBw + bw) : bw;
+        }
+        ctx->h2dBytes = 0.0;
+    }
     dpb::trace_dump();
+    // the arrival events belong to this run only (other drivers reuse the schedule on resident matrices)
+    for (cudaEvent_t e : ctx->evIn) cudaEventDestroy(e);
+    ctx->evIn.clear();
     for (parsec_taskpool_s* tp : ctx->queue) {
         if (!tp->done && tp->info && *tp->info == 0) *tp->info = *ctx->hInfo;  // rank-local until the wrapper reduces it
         stage_free(&tp->dA);

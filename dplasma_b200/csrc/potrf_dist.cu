@@ -46,16 +46,22 @@ static void compute_panel_plan(const DevMatrix& A, int k, int gmFirst, PanelPlan
     }
 }
 
-static int ensure_panel_bufs(parsec_context_s* ctx, const DevMatrix& A) {
+static int ensure_panel_bufs(parsec_context_s* ctx, const DevMatrix& A, int nsets = 2) {
     const size_t diag = (size_t)A.tileElems + (size_t)((A.nb + IB - 1) / IB) * IB * IB * A.esz;
     const size_t need = (size_t)(A.lmt + A.lnt) * A.tileElems + diag;
-    if (ctx->panelBuf[0] && ctx->panelBufElems >= need) return 0;
-    for (int i = 0; i < 2; i++) {
-        if (ctx->panelBuf[i]) cudaFree(ctx->panelBuf[i]);
-        ctx->panelBuf[i] = nullptr;
-        DPB_CUDA(cudaMalloc(&ctx->panelBuf[i], need * sizeof(double)));
+    if (ctx->panelBase && ctx->panelSetElems >= need && ctx->panelSets >= nsets) return 0;
+    if (ctx->panelBase) {
+        // the panels of an earlier operation may still be in use by work in flight on the two streams
+        cudaStreamSynchronize(ctx->sPanel);
+        cudaStreamSynchronize(ctx->sUpdate);
+        cudaFree(ctx->panelBase);
     }
-    ctx->panelBufElems = need;
+    ctx->panelBase = nullptr;
+    const size_t setElems = std::max(need, ctx->panelSetElems);
+    const int sets = std::max(nsets, ctx->panelSets);
+    DPB_CUDA(cudaMalloc(&ctx->panelBase, setElems * sets * sizeof(double)));
+    ctx->panelSetElems = setElems;
+    ctx->panelSets = sets;
     return 0;
 }
 struct PanelBufs {
@@ -65,7 +71,7 @@ struct PanelBufs {
 };
 static PanelBufs panel_bufs(parsec_context_s* ctx, const DevMatrix& A, int set) {
     PanelBufs b;
-    b.row = ctx->panelBuf[set];
+    b.row = ctx->panelBase + (size_t)set * ctx->panelSetElems;
     b.col = b.row + (size_t)A.lmt * A.tileElems;
     b.diag = b.col + (size_t)A.lnt * A.tileElems;
     return b;
@@ -135,6 +141,11 @@ static cudaEvent_t dist_event(parsec_context_s* ctx, size_t idx) {
     return ctx->evPool[idx];
 }
 
+// A host matrix that is still arriving (pipelined stage-in, ctx->evIn holds one event per local tile column):
+// the right-looking step k updates only the local columns [.., avail) that have landed; columns that land later
+// are caught up with every panel factored so far -- which therefore stay alive (one panel set each) during the
+// first `window` steps -- and join the regular update from then on.  Purely local decisions: the collectives of a
+// step do not depend on them.
 int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
     const DevMatrix& A = tp->dA;
     if (A.P * A.Q != ctx->nranks) {
@@ -142,9 +153,17 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
                 ctx->nranks);
         return -303;
     }
+    const bool arriving = !ctx->evIn.empty() && (int)ctx->evIn.size() == A.lnt;
+    ArrivalModel model;
+    int window = 0;
+    if (arriving) {
+        model.init(A, ctx->h2dBw);
+        window = std::max(1, model.window(A, 6));
+    }
+    const int nsets = std::max(2, window);
     int rc = ensure_grid_comms(ctx, A.P, A.Q, A.ip, A.jq);
     if (!rc) rc = ensure_winv(ctx, A.nb);
-    if (!rc) rc = ensure_panel_bufs(ctx, A);
+    if (!rc) rc = ensure_panel_bufs(ctx, A, nsets);
     if (rc) return rc;
     cudaStream_t sp = ctx->sPanel, su = ctx->sUpdate;
     const int nt = A.nt, nb = A.nb;
@@ -156,13 +175,50 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
     size_t evi = 1;
     cudaEvent_t evUpdPrev = nullptr;
     const int rowEnd = std::min(A.firstLocalRowGE(A.mt), A.lmt);
+    const int colEnd = std::min(A.firstLocalColGE(A.nt), A.lnt);
+    int avail = arriving ? 0 : A.lnt;   // local columns [0, avail) have landed and carry every update issued so far
+    std::vector<PanelView> kept;         // panels 0 .. k-1 while columns are still missing
+    // bring local columns [avail, upto) up to date with the panels kept so far, on stream s
+    auto catch_up = [&](cudaStream_t s, int upto, int panels) -> int {
+        upto = std::min(upto, colEnd);
+        if (upto <= avail) return 0;
+        DPB_CUDA(cudaStreamWaitEvent(s, ctx->evIn[upto - 1], 0));  // copies are issued left to right
+        for (int q = 0; q < panels; q++) {
+            const PanelView& v = kept[q];
+            int r = trailing_update(ctx, s, A, v.rowPtr, v.rowStride, v.colPtr, v.colStride, q + 1, nt, -1.0, nb, 0, 0, -1,
+                                    avail, upto);
+            if (r) return r;
+        }
+        return 0;
+    };
     for (int k = 0; k < nt; k++) {
-        const int set = k & 1;
+        const int set = k % nsets;
         const int kp = k % A.P, kq = k % A.Q;
         const int tk = A.rowsOfTile(k);
         PanelBufs b = panel_bufs(ctx, A, set);
         const bool inCol = (A.pcol == kq);
         const int jlk = k / A.Q;  // local column index of tile column k on the ranks of grid column kq
+        if (arriving && k == window) {
+            // the panels kept so far are about to be overwritten: their last readers (the catch-up launches of the
+            // previous step on the update stream) must be done, and everything still missing has to land now
+            if (evUpdPrev) DPB_CUDA(cudaStreamWaitEvent(sp, evUpdPrev, 0));
+            rc = catch_up(sp, colEnd, (int)kept.size());
+            if (rc) return rc;
+            avail = A.lnt;
+            cudaEvent_t evAll = dist_event(ctx, evi++);
+            DPB_CUDA(cudaEventRecord(evAll, sp));
+            DPB_CUDA(cudaStreamWaitEvent(su, evAll, 0));
+        }
+        if (inCol && jlk >= avail) {
+            // my part of the panel itself has not been touched yet: land it and apply panels 0 .. k-1 (look-ahead
+            // normally did that one step ago; this is the first step, or a column that arrived late)
+            rc = catch_up(sp, jlk + 1, (int)kept.size());
+            if (rc) return rc;
+            cudaEvent_t evC = dist_event(ctx, evi++);
+            DPB_CUDA(cudaEventRecord(evC, sp));
+            DPB_CUDA(cudaStreamWaitEvent(su, evC, 0));
+            avail = jlk + 1;
+        }
         // ---- (1) diagonal tile: factor on the owner, broadcast down grid column kq ----
         if (inCol) {
             double* winv = b.diag + te;
@@ -206,15 +262,51 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
         if (rc) return rc;
         cudaEvent_t evPanel = dist_event(ctx, evi++);
         DPB_CUDA(cudaEventRecord(evPanel, sp));
-        // ---- look-ahead update of tile column k+1 on the panel stream ----
+        const int availOld = avail;
+        if (avail < A.lnt) {
+            kept.push_back(pv);
+            // the look-ahead column must be complete before the next step factors it
+            const int jl1 = (k + 1) / A.Q;
+            if (A.pcol == (k + 1) % A.Q && jl1 >= avail) {
+                if (evUpdPrev) DPB_CUDA(cudaStreamWaitEvent(sp, evUpdPrev, 0));
+                rc = catch_up(sp, jl1 + 1, (int)kept.size());   // panels 0 .. k, this step's included
+                if (rc) return rc;
+                avail = jl1 + 1;
+            }
+        }
+        // ---- look-ahead update of tile column k+1 on the panel stream (columns caught up just now already have it) ----
         if (evUpdPrev) DPB_CUDA(cudaStreamWaitEvent(sp, evUpdPrev, 0));
-        rc = trailing_update(ctx, sp, A, pv.rowPtr, pv.rowStride, pv.colPtr, pv.colStride, k + 1, k + 2, -1.0, nb);
+        rc = trailing_update(ctx, sp, A, pv.rowPtr, pv.rowStride, pv.colPtr, pv.colStride, k + 1, k + 2, -1.0, nb, 0, 0, -1, 0,
+                             availOld);
         if (rc) return rc;
-        // ---- bulk update on the update stream ----
+        // ---- bulk update on the update stream: the columns that had landed before this step ----
+        bool bulk = false;
         if (k + 2 < nt) {
             DPB_CUDA(cudaStreamWaitEvent(su, evPanel, 0));
-            rc = trailing_update(ctx, su, A, pv.rowPtr, pv.rowStride, pv.colPtr, pv.colStride, k + 2, nt, -1.0, nb);
+            rc = trailing_update(ctx, su, A, pv.rowPtr, pv.rowStride, pv.colPtr, pv.colStride, k + 2, nt, -1.0, nb, 0, 0, -1, 0,
+                                 availOld);
             if (rc) return rc;
+            bulk = true;
+        }
+        if (avail < A.lnt) {
+            // columns expected to have landed by now: all panels so far, behind their copy event, after the bulk
+            model.step(A, k);
+            int target = std::max(avail, model.arrived());
+            if (k + 1 == window || k + 2 >= nt) target = A.lnt;
+            if (target > avail) {
+                if (avail != availOld) {  // the panel stream has just written columns [availOld, avail)
+                    cudaEvent_t evL = dist_event(ctx, evi++);
+                    DPB_CUDA(cudaEventRecord(evL, sp));
+                    DPB_CUDA(cudaStreamWaitEvent(su, evL, 0));
+                }
+                DPB_CUDA(cudaStreamWaitEvent(su, evPanel, 0));
+                rc = catch_up(su, target, (int)kept.size());
+                if (rc) return rc;
+                avail = target;
+                bulk = true;
+            }
+        }
+        if (bulk) {
             cudaEvent_t evUpd = dist_event(ctx, evi++);
             DPB_CUDA(cudaEventRecord(evUpd, su));
             evUpdPrev = evUpd;

@@ -52,8 +52,9 @@ int parsec_fini(parsec_context_t** pctx) {
     for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
     if (ctx->wInv) cudaFree(ctx->wInv);
     if (ctx->wNorm) cudaFree(ctx->wNorm);
+    if (ctx->panelBase) cudaFree(ctx->panelBase);
     for (int i = 0; i < 2; i++)
-        if (ctx->panelBuf[i]) cudaFree(ctx->panelBuf[i]);
+        if (ctx->evH2d[i]) cudaEventDestroy(ctx->evH2d[i]);
     cudaFree(ctx->dInfo);
     cudaFreeHost(ctx->hInfo);
     cudaEventDestroy(ctx->evStart);
@@ -327,6 +328,12 @@ int stage_in_pipelined(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, De
     const int part = (bc->uplo != dplasmaUpperLower) ? bc->uplo : uploOnly;
     for (cudaEvent_t e : ctx->evIn) cudaEventDestroy(e);
     ctx->evIn.clear();
+    // the copy rate of this stage-in feeds the arrival model of the next one (ArrivalModel, internal.h)
+    for (int i = 0; i < 2; i++)
+        if (!ctx->evH2d[i]) DPB_CUDA(cudaEventCreate(&ctx->evH2d[i]));
+    const int rowEnd = std::min(dm->firstLocalRowGE(dm->mt), dm->lmt);
+    double bytes = 0.0;
+    DPB_CUDA(cudaEventRecord(ctx->evH2d[0], ctx->sCopy));
     for (int jl = 0; jl < dm->lnt; jl++) {
         rc = copy_column(A, dm, jl, 0, part, ctx->sCopy);
         if (rc) return rc;
@@ -334,7 +341,14 @@ int stage_in_pipelined(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, De
         DPB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         DPB_CUDA(cudaEventRecord(e, ctx->sCopy));
         ctx->evIn.push_back(e);
+        const int gn = jl * dm->Q + dm->pcol;
+        int i0 = 0, i1 = rowEnd;
+        if (part == dplasmaLower) i0 = std::min(dm->firstLocalRowGE(gn), rowEnd);
+        else if (part == dplasmaUpper) i1 = std::min(dm->firstLocalRowGE(gn + 1), rowEnd);
+        bytes += (double)std::max(0, i1 - i0) * dm->tileElems * 8.0;
     }
+    DPB_CUDA(cudaEventRecord(ctx->evH2d[1], ctx->sCopy));
+    ctx->h2dBytes = bytes;
     return 0;
 }
 

@@ -285,7 +285,7 @@ def nccl_pdpotrf_worker(rank, world, port, P, Q, N, nb, uplo_name, q, rsrc=0, cs
         dist.destroy_process_group()
 
 
-def nccl_host_potrf_worker(rank, world, port, P, Q, N, nb, kind, q):
+def nccl_host_potrf_worker(rank, world, port, P, Q, N, nb, kind, q, gbs=None):
     """GPU: dplasma_dpotrf on a grid with the matrix in pinned HOST memory (tile or sym-packed storage):
     staged in, factored, finished tile columns written back early on the copy stream."""
     import torch
@@ -306,7 +306,12 @@ def nccl_host_potrf_worker(rank, world, port, P, Q, N, nb, kind, q):
         d = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, kind=kind, uplo=dp.Lower if kind == "sym" else dp.UpperLower, where="host")
         loc0 = full_to_local(A0, nb, nb, P, Q, rank, sym_uplo=sym)
         d.host_array()[:d.elems] = loc0
+        if gbs is not None:
+            # what the schedule BELIEVES about the host link, a different belief on every rank: each rank decides by
+            # itself which of its columns a step updates, the collectives of a step must not depend on it
+            os.environ["DPB_H2D_GBS"] = str(float(gbs) * (1 + 3 * rank))
         info = lib.dplasma_dpotrf(ctx.ptr, dp.Lower, d.ref)
+        os.environ.pop("DPB_H2D_GBS", None)
         want = A0.copy(order="F")
         assert orc.potrf(dp.Lower, want, nb) == 0
         got = local_to_full(d.host_array()[:d.elems].copy(), N, N, nb, nb, P, Q, rank, sym_uplo=sym)

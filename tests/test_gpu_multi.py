@@ -169,10 +169,12 @@ def test_zpotrf_baseline_config5_residual():
         assert info == 0 and bad == 0 and 0.0 <= resid < 60.0, (rank, info, bad, resid)
 
 
-@pytest.mark.parametrize("P,Q", [(1, 2), (2, 2), (2, 4)])
-@pytest.mark.parametrize("kind", ["tile", "sym"])
-def test_dpotrf_grid_host_matrix(P, Q, kind):
-    """the reference's own situation: the distributed matrix lives in host memory on every rank"""
+@pytest.mark.parametrize("P,Q", [(1, 2), (2, 1), (2, 2), (2, 4)])
+@pytest.mark.parametrize("kind,gbs", [("tile", None), ("sym", None), ("tile", 0.002), ("sym", 0.05), ("tile", 500.0)])
+def test_dpotrf_grid_host_matrix(P, Q, kind, gbs):
+    """the reference's own situation: the distributed matrix lives in host memory on every rank.  The tile columns
+    travel to the GPUs while the factorization runs (the panels of the first steps are kept until every column has
+    landed and been caught up); gbs forces what each rank believes about its copy rate"""
     import torch
     import torch.multiprocessing as mp
     from tests.dist_workers import nccl_host_potrf_worker
@@ -182,7 +184,7 @@ def test_dpotrf_grid_host_matrix(P, Q, kind):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = free_port()
-    procs = [ctx.Process(target=nccl_host_potrf_worker, args=(r, world, port, P, Q, 1500, 128, kind, q)) for r in range(world)]
+    procs = [ctx.Process(target=nccl_host_potrf_worker, args=(r, world, port, P, Q, 3000, 128, kind, q, gbs)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=240) for _ in range(world)]

@@ -227,19 +227,39 @@ def test_dpotrf_fast_path_vs_oracle(ctx, oracle, N, nb, uplo):
     d.free()
 
 
-@pytest.mark.parametrize("kind", ["tile", "sym"])
-def test_dpotrf_host_matrix_pipelined_stage_in(ctx, oracle, kind):
-    """host matrices with enough tile columns take the pipelined path: left-looking start while the
-    columns arrive, one catch-up update, right-looking rest, finished columns written back early"""
-    N, nb = 2048, 128   # 16 tile columns -> 4 of them factored left-looking
+@pytest.mark.parametrize("kind", ["tile", "sym", "lapack"])
+@pytest.mark.parametrize("gbs", [None, "0.02", "0.5", "1000"])
+@pytest.mark.parametrize("N,nb", [(2048, 128), (1700, 112)])
+def test_dpotrf_host_matrix_pipelined_stage_in(ctx, oracle, kind, gbs, N, nb):
+    """host matrices take the pipelined path: the tile columns travel to the GPU while the factorization runs, each
+    step updates the columns that have landed and later arrivals are caught up with all finished panels in one
+    launch; finished columns are written back early.  The schedule follows a MODEL of the copy rate (events decide
+    correctness): the result must be the same whatever the model believes -- from a link so slow that no column
+    is ever expected (everything caught up at the last moment) to one so fast that everything is expected at once."""
+    import os
     A0 = oracle.plgsy(float(N), Lower, N, nb, SEED_A)
-    d = make_host(ctx, A0, nb, nb, kind, Lower)
-    assert ctx.lib.dplasma_dpotrf(ctx.ptr, Lower, d.ref) == 0
-    F = read_host(d, N, N, nb, nb, kind, Lower, out=A0.copy(order="F") if kind == "sym" else None)
     want = A0.copy(order="F")
     assert oracle.potrf(Lower, want, nb) == 0
+    if gbs is None:
+        os.environ.pop("DPB_H2D_GBS", None)
+    else:
+        os.environ["DPB_H2D_GBS"] = gbs
+    try:
+        if kind == "lapack":
+            M = np.asfortranarray(np.tril(A0) + np.triu(np.full((N, N), 7.0), 1))   # junk above the diagonal must survive
+            d = dp.BlockCyclic(ctx.lib, N, N, nb, nb, kind="lapack", where="host")
+            d.host_array()[:N * N] = M.ravel(order="F")
+            assert ctx.lib.dplasma_dpotrf(ctx.ptr, Lower, d.ref) == 0
+            F = d.host_array()[:N * N].reshape((N, N), order="F").copy()
+            assert np.array_equal(np.triu(F, 1), np.triu(M, 1))
+        else:
+            d = make_host(ctx, A0, nb, nb, kind, Lower)
+            assert ctx.lib.dplasma_dpotrf(ctx.ptr, Lower, d.ref) == 0
+            F = read_host(d, N, N, nb, nb, kind, Lower, out=A0.copy(order="F") if kind == "sym" else None)
+            assert np.array_equal(np.triu(F, 1), np.triu(A0, 1))
+    finally:
+        os.environ.pop("DPB_H2D_GBS", None)
     assert relerr(np.tril(F), np.tril(want)) < VTOL
-    assert np.array_equal(np.triu(F, 1), np.triu(A0, 1))
     d.free()
 
 
