@@ -105,6 +105,8 @@ struct parsec_context_s {
     // schedule uses it to guess which tile columns will have landed by the time a step runs
     double h2dBw = 0.0;
     double h2dBytes = 0.0;
+    int* tileSync = nullptr;     // arrival counter of the single-launch tile factorization (only ever incremented)
+    int tileSyncCount = 0;       // arrivals accounted for by the launches enqueued so far
     cudaEvent_t evH2d[2] = {nullptr, nullptr};
     double lastElapsed = 0.0;
     double lastCheck = 0.0;
@@ -188,6 +190,8 @@ int launch_zpotrf_leaf(parsec_context_s* ctx, cudaStream_t s, double* A, int lda
                        int infoBase);
 int launch_potrf_colblock(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, int j0, double* winv,
                           double* wdiag, int* dInfo, int infoBase);
+int launch_potrf_tile(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv, int* dInfo,
+                      int infoBase);
 int launch_potrf_diag_writeback(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, const double* wdiag);
 int launch_generate(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int kind /*0 plgsy,1 plrnt*/,
                     double bump, int uplo, unsigned long long seed);

@@ -1,0 +1,215 @@
+// Block-level building blocks of the 64 x 64 leaf: Cholesky of a diagonal block in shared memory and the inverse
+// of its factor (shared by kernels.cu and potrf_tile.cu).
+#pragma once
+#include "internal.h"
+
+namespace dpb {
+
+// X <- inverse of the lower-triangular S (both IB x IB in shared memory, X zeroed on entry):
+// 16x16 diagonal blocks by substitution, then two doubling levels
+// inv([L11 0; L21 L22]) = [X11 0; -X22 L21 X11, X22].
+__device__ __forceinline__ void invert_lower_64(double (*S)[IB + 1], double (*X)[IB + 1], int tid) {
+    if (tid < IB) {
+        const int r0 = (tid >> 4) << 4, c = tid & 15;
+        X[r0 + c][r0 + c] = 1.0 / S[r0 + c][r0 + c];
+        for (int i = c + 1; i < 16; i++) {
+            double sum = 0.0;
+            for (int l = c; l < i; l++) sum += S[r0 + i][r0 + l] * X[r0 + l][r0 + c];
+            X[r0 + i][r0 + c] = -sum / S[r0 + i][r0 + i];
+        }
+    }
+    __syncthreads();
+    for (int b = 16; b < IB; b <<= 1) {
+        const int E = (IB / (2 * b)) * b * b;
+        // T = L21 * X11, parked (transposed) in the unused upper triangle of X
+        for (int e = tid; e < E; e += 256) {
+            const int p = e / (b * b), r = e - p * b * b, i = r % b, c = r / b, r0 = p * 2 * b;
+            double t = 0.0;
+            for (int l = c; l < b; l++) t += S[r0 + b + i][r0 + l] * X[r0 + l][r0 + c];
+            X[r0 + c][r0 + b + i] = t;
+        }
+        __syncthreads();
+        // X21 = -X22 * T
+        for (int e = tid; e < E; e += 256) {
+            const int p = e / (b * b), r = e - p * b * b, i = r % b, c = r / b, r0 = p * 2 * b;
+            double x = 0.0;
+            for (int l = 0; l <= i; l++) x += X[r0 + b + i][r0 + b + l] * X[r0 + c][r0 + b + l];
+            X[r0 + b + i][r0 + c] = -x;
+        }
+        __syncthreads();
+    }
+}
+
+// In-place lower Cholesky of the n x n (n <= IB) leading block of S (shared memory), 256 threads.
+// Right-looking, unblocked.  report: write info for the first non-positive pivot.
+__device__ __forceinline__ void leaf_cholesky_64(double (*S)[IB + 1], int n, int tid, int* failed, int* dInfo,
+                                                 int infoBase, bool report) {
+    for (int j = 0; j < n; j++) {
+        const double d = S[j][j];
+        if (report && tid == 0 && !(d > 0.0) && !*failed) {
+            *failed = 1;
+            if (*dInfo == 0) *dInfo = infoBase + j + 1;
+        }
+        const double s = sqrt(d), inv = 1.0 / s;
+        __syncthreads();
+        if (tid < IB) {
+            if (tid == j) S[j][j] = s;
+            else if (tid > j && tid < n) S[tid][j] *= inv;
+        }
+        __syncthreads();
+        const int i = tid & (IB - 1);
+        const double lij = S[i][j];
+        for (int c = j + 1 + (tid >> 6); c < n; c += 4)
+            if (i >= c && i < n) S[i][c] -= lij * S[c][j];
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Fast 64x64 leaf: 2x2 blocks of 32, the sequential parts (32x32 Cholesky, 32x32 triangular
+// inverse) done by ONE warp in registers with shuffles -- no block-wide barrier per column.
+//   S (in/out): lower triangle of the block, identity beyond n.   X (out): inverse of L.
+// 256 threads.  info rule as leaf_cholesky_64.
+// ---------------------------------------------------------------------------------------
+#ifdef DPB_DEBUG_CLOCKS
+extern __device__ long long g_leaf_clk[8];
+#endif
+#ifdef DPB_DEBUG_CLOCKS
+#define LEAF_CLK(i) do { if (tid == 0 && report) g_leaf_clk[i] = clock64(); } while (0)
+#else
+#define LEAF_CLK(i) do { } while (0)
+#endif
+// warp-level: lane r owns row r of the 32x32 block at S[o..o+32)[o..o+32)
+__device__ __forceinline__ void warp_chol32(double (*S)[IB + 1], double* invd, int o, int lane, int nvalid,
+                                            int* failed, int* dInfo, int infoBase, bool report) {
+    // The sequential chain of a column is  broadcast of the pivot -> rsqrt -> scale -> update of the next pivot ;
+    // everything else hides behind it.  Each lane therefore keeps the running diagonal entry of ITS row in a
+    // register of its own (dg): the pivot update needs no shuffle, and the one shuffle on the chain is the pivot
+    // broadcast.  rsqrt(double) is accurate to an ulp or two -- far inside the 1e-11 the factor is held to -- so
+    // the square root and the reciprocal come from it with one multiplication each.
+    double a[32];
+#pragma unroll
+    for (int c = 0; c < 32; c++) a[c] = S[o + lane][o + c];
+    double dg = S[o + lane][o + lane];
+    int firstBad = -1;
+#pragma unroll
+    for (int c = 0; c < 32; c++) {
+        const double d = __shfl_sync(0xffffffffu, dg, c);
+        if (firstBad < 0 && c < nvalid && !(d > 0.0)) firstBad = c;
+        const double inv = rsqrt(d);
+        const double l = a[c] * inv;   // lanes > c: the column entry
+        if (lane == c) { a[c] = d * inv; invd[o + c] = inv; }
+        else if (lane > c) { a[c] = l; dg = fma(-l, l, dg); }
+#pragma unroll
+        for (int c2 = c + 1; c2 < 32; c2++) {
+            const double lc2 = __shfl_sync(0xffffffffu, l, c2);
+            if (lane > c2) a[c2] = fma(-l, lc2, a[c2]);
+        }
+    }
+    if (report && lane == 0 && firstBad >= 0 && !*failed) {
+        *failed = 1;
+        if (*dInfo == 0) *dInfo = infoBase + o + firstBad + 1;
+    }
+#pragma unroll
+    for (int c = 0; c < 32; c++)
+        if (c <= lane) S[o + lane][o + c] = a[c];
+}
+// warp-level: X block (o,o) = inverse of the lower-triangular S block (o,o); lane c owns column c.
+// Column-oriented substitution: as soon as x[k] is final it is folded into every later entry, so the 31 updates of
+// a step are independent of each other and only one multiply-add per step sits on the dependent chain.
+__device__ __forceinline__ void warp_trinv32(double (*S)[IB + 1], double (*X)[IB + 1], const double* invd, int o,
+                                             int lane) {
+    double x[32];
+#pragma unroll
+    for (int i = 0; i < 32; i++) x[i] = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+    for (int k = 0; k < 32; k++) {
+        x[k] *= invd[o + k];
+#pragma unroll
+        for (int i = k + 1; i < 32; i++) x[i] = fma(-S[o + i][o + k], x[k], x[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < 32; i++) X[o + i][o + lane] = (i >= lane) ? x[i] : 0.0;
+}
+
+__device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB + 1], int n, int tid, int* failed,
+                                             int* dInfo, int infoBase, bool report) {
+    const int warp = tid >> 5, lane = tid & 31;
+    __shared__ double invd[IB];  // reciprocals of the diagonal of L
+    // 1. L11 = chol(A11)
+    if (warp == 0) warp_chol32(S, invd, 0, lane, min(n, 32), failed, dInfo, infoBase, report);
+    __syncthreads();
+    LEAF_CLK(0);
+    // 2. warp 0: X11 = inv(L11) ; warp 1: L21 = A21 L11^-T (one row per lane, column-oriented forward substitution)
+    if (warp == 0) warp_trinv32(S, X, invd, 0, lane);
+    else if (warp == 1) {
+        double r[32];
+#pragma unroll
+        for (int c = 0; c < 32; c++) r[c] = S[32 + lane][c];
+#pragma unroll
+        for (int k = 0; k < 32; k++) {
+            r[k] *= invd[k];
+#pragma unroll
+            for (int c = k + 1; c < 32; c++) r[c] = fma(-r[k], S[c][k], r[c]);
+        }
+#pragma unroll
+        for (int c = 0; c < 32; c++) S[32 + lane][c] = r[c];
+    }
+    __syncthreads();
+    LEAF_CLK(1);
+    // 3. A22 -= L21 L21^T (lower part), all threads: 4 outputs each, accumulated side by side
+    {
+        const int i = tid & 31, c0 = tid >> 5;  // outputs (i, c0 + 8 q), q = 0..3
+        double sum[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 8
+        for (int k = 0; k < 32; k++) {
+            const double li = S[32 + i][k];
+#pragma unroll
+            for (int q = 0; q < 4; q++) sum[q] = fma(li, S[32 + c0 + 8 * q][k], sum[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+            if (i >= c0 + 8 * q) S[32 + i][32 + c0 + 8 * q] -= sum[q];
+    }
+    __syncthreads();
+    LEAF_CLK(2);
+    // 4. L22 = chol(A22)
+    if (warp == 0) warp_chol32(S, invd, 32, lane, max(0, min(n - 32, 32)), failed, dInfo, infoBase, report);
+    __syncthreads();
+    LEAF_CLK(3);
+    // 5. warp 0: X22 = inv(L22) ; warps 1-4: T = L21 X11 parked in X's upper-right block (transposed), 8 outputs
+    //    per thread side by side
+    if (warp == 0) warp_trinv32(S, X, invd, 32, lane);
+    else if (warp <= 4) {
+        const int i = lane, c0 = warp - 1;  // outputs (i, c0 + 4 q), q = 0..7
+        double tq[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) tq[q] = 0.0;
+#pragma unroll 4
+        for (int k = 0; k < 32; k++) {
+            const double li = S[32 + i][k];
+#pragma unroll
+            for (int q = 0; q < 8; q++) tq[q] = fma(li, X[k][c0 + 4 * q], tq[q]);  // X11 is zero above its diagonal
+        }
+#pragma unroll
+        for (int q = 0; q < 8; q++) X[c0 + 4 * q][32 + i] = tq[q];
+    }
+    __syncthreads();
+    LEAF_CLK(4);
+    // 6. X21 = -X22 T, 4 outputs per thread side by side
+    {
+        const int i = tid & 31, c0 = tid >> 5;
+        double xs[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 8
+        for (int k = 0; k < 32; k++) {
+            const double xi = X[32 + i][32 + k];  // X22 is zero above its diagonal
+#pragma unroll
+            for (int q = 0; q < 4; q++) xs[q] = fma(xi, X[c0 + 8 * q][32 + k], xs[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++) X[32 + i][c0 + 8 * q] = -xs[q];
+    }
+    __syncthreads();
+}
+
+}  // namespace dpb

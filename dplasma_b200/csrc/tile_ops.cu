@@ -170,13 +170,14 @@ int potrf_tile_lower(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, 
 int potrf_tile_fused(parsec_context_s* ctx, cudaStream_t s, double* A, int lda, int n, double* winv, int* dInfo,
                      int infoBase) {
     if (n <= 0) return 0;
-    static int mode = -1;  // DPB_POTRF_TILE=rec selects the recursive multi-launch variant
+    static int mode = -1;  // DPB_POTRF_TILE=rec: recursive multi-launch variant; =col: one launch per block column
     if (mode < 0) {
         const char* e = getenv("DPB_POTRF_TILE");
-        mode = (e && e[0] == 'r') ? 1 : 0;
+        mode = (e && e[0] == 'r') ? 1 : ((e && e[0] == 'c') ? 2 : 0);
     }
-    // the fused kernel is real-only; complex tiles take the recursive variant
+    // the fused kernels are real-only; complex tiles take the recursive variant
     if (mode == 1 || ctx->cplx) return potrf_rec(ctx, s, A, lda, winv, 0, n, dInfo, infoBase);
+    if (mode == 0) return launch_potrf_tile(ctx, s, A, lda, n, winv, dInfo, infoBase);  // one launch for the whole tile
     double* wdiag = winv + ctx->wInvSlot / 2;
     for (int j0 = 0; j0 < n; j0 += IB) {
         int rc = launch_potrf_colblock(ctx, s, A, lda, n, j0, winv + (size_t)(j0 / IB) * IB * IB,
