@@ -140,36 +140,49 @@ namespace dpb {
 // ---------------------------------------------------------------------------------------
 struct ArrivalModel {
     std::vector<double> landed;  // landed[jl]: modelled time at which local tile column jl is in HBM
-    double now = 0.0;            // modelled GPU time consumed by the steps enqueued so far
-    double rate = 28e12;         // sustained flop/s of the update kernel used for `now`
+    double now = 0.0;            // modelled time at which the GPU gets through what was enqueued so far
+    double rate = 34e12;         // flop/s of the update kernel (on the fast side: `now` early = fewer columns expected)
     void init(const DevMatrix& A, double bytesPerSecond) {
         if (const char* e = getenv("DPB_H2D_GBS")) bytesPerSecond = atof(e) * 1e9 / 0.85;  // tests: force a rate
         const double bw = 0.85 * (bytesPerSecond > 1e6 ? bytesPerSecond : 20e9);
         landed.assign(A.lnt, 0.0);
         double t = 0.0;
         for (int jl = 0; jl < A.lnt; jl++) {
-            const int gn = jl * A.Q + A.pcol;
-            const int rows = std::max(0, std::min(A.firstLocalRowGE(A.mt), A.lmt) - A.firstLocalRowGE(gn));
-            t += (double)rows * A.tileElems * 8.0 / bw;
+            t += tiles(A, jl, jl + 1) * A.tileElems * 8.0 / bw;
             landed[jl] = t;
         }
     }
-    // local flops of the trailing update of step k (my share of the (nt-k-1)(nt-k)/2 tiles) plus the panel
-    void step(const DevMatrix& A, int k) {
-        const double tiles = 0.5 * (double)(A.nt - k - 1) * (A.nt - k) / (A.P * A.Q);
-        now += 2.0 * tiles * A.nb * (double)A.nb * A.nb / rate + 0.8e-3;
+    // local tiles on or below the diagonal in local tile columns [jl0, jl1)
+    static double tiles(const DevMatrix& A, int jl0, int jl1) {
+        const int rowEnd = std::min(A.firstLocalRowGE(A.mt), A.lmt);
+        double n = 0.0;
+        for (int jl = std::max(jl0, 0); jl < std::min(jl1, A.lnt); jl++)
+            n += std::max(0, rowEnd - std::min(A.firstLocalRowGE(jl * A.Q + A.pcol), rowEnd));
+        return n;
     }
+    // `panels` rank-nb updates of the local columns [jl0, jl1) have been enqueued (either stream: they share the GPU)
+    void work(const DevMatrix& A, int jl0, int jl1, int panels) {
+        now += 2.0 * tiles(A, jl0, jl1) * panels * A.nb * (double)A.nb * A.nb / rate;
+    }
+    void overhead(double seconds) { now += seconds; }
+    // a stream was made to wait for the copy of local column jl
+    void waited(int jl) { if (jl >= 0 && jl < (int)landed.size()) now = std::max(now, landed[jl]); }
     // number of local columns modelled as landed by `now` (a prefix: copies are issued left to right)
     int arrived() const {
         int n = 0;
         while (n < (int)landed.size() && landed[n] <= now) n++;
         return n;
     }
-    // steps needed before everything has landed (the window during which earlier panels must stay available)
+    // steps a grid factorization should keep its panels for: until everything has landed even if the GPU had
+    // all the work of every step available (the real window may be shorter; it is capped by memory)
     int window(const DevMatrix& A, int cap) const {
         ArrivalModel m = *this;
         int w = 0;
-        while (w < cap && w < A.nt && m.arrived() < (int)landed.size()) { m.step(A, w); w++; }
+        while (w < cap && w < A.nt && m.arrived() < (int)landed.size()) {
+            m.work(A, A.firstLocalColGE(w + 1), A.lnt, 1);
+            m.overhead(1.5e-3);
+            w++;
+        }
         return w;
     }
 };
@@ -272,6 +285,12 @@ int symm_residual_1gpu(parsec_context_s* ctx, cudaStream_t s, int uplo, const De
 int inf_norm_public(parsec_context_s* ctx, const DevMatrix& A, bool sym, int uplo, double* out);
 // potrf.cu
 int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp);
+// DPB_TRACE=1: event timestamps at the end of every phase of every step, printed at parsec_context_wait
+// (phases: 0 potrf tile, 1 panel solve, 2 look-ahead update, 3 bulk update, 4 diagonal-tile broadcast,
+//  5 panel broadcasts, 6 catch-up of late columns)
+bool trace_on();
+void trace_begin(cudaStream_t s);
+void trace_mark(cudaStream_t s, int k, int phase);
 int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, const double* rowPanel,
                     long long rowStride, const double* colPanel, long long colStride, int gnFirst,
                     int gnEnd, double alpha, int K, int kTile = 0, long long kTileStride = 0, int rowFirstFixed = -1,

@@ -112,21 +112,26 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
 struct TraceRec { int k; int phase; cudaEvent_t ev; };
 static std::vector<TraceRec> g_trace;
 static cudaEvent_t g_trace0 = nullptr;
-static bool trace_on() {
+bool trace_on() {
     static int on = -1;
     if (on < 0) on = getenv("DPB_TRACE") ? 1 : 0;
     return on == 1;
 }
-static void trace_mark(cudaStream_t s, int k, int phase) {
+void trace_mark(cudaStream_t s, int k, int phase) {
     if (!trace_on()) return;
     cudaEvent_t e;
     cudaEventCreate(&e);
     cudaEventRecord(e, s);
     g_trace.push_back({k, phase, e});
 }
+void trace_begin(cudaStream_t s) {
+    if (!trace_on()) return;
+    if (!g_trace0) cudaEventCreate(&g_trace0);
+    cudaEventRecord(g_trace0, s);
+}
 void trace_dump() {
     if (!trace_on() || !g_trace0) return;
-    static const char* names[] = {"potrf", "trsm", "lookahead", "bulk"};
+    static const char* names[] = {"potrf", "trsm", "lookahead", "bulk", "bcast_diag", "bcast_panel", "catchup"};
     for (auto& r : g_trace) {
         float ms = 0;
         cudaEventElapsedTime(&ms, g_trace0, r.ev);
@@ -139,10 +144,7 @@ void trace_dump() {
 // ---- single-process schedule (P = Q = 1): panels are read in place from the matrix ----
 static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
     const int nt = A.nt, nb = A.nb;
-    if (trace_on()) {
-        if (!g_trace0) cudaEventCreate(&g_trace0);
-        cudaEventRecord(g_trace0, ctx->sPanel);
-    }
+    trace_begin(ctx->sPanel);
     int rc = ensure_winv(ctx, nb);
     if (rc) return rc;
     cudaStream_t sp = ctx->sPanel, su = ctx->sUpdate;
@@ -180,6 +182,7 @@ static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
         if (k >= avail) {  // first step, or a column that landed late: bring it up to date before factoring it
             rc = catch_up(sp, k + 1, k);
             if (rc) return rc;
+            if (arriving) { model.waited(k); model.work(A, avail, k + 1, k); }
             avail = k + 1;
         }
         rc = potrf_tile_fused(ctx, sp, Akk, A.mb, tk, winv, ctx->dInfo, k * nb);
@@ -205,6 +208,8 @@ static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
         if (evUpdPrev) DPB_CUDA(cudaStreamWaitEvent(sp, evUpdPrev, 0));
         if (k + 1 >= avail) {
             rc = catch_up(sp, k + 2, k + 1);  // not touched yet: panels 0 .. k at once
+            // the two streams share the GPU: what the panel stream does also lets time pass for the copies
+            if (arriving) { model.waited(k + 1); model.work(A, avail, k + 2, k + 1); }
             avail = k + 2;
         } else {
             rc = trailing_update(ctx, sp, A, panel, A.tileElems, panel, A.tileElems, k + 1, k + 2, -1.0, nb);
@@ -219,16 +224,20 @@ static int potrf_lower_1gpu(parsec_context_s* ctx, const DevMatrix& A) {
             if (rc) return rc;
             trace_mark(su, k, 3);
             bulk = true;
+            if (arriving) model.work(A, k + 2, availOld, 1);
         }
         if (avail < nt) {
-            // the columns expected to have landed by now: panels 0 .. k in one launch, behind their copy event
-            model.step(A, k);
+            // the columns expected to have landed by the time the GPU gets here: panels 0 .. k in one launch,
+            // behind their copy event
+            model.overhead(0.6e-3);  // tile factorization + panel solve of the step
             int target = std::max(avail, model.arrived());
             if (k + 3 >= nt) target = nt;
             if (target > avail) {
                 DPB_CUDA(cudaStreamWaitEvent(su, evPanel, 0));
                 rc = catch_up(su, target, k + 1);
                 if (rc) return rc;
+                trace_mark(su, k, 6);
+                model.work(A, avail, target, k + 1);
                 avail = target;
                 bulk = true;
             }

@@ -169,6 +169,7 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
     const int nt = A.nt, nb = A.nb;
     const size_t te = (size_t)A.tileElems;
     const size_t winvElems = (size_t)((nb + IB - 1) / IB) * IB * IB * A.esz;
+    trace_begin(sp);
     cudaEvent_t ev0 = dist_event(ctx, 0);
     DPB_CUDA(cudaEventRecord(ev0, sp));
     DPB_CUDA(cudaStreamWaitEvent(su, ev0, 0));
@@ -214,6 +215,8 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
             // normally did that one step ago; this is the first step, or a column that arrived late)
             rc = catch_up(sp, jlk + 1, (int)kept.size());
             if (rc) return rc;
+            model.waited(jlk);
+            model.work(A, avail, jlk + 1, (int)kept.size());
             cudaEvent_t evC = dist_event(ctx, evi++);
             DPB_CUDA(cudaEventRecord(evC, sp));
             DPB_CUDA(cudaStreamWaitEvent(su, evC, 0));
@@ -231,12 +234,14 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
                 DPB_CUDA(cudaMemcpyAsync(winv, ctx->wInv, winvElems * sizeof(double), cudaMemcpyDeviceToDevice, sp));
                 if (A.P > 1)
                     DPB_CUDA(cudaMemcpyAsync(b.diag, Akk, te * sizeof(double), cudaMemcpyDeviceToDevice, sp));
+                trace_mark(sp, k, 0);
             }
             const double* Lkk = b.diag;
             if (A.P == 1) Lkk = A.tile(k / A.P, jlk);
             else {
                 rc = bcast(ctx, ctx->commCol, b.diag, b.diag, te + winvElems, kp, sp);
                 if (rc) return rc;
+                trace_mark(sp, k, 4);
             }
             // ---- panel solve on my tiles of column k ----
             const int il0 = std::min(A.firstLocalRowGE(k + 1), rowEnd), cnt = rowEnd - il0;
@@ -245,6 +250,7 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
                 rc = trsm_panel_lower(ctx, sp, Lkk, A.mb, tk, winv, A.tile(il0, jlk), A.mb, A.mb, cnt, A.tileElems,
                                       A.rowsOfTile(lastGm));
                 if (rc) return rc;
+                trace_mark(sp, k, 1);
             }
             // my tiles of tile column k are final: a staged (host) matrix gets them back now
             if (ctx->curTp && ctx->earlyOut >= 0) {
@@ -260,6 +266,7 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
         PanelView pv;
         rc = panel_exchange(ctx, sp, A, k, k + 1, inCol ? A.tile(0, jlk) : nullptr, A.tileElems, set, true, &pv);
         if (rc) return rc;
+        trace_mark(sp, k, 5);
         cudaEvent_t evPanel = dist_event(ctx, evi++);
         DPB_CUDA(cudaEventRecord(evPanel, sp));
         const int availOld = avail;
@@ -271,6 +278,8 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
                 if (evUpdPrev) DPB_CUDA(cudaStreamWaitEvent(sp, evUpdPrev, 0));
                 rc = catch_up(sp, jl1 + 1, (int)kept.size());   // panels 0 .. k, this step's included
                 if (rc) return rc;
+                model.waited(jl1);
+                model.work(A, avail, jl1 + 1, (int)kept.size());
                 avail = jl1 + 1;
             }
         }
@@ -279,6 +288,7 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
         rc = trailing_update(ctx, sp, A, pv.rowPtr, pv.rowStride, pv.colPtr, pv.colStride, k + 1, k + 2, -1.0, nb, 0, 0, -1, 0,
                              availOld);
         if (rc) return rc;
+        trace_mark(sp, k, 2);
         // ---- bulk update on the update stream: the columns that had landed before this step ----
         bool bulk = false;
         if (k + 2 < nt) {
@@ -286,11 +296,14 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
             rc = trailing_update(ctx, su, A, pv.rowPtr, pv.rowStride, pv.colPtr, pv.colStride, k + 2, nt, -1.0, nb, 0, 0, -1, 0,
                                  availOld);
             if (rc) return rc;
+            trace_mark(su, k, 3);
             bulk = true;
+            if (arriving) model.work(A, A.firstLocalColGE(k + 2), availOld, 1);
         }
         if (avail < A.lnt) {
-            // columns expected to have landed by now: all panels so far, behind their copy event, after the bulk
-            model.step(A, k);
+            // columns expected to have landed by the time the GPU gets here: all panels so far, behind their copy
+            // event, after the bulk
+            model.overhead(1.5e-3);  // tile factorization, panel solve and panel broadcasts of the step
             int target = std::max(avail, model.arrived());
             if (k + 1 == window || k + 2 >= nt) target = A.lnt;
             if (target > avail) {
@@ -302,6 +315,8 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
                 DPB_CUDA(cudaStreamWaitEvent(su, evPanel, 0));
                 rc = catch_up(su, target, (int)kept.size());
                 if (rc) return rc;
+                trace_mark(su, k, 6);
+                model.work(A, avail, target, (int)kept.size());
                 avail = target;
                 bulk = true;
             }
