@@ -81,6 +81,7 @@ struct parsec_taskpool_s {
     double alpha = 1.0, beta = 0.0;
     const parsec_tiled_matrix_t* B = nullptr;
     parsec_tiled_matrix_t* C = nullptr;
+    bool ooc = false;   // host matrix larger than the device memory it may use: out-of-core schedule (potrf_ooc.cu)
     bool done = false;  // ran to completion inside parsec_context_start (mixed queues run in order)
 };
 
@@ -95,6 +96,8 @@ struct parsec_context_s {
     double* wInv = nullptr;     // 2 slots, each: inverted diagonal blocks + factored diagonal blocks (2*(maxNB/IB)*IB*IB doubles)
     size_t wInvSlot = 0;
     double* wNorm = nullptr;    // row-sum scratch for norms
+    double* wSolve = nullptr;   // solved RHS tile row of the grid solves
+    size_t wSolveLen = 0;
     size_t wNormLen = 0;
     // multi-GPU panel workspaces: panelSets sets of panelSetElems doubles in one allocation (two alternate in
     // steady state; more are kept alive while a host matrix is still arriving, see potrf_dist.cu)
@@ -249,6 +252,13 @@ int ensure_wnorm(parsec_context_s* ctx, size_t n);
 int stage_in(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* out, bool copyData, int uploOnly);
 int stage_out(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int uploOnly);
 void stage_free(DevMatrix* dm);
+int describe_matrix(const parsec_tiled_matrix_t* A, DevMatrix* dm);
+// local tile rows [i0, i1) of local tile column jl <-> consecutive device tiles from devBase (dir 0: in, 1: out)
+int stage_column_rows(const parsec_tiled_matrix_t* A, const DevMatrix* dm, int jl, int i0, int i1, double* devBase, int dir,
+                      cudaStream_t s);
+// potrf_ooc.cu
+bool ooc_wanted(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, int uplo);
+int potrf_out_of_core(parsec_context_s* ctx, parsec_taskpool_s* tp);
 int stage_in_pipelined(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* out, int uploOnly);
 int stage_out_column(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, int uploOnly,
                      cudaEvent_t ready);

@@ -366,6 +366,8 @@ int parsec_context_start(parsec_context_t* ctx) {
         const bool pipe = ctx->queue.size() == 1 && tp->uplo == dplasmaLower && tp->A->mtype == PARSEC_MATRIX_DOUBLE &&
                           !onDevice && tp->A->mb == tp->A->nb && tp->A->nb % 16 == 0 && tp->A->nt >= 4 &&
                           !getenv("DPB_NO_PIPELINE");
+        tp->ooc = ctx->queue.size() == 1 && ooc_wanted(ctx, tp->A, tp->uplo);
+        if (tp->ooc) continue;  // never resident as a whole: the out-of-core schedule moves its own blocks
         int rc = pipe ? stage_in_pipelined(ctx, tp->A, &tp->dA, tp->uplo) : stage_in(ctx, tp->A, &tp->dA, true, tp->uplo);
         if (rc) return rc;
         tp->staged = true;
@@ -378,7 +380,7 @@ int parsec_context_start(parsec_context_t* ctx) {
         const bool canEarly = tp->dA.owned && tp->uplo == dplasmaLower;
         ctx->curTp = canEarly ? tp : nullptr;
         ctx->earlyOut = canEarly ? 0 : -1;
-        int rc = potrf_enqueue(ctx, tp);
+        int rc = tp->ooc ? potrf_out_of_core(ctx, tp) : potrf_enqueue(ctx, tp);
         early[i] = canEarly ? ctx->earlyOut : 0;
         ctx->curTp = nullptr;
         if (rc) return rc;

@@ -435,6 +435,9 @@ int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T
 //   backward (Tm upper): B(k) = Tm(k,k)^-1 B(k); B(m) -= Tm(m,k) B(k), m < k   (ztrsm_LUN.jdf)
 // The transposed variants (LLT / LUT) run on a distributed transpose of the factor.
 // ---------------------------------------------------------------------------------------
+// The tile columns of Tm are final data: their broadcast along the grid rows for step k+1 is posted on the
+// communication stream while step k computes (two panel sets alternate); the solved RHS row travels down the grid
+// columns on the compute stream, where the next update needs it.
 static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower, int diag, double alpha,
                               const DevMatrix& Tm, const DevMatrix& B) {
     int rc = ensure_grid_comms(ctx, Tm.P, Tm.Q, Tm.ip, Tm.jq);
@@ -445,28 +448,59 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
     const int mt = Tm.mt;
     const int rowEnd = std::min(Tm.firstLocalRowGE(Tm.mt), Tm.lmt);
     const int colEndB = std::min(B.firstLocalColGE(B.nt), B.lnt);
-    double* xrow = nullptr;  // solved tile row k of the RHS, one tile per local RHS tile column
-    DPB_CUDA(cudaMalloc(&xrow, (size_t)std::max(colEndB, 1) * teB * sizeof(double)));
-    PanelBufs pb = panel_bufs(ctx, Tm, 0);
+    // solved tile row k of the RHS, one tile per local RHS tile column (context-owned, grown on demand)
+    const size_t xNeed = (size_t)std::max(colEndB, 1) * teB;
+    if (ctx->wSolveLen < xNeed) {
+        if (ctx->wSolve) { cudaStreamSynchronize(s); cudaFree(ctx->wSolve); }
+        ctx->wSolve = nullptr;
+        DPB_CUDA(cudaMalloc(&ctx->wSolve, xNeed * sizeof(double)));
+        ctx->wSolveLen = xNeed;
+    }
+    double* xrow = ctx->wSolve;
+    cudaStream_t sc = ctx->sComm;
+    const size_t evBase = 900;  // events of this routine (a factorization's own count up from 0)
+    cudaEvent_t evRecv[2] = {dist_event(ctx, evBase), dist_event(ctx, evBase + 1)};
+    cudaEvent_t evFree[2] = {dist_event(ctx, evBase + 2), dist_event(ctx, evBase + 3)};
+    cudaEvent_t evStart = dist_event(ctx, evBase + 4);
+    DPB_CUDA(cudaEventRecord(evStart, s));
+    DPB_CUDA(cudaStreamWaitEvent(sc, evStart, 0));  // Tm may have been produced on s just before
+    auto rows_of = [&](int k, int* ilA, int* cnt) {
+        // local tile rows that take part in step k: the diagonal tile's row and the rows still to update
+        const int a = lower ? std::min(Tm.firstLocalRowGE(k), rowEnd) : 0;
+        const int b = lower ? rowEnd : std::min(Tm.firstLocalRowGE(k + 1), rowEnd);
+        *ilA = a;
+        *cnt = b - a;
+    };
+    // (a) tile column k of Tm along the grid rows, into panel set kk & 1 (in place on the owners)
+    auto post_panel = [&](int kk) -> int {
+        const int k = lower ? kk : mt - 1 - kk, set = kk & 1;
+        const int kq = k % Tm.Q, jlk = k / Tm.Q;
+        int ilA, cnt;
+        rows_of(k, &ilA, &cnt);
+        if (kk >= 2) DPB_CUDA(cudaStreamWaitEvent(sc, evFree[set], 0));
+        if (Tm.Q > 1 && cnt > 0) {
+            const bool owner = (Tm.pcol == kq);
+            PanelBufs pb = panel_bufs(ctx, Tm, set);
+            double* buf = owner ? Tm.tile(ilA, jlk) : pb.row + (size_t)ilA * te;
+            int r = bcast(ctx, ctx->commRow, buf, buf, (size_t)cnt * te, kq, sc);
+            if (r) return r;
+        }
+        DPB_CUDA(cudaEventRecord(evRecv[set], sc));
+        return 0;
+    };
+    rc = post_panel(0);
     for (int kk = 0; kk < mt && !rc; kk++) {
-        const int k = lower ? kk : mt - 1 - kk;
+        const int k = lower ? kk : mt - 1 - kk, set = kk & 1;
         const int kp = k % Tm.P, kq = k % Tm.Q, jlk = k / Tm.Q;
         const int tk = Tm.rowsOfTile(k);
         const double lalpha = (kk == 0) ? alpha : 1.0;
-        // local tile rows that take part: the diagonal tile's row and the rows still to update
-        const int ilA = lower ? std::min(Tm.firstLocalRowGE(k), rowEnd) : 0;
-        const int ilB = lower ? rowEnd : std::min(Tm.firstLocalRowGE(k + 1), rowEnd);
-        const int cnt = ilB - ilA;
-        // (a) tile column k of Tm along the grid rows
-        const double* rowPtr = pb.row;
-        if (Tm.Q == 1) rowPtr = Tm.tile(0, jlk);
-        else if (cnt > 0) {
-            const bool owner = (Tm.pcol == kq);
-            double* buf = owner ? Tm.tile(ilA, jlk) : pb.row + (size_t)ilA * te;
-            if (owner) rowPtr = Tm.tile(0, jlk);
-            rc = bcast(ctx, ctx->commRow, buf, buf, (size_t)cnt * te, kq, s);
+        if (kk + 1 < mt) {
+            rc = post_panel(kk + 1);
             if (rc) break;
         }
+        DPB_CUDA(cudaStreamWaitEvent(s, evRecv[set], 0));
+        const double* rowPtr = panel_bufs(ctx, Tm, set).row;
+        if (Tm.Q == 1 || Tm.pcol == kq) rowPtr = Tm.tile(0, jlk);
         // (b) solve the RHS tiles of tile row k (ranks of grid row kp, each for its own RHS columns)
         const int ilk = k / Tm.P;
         if (Tm.prow == kp) {
@@ -499,9 +533,12 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
                                  false, xPtr + (size_t)jl * xStride, B.mb, true, lalpha, B.tile(u0, jl), B.mb, 0, u1 - u0,
                                  (long long)te, 0, (long long)teB, B.rowsOfTile(lastGm));
         }
+        DPB_CUDA(cudaEventRecord(evFree[set], s));
     }
-    cudaStreamSynchronize(s);
-    cudaFree(xrow);
+    // the communication stream must be idle before the caller reuses or frees the operands
+    cudaEvent_t evDone = dist_event(ctx, evBase + 5);
+    DPB_CUDA(cudaEventRecord(evDone, sc));
+    DPB_CUDA(cudaStreamWaitEvent(s, evDone, 0));
     return rc;
 }
 

@@ -52,6 +52,7 @@ int parsec_fini(parsec_context_t** pctx) {
     for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
     if (ctx->wInv) cudaFree(ctx->wInv);
     if (ctx->wNorm) cudaFree(ctx->wNorm);
+    if (ctx->wSolve) cudaFree(ctx->wSolve);
     if (ctx->panelBase) cudaFree(ctx->panelBase);
     if (ctx->tileSync) cudaFree(ctx->tileSync);
     for (int i = 0; i < 2; i++)
@@ -224,21 +225,21 @@ static int describe(const parsec_tiled_matrix_t* A, DevMatrix* dm) {
     return 0;
 }
 
-// Copies one local tile column between the caller's layout and the regular device tile grid.
-// dir 0: in, 1: out.  Only the `part` triangle moves (dplasmaUpperLower: everything).
-static int copy_column(const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, int dir, int part, cudaStream_t s) {
+// Copies local tile rows [i0, i1) of local tile column jl between the caller's layout and device tiles laid out
+// one after the other from devBase (tile of row i at devBase + (i - i0) * tileElems).  dir 0: in, 1: out.
+// For sym-packed storage the rows must lie inside the stored triangle.
+static int copy_column_rows(const parsec_tiled_matrix_t* A, const DevMatrix* dm, int jl, int i0, int i1, double* devBase,
+                            int dir, cudaStream_t s) {
     const parsec_matrix_block_cyclic_t* bc = (const parsec_matrix_block_cyclic_t*)A;
     double* user = (double*)bc->mat;
     const bool sym = bc->uplo != dplasmaUpperLower;
     const int gn = jl * dm->Q + dm->pcol;
-    int i0 = 0, i1 = dm->lmt;
-    if (part == dplasmaLower) i0 = dm->firstLocalRowGE(gn);
-    else if (part == dplasmaUpper) i1 = dm->firstLocalRowGE(gn + 1);
     if (i1 > dm->lmt) i1 = dm->lmt;
     if (i0 >= i1) return 0;
     if (A->storage == PARSEC_MATRIX_TILE) {
-        size_t packed = 0;  // tile offset of this column in a sym-packed array
-        if (sym)
+        size_t off;  // tile offset of (i0, jl) in the caller's array
+        if (sym) {
+            size_t packed = 0;
             for (int j = 0; j < jl; j++) {
                 const int g = j * dm->Q + dm->pcol;
                 int a = 0, b = dm->lmt;
@@ -246,12 +247,16 @@ static int copy_column(const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, in
                 else b = std::min(dm->firstLocalRowGE(g + 1), dm->lmt);
                 if (b > a) packed += (size_t)(b - a);
             }
+            const int first = (bc->uplo == dplasmaLower) ? dm->firstLocalRowGE(gn) : 0;
+            if (i0 < first) return -120;
+            off = packed + (size_t)(i0 - first);
+        } else {
+            off = (size_t)(i0 + dm->offR) + (size_t)(jl + dm->offC) * dm->userLmt;
+        }
         const size_t cnt = (size_t)(i1 - i0) * dm->tileElems;
-        double* dev = dm->tile(i0, jl);
-        double* usr = sym ? user + packed * dm->tileElems
-                          : user + ((size_t)(i0 + dm->offR) + (size_t)(jl + dm->offC) * dm->userLmt) * dm->tileElems;
-        if (dir == 0) DPB_CUDA(cudaMemcpyAsync(dev, usr, cnt * sizeof(double), cudaMemcpyDefault, s));
-        else DPB_CUDA(cudaMemcpyAsync(usr, dev, cnt * sizeof(double), cudaMemcpyDefault, s));
+        double* usr = user + off * dm->tileElems;
+        if (dir == 0) DPB_CUDA(cudaMemcpyAsync(devBase, usr, cnt * sizeof(double), cudaMemcpyDefault, s));
+        else DPB_CUDA(cudaMemcpyAsync(usr, devBase, cnt * sizeof(double), cudaMemcpyDefault, s));
         return 0;
     }
     // LAPACK storage: pitched copies, one per tile (src/dplasmajdf_lapack_dtt.h:161-178,238-255)
@@ -260,7 +265,7 @@ static int copy_column(const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, in
     for (int il = i0; il < i1; il++) {
         const int gm = il * dm->P + dm->prow;
         const int tm = dm->rowsOfTile(gm);
-        double* dev = dm->tile(il, jl);
+        double* dev = devBase + (size_t)(il - i0) * dm->tileElems;
         double* usr = user + ((size_t)(il + dm->offR) * dm->mb + (size_t)(jl + dm->offC) * dm->nb * lld) * dm->esz;
         if (dir == 0)
             DPB_CUDA(cudaMemcpy2DAsync(dev, (size_t)dm->mb * eb, usr, lld * eb, (size_t)tm * eb, tn, cudaMemcpyDefault, s));
@@ -268,6 +273,23 @@ static int copy_column(const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, in
             DPB_CUDA(cudaMemcpy2DAsync(usr, lld * eb, dev, (size_t)dm->mb * eb, (size_t)tm * eb, tn, cudaMemcpyDefault, s));
     }
     return 0;
+}
+int stage_column_rows(const parsec_tiled_matrix_t* A, const DevMatrix* dm, int jl, int i0, int i1, double* devBase, int dir,
+                      cudaStream_t s) {
+    return copy_column_rows(A, dm, jl, i0, i1, devBase, dir, s);
+}
+int describe_matrix(const parsec_tiled_matrix_t* A, DevMatrix* dm) { return describe(A, dm); }
+
+// Copies one local tile column between the caller's layout and the regular device tile grid.
+// dir 0: in, 1: out.  Only the `part` triangle moves (dplasmaUpperLower: everything).
+static int copy_column(const parsec_tiled_matrix_t* A, DevMatrix* dm, int jl, int dir, int part, cudaStream_t s) {
+    const int gn = jl * dm->Q + dm->pcol;
+    int i0 = 0, i1 = dm->lmt;
+    if (part == dplasmaLower) i0 = dm->firstLocalRowGE(gn);
+    else if (part == dplasmaUpper) i1 = dm->firstLocalRowGE(gn + 1);
+    if (i1 > dm->lmt) i1 = dm->lmt;
+    if (i0 >= i1) return 0;
+    return copy_column_rows(A, dm, jl, i0, i1, dm->tile(i0, jl), dir, s);
 }
 
 static int copy_layout(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* dm, int dir, int uploOnly) {

@@ -295,10 +295,8 @@ int dplasma_b200_dtrsm_tile(parsec_context_t* ctx, void* stream, dplasma_enum_t 
         return trsm_right(ctx, s, uplo, trans, diag, m, n, alpha, T, ldt, C, ldc, ctx->wInv, 1, 0, m);
     // Right side, the form the factorization uses: C <- C L^-T  (src/zpotrf_L.jdf:236-240)
     if (uplo == dplasmaLower && trans != dplasmaNoTrans && alpha == 1.0) {
-        rc = 0;
-        for (int j0 = 0; j0 < n && !rc; j0 += IB)
-            rc = launch_trtri_leaf(ctx, s, T + j0 + (size_t)j0 * ldt, ldt, std::min(IB, n - j0), uplo,
-                                   diag == dplasmaUnit, ctx->wInv + (size_t)(j0 / IB) * IB * IB);
+        // inverses of all 64 x 64 diagonal blocks in one launch
+        rc = launch_trtri_blocks(ctx, s, T, ldt, n, uplo, diag == dplasmaUnit, ctx->wInv);
         if (rc) return rc;
         return trsm_panel_lower(ctx, s, T, ldt, n, ctx->wInv, C, ldc, m, 1, 0, m);
     }

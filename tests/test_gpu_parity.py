@@ -699,3 +699,40 @@ def test_dpotrf_upper_more_than_65535_tile_pairs(ctx, oracle):
     assert relerr(np.triu(F), np.triu(want)) < VTOL
     assert np.array_equal(np.tril(F, -1), np.tril(A0, -1))
     d.free()
+
+
+@pytest.mark.parametrize("kind", ["tile", "sym", "lapack"])
+@pytest.mark.parametrize("N,nb,budget_mb", [(4096, 256, 90), (1700, 112, 6.5), (2048, 128, 7)])
+def test_dpotrf_out_of_core_host_matrix(ctx, oracle, kind, N, nb, budget_mb):
+    """a host matrix larger than the device memory the factorization may use (the reference's `lowmem` GPU test limits
+    PaRSEC's device tile cache the same way, tests/Testings.cmake:147): left-looking by blocks of tile columns, finished
+    columns streamed back from the host as update operands.  Same result as the in-core path, whatever the storage."""
+    import os
+    A0 = oracle.plgsy(float(N), Lower, N, nb, SEED_A)
+    want = A0.copy(order="F")
+    assert oracle.potrf(Lower, want, nb) == 0
+    os.environ["DPB_DEVICE_BUDGET_MB"] = str(budget_mb)
+    try:
+        if kind == "lapack":
+            M = np.asfortranarray(np.tril(A0) + np.triu(np.full((N, N), 7.0), 1))
+            d = dp.BlockCyclic(ctx.lib, N, N, nb, nb, kind="lapack", where="host")
+            d.host_array()[:N * N] = M.ravel(order="F")
+            assert ctx.lib.dplasma_dpotrf(ctx.ptr, Lower, d.ref) == 0
+            F = d.host_array()[:N * N].reshape((N, N), order="F").copy()
+            assert np.array_equal(np.triu(F, 1), np.triu(M, 1))
+        else:
+            d = make_host(ctx, A0, nb, nb, kind, Lower)
+            assert ctx.lib.dplasma_dpotrf(ctx.ptr, Lower, d.ref) == 0
+            F = read_host(d, N, N, nb, nb, kind, Lower, out=A0.copy(order="F") if kind == "sym" else None)
+            assert np.array_equal(np.triu(F, 1), np.triu(A0, 1))
+        # not positive definite: the global index of the first bad leading minor comes back like in core
+        B0 = A0.copy(order="F")
+        bad = 5 * nb + 3
+        B0[bad, bad] = -1.0
+        d2 = make_host(ctx, B0, nb, nb, "tile", Lower)
+        assert ctx.lib.dplasma_dpotrf(ctx.ptr, Lower, d2.ref) == bad + 1
+        d2.free()
+    finally:
+        os.environ.pop("DPB_DEVICE_BUDGET_MB", None)
+    assert relerr(np.tril(F), np.tril(want)) < VTOL
+    d.free()
