@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(256) potrf_colblock_kernel(double* __restrict_
     }
     __syncthreads();
     DBG_CLK(2);
-    leaf_fast_64(D, X, nj, tid, &failed, dInfo, infoBase + j0, isDiag);
+    leaf64(D, X, nj, &failed, dInfo, infoBase + j0, isDiag);
     DBG_CLK(3);
     // ---- 3. write back ----
     if (isDiag) {

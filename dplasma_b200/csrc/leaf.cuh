@@ -212,4 +212,13 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
     __syncthreads();
 }
 
+// The leaf keeps a 32-entry row of the block per lane in registers.  Inlined into a kernel body with block products
+// and staging loops around it, the register allocator ran out and moved that array to local memory -- a memory
+// round trip on every step of the dependent chain.  As a function of its own the leaf gets a clean register file,
+// for the price of one call.
+static __device__ __noinline__ void leaf64(double (*S)[IB + 1], double (*X)[IB + 1], int n, int* failed, int* dInfo,
+                                           int infoBase, bool report) {
+    leaf_fast_64(S, X, n, (int)threadIdx.x, failed, dInfo, infoBase, report);
+}
+
 }  // namespace dpb

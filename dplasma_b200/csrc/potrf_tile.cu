@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(256) potrf_tile_kernel(double* __restrict__ A,
     // factor the diagonal block held in S (lower triangle, identity padding), publish L(j,j) and X_j
     auto leaf_and_publish = [&](int j) {
         const int nj = bsize(j);
-        leaf_fast_64(S, X, nj, tid, &failed, dInfo, infoBase + j * IB, true);
+        leaf64(S, X, nj, &failed, dInfo, infoBase + j * IB, true);
         double* Ajj = A + (size_t)j * IB + (size_t)j * IB * lda;
         double* W = winv + (size_t)j * IB * IB;
         for (int e = tid; e < IB * IB; e += 256) {
