@@ -6,7 +6,9 @@
 
 namespace dpb {
 
+#ifndef DPB_DEBUG_CLOCKS
 __device__ long long g_leaf_clk[8];
+#endif
 
 // ---------------------------------------------------------------------------------------
 // Leaf of the in-tile recursion: factor an n x n (n <= 64) diagonal block A = L L^T in

@@ -72,7 +72,7 @@ __device__ __forceinline__ void leaf_cholesky_64(double (*S)[IB + 1], int n, int
 // 256 threads.  info rule as leaf_cholesky_64.
 // ---------------------------------------------------------------------------------------
 #ifdef DPB_DEBUG_CLOCKS
-extern __device__ long long g_leaf_clk[8];
+static __device__ long long g_leaf_clk[8];  // one copy per translation unit (no relocatable device code)
 #endif
 #ifdef DPB_DEBUG_CLOCKS
 #define LEAF_CLK(i) do { if (tid == 0 && report) g_leaf_clk[i] = clock64(); } while (0)
@@ -80,13 +80,19 @@ extern __device__ long long g_leaf_clk[8];
 #define LEAF_CLK(i) do { } while (0)
 #endif
 // warp-level: lane r owns row r of the 32x32 block at S[o..o+32)[o..o+32)
-__device__ __forceinline__ void warp_chol32(double (*S)[IB + 1], double* invd, int o, int lane, int nvalid,
+// warp-level: lane r owns row r of the 32x32 block at S[o..o+32)[o..o+32), the row lives in registers.
+// The sequential chain of a column is  broadcast of the pivot -> rsqrt -> scale -> update of the next pivot ;
+// each lane keeps the running diagonal entry of ITS row in a register of its own (dg), so the pivot update needs
+// no shuffle, and rsqrt(double) -- accurate to an ulp or two, far inside the 1e-11 the factor is held to -- gives
+// the square root and the reciprocal with one multiplication each.  All the shuffles of a column are issued before
+// the updates that use them (a warp issues in order).  The code is straight-line and long: it runs fast only from
+// a warm instruction cache, which is why one CTA runs every leaf of a tile (potrf_tile.cu).
+// Variants measured on B200 and rejected (us per 32x32 block, warm): block in shared memory with a rolled column
+// loop 19.6 (store-to-load ordering serialises the column); register row with a rolled column loop and predicated
+// static indices 29.7.
+__device__ __forceinline__ void warp_chol32(double (*S)[IB + 1], double* invd, double* col, int o, int lane, int nvalid,
                                             int* failed, int* dInfo, int infoBase, bool report) {
-    // The sequential chain of a column is  broadcast of the pivot -> rsqrt -> scale -> update of the next pivot ;
-    // everything else hides behind it.  Each lane therefore keeps the running diagonal entry of ITS row in a
-    // register of its own (dg): the pivot update needs no shuffle, and the one shuffle on the chain is the pivot
-    // broadcast.  rsqrt(double) is accurate to an ulp or two -- far inside the 1e-11 the factor is held to -- so
-    // the square root and the reciprocal come from it with one multiplication each.
+    (void)col;
     double a[32];
 #pragma unroll
     for (int c = 0; c < 32; c++) a[c] = S[o + lane][o + c];
@@ -100,11 +106,12 @@ __device__ __forceinline__ void warp_chol32(double (*S)[IB + 1], double* invd, i
         const double l = a[c] * inv;   // lanes > c: the column entry
         if (lane == c) { a[c] = d * inv; invd[o + c] = inv; }
         else if (lane > c) { a[c] = l; dg = fma(-l, l, dg); }
+        double lc[32];
 #pragma unroll
-        for (int c2 = c + 1; c2 < 32; c2++) {
-            const double lc2 = __shfl_sync(0xffffffffu, l, c2);
-            if (lane > c2) a[c2] = fma(-l, lc2, a[c2]);
-        }
+        for (int c2 = c + 1; c2 < 32; c2++) lc[c2] = __shfl_sync(0xffffffffu, l, c2);
+#pragma unroll
+        for (int c2 = c + 1; c2 < 32; c2++)
+            if (lane > c2) a[c2] = fma(-l, lc[c2], a[c2]);
     }
     if (report && lane == 0 && firstBad >= 0 && !*failed) {
         *failed = 1;
@@ -136,8 +143,9 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
                                              int* dInfo, int infoBase, bool report) {
     const int warp = tid >> 5, lane = tid & 31;
     __shared__ double invd[IB];  // reciprocals of the diagonal of L
+    LEAF_CLK(7);
     // 1. L11 = chol(A11)
-    if (warp == 0) warp_chol32(S, invd, 0, lane, min(n, 32), failed, dInfo, infoBase, report);
+    if (warp == 0) warp_chol32(S, invd, &X[0][0], 0, lane, min(n, 32), failed, dInfo, infoBase, report);
     __syncthreads();
     LEAF_CLK(0);
     // 2. warp 0: X11 = inv(L11) ; warp 1: L21 = A21 L11^-T (one row per lane, column-oriented forward substitution)
@@ -174,7 +182,7 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
     __syncthreads();
     LEAF_CLK(2);
     // 4. L22 = chol(A22)
-    if (warp == 0) warp_chol32(S, invd, 32, lane, max(0, min(n - 32, 32)), failed, dInfo, infoBase, report);
+    if (warp == 0) warp_chol32(S, invd, &X[32][32], 32, lane, max(0, min(n - 32, 32)), failed, dInfo, infoBase, report);
     __syncthreads();
     LEAF_CLK(3);
     // 5. warp 0: X22 = inv(L22) ; warps 1-4: T = L21 X11 parked in X's upper-right block (transposed), 8 outputs

@@ -116,7 +116,9 @@ __global__ void __launch_bounds__(256) potrf_tile_kernel(double* __restrict__ A,
     int arrivals = counterBase;
     if (tid == 0) failed = 0;
     auto bsize = [&](int b) { return min(IB, n - b * IB); };
-    auto leaf_cta = [&](int j) { return j % G; };
+    // ONE CTA runs every leaf (and the solve / update product in front of it): the leaf is long straight-line code
+    // that runs several times faster from a warm instruction cache than on an SM that sees it for the first time
+    auto leaf_cta = [&](int j) { (void)j; return 0; };
 
     // factor the diagonal block held in S (lower triangle, identity padding), publish L(j,j) and X_j
     auto leaf_and_publish = [&](int j) {
@@ -234,6 +236,14 @@ __global__ void __launch_bounds__(256) potrf_tile_kernel(double* __restrict__ A,
 }
 
 }  // namespace
+
+#ifdef DPB_DEBUG_CLOCKS
+// phase clocks of the last leaf of the last tile: [7] entry, [0] after chol(A11), [1] after inv(L11) | L21,
+// [2] after the A22 update, [3] after chol(A22), [4] after inv(L22) | T
+extern "C" int dplasma_b200_debug_read_tile_leaf(long long* leaf) {
+    return (int)cudaMemcpyFromSymbol(leaf, g_leaf_clk, sizeof(long long) * 8);
+}
+#endif
 
 // One launch for the whole tile.  `counter`: a device int owned by the context, only ever incremented -- the launch is
 // told where it stands (counterBase) so that no reset (and no memset node) is needed between tiles.  Consequence: the
