@@ -157,8 +157,10 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
     ArrivalModel model;
     int window = 0;
     if (arriving) {
+        // the panels of the first `window` steps stay alive (one set each, ~ (lmt + lnt) tiles) so that columns
+        // landing during those steps can be caught up
         model.init(A, ctx->h2dBw);
-        window = std::max(1, model.window(A, 6));
+        window = std::min(A.nt, 8);
     }
     const int nsets = std::max(2, window);
     int rc = ensure_grid_comms(ctx, A.P, A.Q, A.ip, A.jq);
@@ -305,7 +307,11 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
             // event, after the bulk
             model.overhead(1.5e-3);  // tile factorization, panel solve and panel broadcasts of the step
             int target = std::max(avail, model.arrived());
-            if (k + 1 == window || k + 2 >= nt) target = A.lnt;
+            // steps that find little to do are short, and the window is counted in steps: every step asks for its
+            // share of the columns at least, so that the waiting is spread over steps that have work to do instead
+            // of falling on the last step of the window
+            target = std::max(target, (int)(((long long)A.lnt * (k + 1) + window - 1) / window));
+            if (k + 1 >= window || k + 2 >= nt) target = A.lnt;
             if (target > avail) {
                 if (avail != availOld) {  // the panel stream has just written columns [availOld, avail)
                     cudaEvent_t evL = dist_event(ctx, evi++);
@@ -316,6 +322,7 @@ int potrf_multi(parsec_context_s* ctx, parsec_taskpool_s* tp) {
                 rc = catch_up(su, target, (int)kept.size());
                 if (rc) return rc;
                 trace_mark(su, k, 6);
+                model.waited(target - 1);
                 model.work(A, avail, target, (int)kept.size());
                 avail = target;
                 bulk = true;
