@@ -265,9 +265,10 @@ def run_reference(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel from the committed
 # `ncu --set full` capture (16384 x 16384 x 512 NT update = one bulk launch of C2 at k ~ 32); see profiles/
-GEMM_TRAFFIC = {"bytes": 7.03e9,
-                "note": "profiles/ncu_gemm_r01_final_summary.md: dram read 4.78 GB + write 2.25 GB for a launch whose "
-                        "algorithmic bytes are 4.43 GB (C read + write, both operand panels once) -> 1.59 x"}
+GEMM_TRAFFIC = {"bytes": 7.30e9,
+                "note": "profiles/ncu_gemm_r02_summary.md: dram read 5.15 GB + write 2.15 GB for a launch whose "
+                        "algorithmic bytes are 4.43 GB (C read + write, both operand panels once) -> 1.65 x, "
+                        "14 % of the HBM roof"}
 
 
 def flops_zpotrf(n):
