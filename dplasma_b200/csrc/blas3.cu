@@ -14,7 +14,7 @@
 
 namespace dpb {
 
-// C <- beta C on the stored part of a single-process tile grid: uplo = Lower (global i >= j),
+// C <- beta C on the stored part of the local tiles of a (distributed) tile grid: uplo = Lower (global i >= j),
 // Upper (i <= j) or UpperLower (everything); beta == 0 stores zeros (no 0 * NaN)
 __global__ void scale_grid_kernel(DevMatrix C, int uplo, double beta) {
     const long long total = (long long)C.lmt * C.lnt * C.tileElems;
@@ -22,7 +22,8 @@ __global__ void scale_grid_kernel(DevMatrix C, int uplo, double beta) {
          e += (long long)gridDim.x * blockDim.x) {
         const long long t = e / C.tileElems, r = e % C.tileElems;
         const int il = (int)(t % C.lmt), jl = (int)(t / C.lmt);
-        const long long gi = (long long)il * C.mb + (int)(r % C.mb), gj = (long long)jl * C.nb + (int)(r / C.mb);
+        const long long gi = ((long long)il * C.P + C.prow) * C.mb + (int)(r % C.mb);  // global element indices
+        const long long gj = ((long long)jl * C.Q + C.pcol) * C.nb + (int)(r / C.mb);
         if (gi >= C.M || gj >= C.N) continue;
         if (uplo == dplasmaLower && gi < gj) continue;
         if (uplo == dplasmaUpper && gi > gj) continue;
@@ -55,16 +56,37 @@ int dplasma_dgemm(parsec_context_t* parsec, dplasma_enum_t transA, dplasma_enum_
     const int M = C->m, N = C->n, K = An;
     if (M == 0 || N == 0 || ((alpha == 0.0 || K == 0) && beta == 1.0)) return 0;  // :716-719
     if (!parsec) return -100;
-    if (C->super.nodes > 1) {
-        fprintf(stderr, "dplasma_dgemm: not built for a process grid yet (single process only)\n");
-        return -101;
-    }
     if (A->mtype != PARSEC_MATRIX_DOUBLE || B->mtype != PARSEC_MATRIX_DOUBLE || C->mtype != PARSEC_MATRIX_DOUBLE) {
         fprintf(stderr, "dplasma_dgemm: only real double precision is built\n");
         return -101;
     }
     cudaSetDevice(parsec->device);
     cudaStream_t s = parsec->sPanel;
+    if (C->super.nodes > 1) {
+        // process grid: C = alpha A B^T + beta C on square C with one square tile size (src/zgemm_NT.jdf); the
+        // panels of A and B travel like the factorization's (potrf_dist.cu: gemm_nt_multi)
+        if (tA || !tB || C->m != C->n || C->mb != C->nb || Amb != C->mb || Anb != C->mb || Bmb != C->mb) {
+            fprintf(stderr, "dplasma_dgemm: on a process grid only C = alpha A B^T + beta C with square C and one square tile size is built\n");
+            return -101;
+        }
+        DevMatrix gA, gB, gC;
+        int grc = stage_in(parsec, A, &gA, true, dplasmaUpperLower);
+        if (!grc) grc = stage_in(parsec, B, &gB, true, dplasmaUpperLower);
+        if (!grc) grc = stage_in(parsec, C, &gC, beta != 0.0, dplasmaUpperLower);
+        if (!grc) grc = (int)cudaEventRecord(parsec->evStart, s);
+        if (!grc) grc = launch_scale_grid(parsec, s, gC, dplasmaUpperLower, beta);
+        if (!grc && alpha != 0.0 && K > 0) grc = gemm_nt_multi(parsec, s, alpha, gA, gB, gC);
+        if (!grc) grc = (int)cudaEventRecord(parsec->evStop, s);
+        if (!grc) grc = stage_out(parsec, C, &gC, dplasmaUpperLower);
+        cudaError_t ge = cudaStreamSynchronize(s);
+        float gms = 0.f;
+        if (!grc && cudaEventElapsedTime(&gms, parsec->evStart, parsec->evStop) == cudaSuccess) parsec->lastElapsed = gms * 1e-3;
+        stage_free(&gA);
+        stage_free(&gB);
+        stage_free(&gC);
+        if (grc) { fprintf(stderr, "dplasma_dgemm: internal error %d\n", grc); return -101; }
+        return ge == cudaSuccess ? 0 : -101;
+    }
     DevMatrix dA, dB, dC;
     double *At = nullptr, *Bt = nullptr;
     int rc = stage_in(parsec, A, &dA, true, dplasmaUpperLower);
@@ -118,8 +140,8 @@ int dplasma_dsyrk(parsec_context_t* parsec, dplasma_enum_t uplo, dplasma_enum_t 
     const bool tr = trans != dplasmaNoTrans;
     if ((!tr && A->m != C->m) || (tr && A->n != C->m)) { fprintf(stderr, "dplasma_dsyrk: illegal size of matrix A\n"); return -4; }
     if (!parsec) return -100;
-    if (C->super.nodes > 1) {
-        fprintf(stderr, "dplasma_dsyrk: not built for a process grid yet (single process only)\n");
+    if (C->super.nodes > 1 && (uplo != dplasmaLower || tr || A->nb != C->nb)) {
+        fprintf(stderr, "dplasma_dsyrk: on a process grid only dplasmaLower / dplasmaNoTrans with one square tile size is built\n");
         return -101;
     }
     if (A->mtype != PARSEC_MATRIX_DOUBLE || C->mtype != PARSEC_MATRIX_DOUBLE || C->mb != C->nb || (tr ? A->nb : A->mb) != C->nb) {
@@ -141,7 +163,7 @@ int dplasma_dsyrk(parsec_context_t* parsec, dplasma_enum_t uplo, dplasma_enum_t 
     // Upper: C(m,n)^T = alpha op(A)(n,:) op(A)(m,:)^T + beta C(m,n)^T is the lower problem on the transposed grid
     if (!rc && uplo == dplasmaUpper) rc = launch_transpose_grid(parsec, s, dC);
     if (!rc) rc = launch_scale_grid(parsec, s, dC, dplasmaLower, beta);
-    for (int k = 0; !rc && alpha != 0.0 && k < kt; k++) {
+    for (int k = 0; !rc && alpha != 0.0 && k < kt && C->super.nodes == 1; k++) {
         const int tk = (k == kt - 1) ? K - k * kb : kb;
         const double* panel = dA.tile(0, k);
         long long stride = dA.tileElems;
@@ -153,6 +175,8 @@ int dplasma_dsyrk(parsec_context_t* parsec, dplasma_enum_t uplo, dplasma_enum_t 
         // C(m,n) += alpha op(A)(m,k) op(A)(n,k)^T, m >= n (zsyrk_LN.jdf:24-55 diagonal tiles, :66-112 the others)
         if (!rc) rc = trailing_update(parsec, s, dC, panel, stride, panel, stride, 0, nt, alpha, tk);
     }
+    // process grid: the same per-k update, the panels of A exchanged like the factorization's (syrk_lower_multi)
+    if (!rc && alpha != 0.0 && K > 0 && C->super.nodes > 1) rc = syrk_lower_multi(parsec, s, alpha, dA, dC);
     if (!rc && uplo == dplasmaUpper) rc = launch_transpose_grid(parsec, s, dC);
     if (!rc) rc = (int)cudaEventRecord(parsec->evStop, s);
     if (!rc) rc = stage_out(parsec, C, &dC, uplo);

@@ -77,6 +77,7 @@ struct GemmDesc {
     int mtGlobal, ntGlobal;   // global tile counts
     int rowFirst[kMaxCols];   // per column: first local tile row with global m >= global n
     int rowEnd;               // local tile rows end (exclusive)
+    int full;                 // 1: general product, diagonal tiles are updated in full (no SYRK mask)
     int itemStart[kMaxCols + 1];  // prefix sum of work items (CTA tiles) per column
     // ---- tensor maps of the M-major operands (fast mode): 4-D views {rows, k, tile | batch, k-tile}
     alignas(64) CUtensorMap tmA;
@@ -260,7 +261,7 @@ __device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
     w.A = d.rowPanel + (size_t)i * d.rowPanelStride + i0;
     w.B = d.colPanel + (size_t)j * d.colPanelStride + j0;
     w.C = d.Cbase + ((size_t)i + (size_t)j * d.tileLdT) * d.tileElems + i0 + (size_t)j0 * d.nb;
-    w.lower = (gm == gn);
+    w.lower = (gm == gn) && !d.full;
     w.gi0 = i0; w.gj0 = j0;
     w.aRow = i0; w.aTile = i; w.bRow = j0; w.bTile = j;
     if (w.lower && (i0 + w.M - 1 < j0)) w.valid = false;

@@ -125,6 +125,7 @@ struct parsec_context_s {
     std::vector<cudaEvent_t> evIn;       // per local tile column: its host-to-device copy has landed (pipelined stage-in)
     double seqElapsed = -1.0;  // >= 0: GPU seconds summed over a queue that ran operation by operation
     int cplx = 0;         // set by the drivers while they work on a complex (esz = 2) matrix
+    int gemmFull = 0;     // grouped update of a general (not symmetric) matrix: no SYRK mask on diagonal tiles
     int gemmPreload = 1;  // internal products preload C into the accumulators; the tile seam API does not
     // optional per-kernel profile of the trailing-update launches (bench.py roofline leg)
     int profile = 0;
@@ -281,6 +282,9 @@ int trsm_left_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, 
 int symm_residual_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, const DevMatrix& A, const DevMatrix& X,
                         const DevMatrix& B);
 int check_update_multi(parsec_context_s* ctx, const DevMatrix& L, const DevMatrix& R);
+// grid forms of the level-3 operations (potrf_dist.cu): the factorization's panel exchange with gmFirst = 0
+int syrk_lower_multi(parsec_context_s* ctx, cudaStream_t s, double alpha, const DevMatrix& A, const DevMatrix& C);
+int gemm_nt_multi(parsec_context_s* ctx, cudaStream_t s, double alpha, const DevMatrix& A, const DevMatrix& B, const DevMatrix& C);
 // potri.cu
 enum { OP_TRTRI = 1, OP_LAUUM = 2, OP_POTRF = 4 };
 int run_inverse_chain(parsec_context_s* ctx, const char* name, int ops, int uplo, int diag, parsec_tiled_matrix_t* A,

@@ -51,6 +51,7 @@ int trailing_update(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& C, c
         d.lastM = C.rowsOfTile(C.mt - 1); d.lastN = C.colsOfTile(C.nt - 1);
         d.mtGlobal = C.mt; d.ntGlobal = C.nt;
         d.rowEnd = rowEnd;
+        d.full = ctx->gemmFull;
         if (ctx->cplx) d.fast = (K % 8 == 0) ? 1 : 0;
         else d.fast = ((C.nb % 2 == 0) && (kTile % 16 == 0) && (kTileStride % 2 == 0) && ((reinterpret_cast<uintptr_t>(rowPanel) & 15) == 0) &&
                   ((reinterpret_cast<uintptr_t>(colPanel) & 15) == 0) && (rowStride % 2 == 0) &&

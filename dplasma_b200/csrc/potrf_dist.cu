@@ -379,6 +379,50 @@ int check_update_multi(parsec_context_s* ctx, const DevMatrix& L, const DevMatri
 }
 
 // ---------------------------------------------------------------------------------------
+// Level-3 operations on a process grid (src/zsyrk_LN.jdf, src/zgemm_NT.jdf distributed by PaRSEC's remote dependencies):
+// per tile column k of the operand, the factorization's panel exchange with gmFirst = 0 -- A(m,k) along the grid row
+// of m, and the operand of the other side down the grid column of n -- then ONE grouped update launch of the local
+// tiles of C.  Operands and C share the grid and the (square) tile size.  C has been scaled by beta already.
+//   syrk:  C(m,n) += alpha A(m,k) A(n,k)^T   m >= n, diagonal tiles in their lower part
+//   gemm:  C(m,n) += alpha A(m,k) B(n,k)^T   all local tiles
+// ---------------------------------------------------------------------------------------
+int syrk_lower_multi(parsec_context_s* ctx, cudaStream_t s, double alpha, const DevMatrix& A, const DevMatrix& C) {
+    if (A.P != C.P || A.Q != C.Q || A.ip != C.ip || A.jq != C.jq || A.mb != C.mb || A.nb != C.nb || C.mb != C.nb) return -102;
+    if (C.P * C.Q != ctx->nranks) return -303;
+    int rc = ensure_grid_comms(ctx, C.P, C.Q, C.ip, C.jq);
+    if (!rc) rc = ensure_panel_bufs(ctx, C);
+    for (int k = 0; !rc && k < A.nt; k++) {
+        const bool inCol = (A.pcol == k % A.Q);
+        PanelView pv;
+        rc = panel_exchange(ctx, s, C, k, 0, inCol ? A.tile(0, k / A.Q) : nullptr, A.tileElems, k & 1, true, &pv);
+        if (!rc) rc = trailing_update(ctx, s, C, pv.rowPtr, pv.rowStride, pv.colPtr, pv.colStride, 0, C.nt, alpha, A.colsOfTile(k));
+    }
+    return rc;
+}
+
+int gemm_nt_multi(parsec_context_s* ctx, cudaStream_t s, double alpha, const DevMatrix& A, const DevMatrix& B,
+                  const DevMatrix& C) {
+    // square C only: both exchanges then run on the plan of one nt x nt tile grid
+    if (C.M != C.N || C.mb != C.nb || A.mb != C.mb || A.nb != C.nb || B.mb != C.mb || B.nb != C.nb) return -102;
+    if (A.P != C.P || A.Q != C.Q || B.P != C.P || B.Q != C.Q || A.ip != C.ip || A.jq != C.jq || B.ip != C.ip || B.jq != C.jq) return -102;
+    if (C.P * C.Q != ctx->nranks) return -303;
+    int rc = ensure_grid_comms(ctx, C.P, C.Q, C.ip, C.jq);
+    if (!rc) rc = ensure_panel_bufs(ctx, C);
+    ctx->gemmFull = 1;
+    for (int k = 0; !rc && k < A.nt; k++) {
+        const bool inCol = (C.pcol == k % C.Q);
+        PanelView pa, pb;
+        // rows of the product come from A's tile column k, columns from B's: two exchanges, one panel set each
+        rc = panel_exchange(ctx, s, C, k, 0, inCol ? A.tile(0, k / A.Q) : nullptr, A.tileElems, 0, true, &pa);
+        if (!rc) rc = panel_exchange(ctx, s, C, k, 0, inCol ? B.tile(0, k / B.Q) : nullptr, B.tileElems, 1, true, &pb);
+        if (!rc) rc = trailing_update(ctx, s, C, pa.rowPtr, pa.rowStride, pb.colPtr, pb.colStride, 0, C.nt, alpha, A.colsOfTile(k), 0,
+                                      0, 0);
+    }
+    ctx->gemmFull = 0;
+    return rc;
+}
+
+// ---------------------------------------------------------------------------------------
 // Distributed transpose of a triangle:  Tt(n,m) = T(m,n)^T for every stored tile (m,n) of T.
 // Tile (m,n) lives on rank (m%P)*Q + n%Q, its image on rank (n%P)*Q + m%Q: point-to-point
 // NCCL send/recv, one group per global tile column, then a local transposing copy.
