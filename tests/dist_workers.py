@@ -662,3 +662,52 @@ def gloo_gemm_syrk_worker(rank, world, port, P, Q, M, N, K, nb, q):
         q.put((rank, err_gemm, err_syrk))
     finally:
         dist.destroy_process_group()
+
+
+def nccl_blas3_worker(rank, world, port, P, Q, N, K, nb, q):
+    """GPU: dplasma_dsyrk (Lower / NoTrans) and dplasma_dgemm (NoTrans, Trans) on a P x Q grid, device-resident
+    operands, against numpy on the full matrices (the single-process forms are checked against the oracle and the
+    reference's CORE kernels in tests/test_gpu_blas3.py)."""
+    import torch
+    import dplasma_b200 as dp
+    from oracle.oracle import Oracle
+    from tests.util import full_to_local
+    torch.cuda.set_device(rank)
+    dist = _init(rank, world, port, "nccl")
+    try:
+        lib = dp.load()
+        ctx = dp.Context(lib)
+        ids = [ctx.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.comm_init(ids[0], rank, world)
+        orc = Oracle()
+        A = orc.plrnt(N, K, nb, nb, 101)
+        B = orc.plrnt(N, K, nb, nb, 202)
+        C0 = orc.plrnt(N, N, nb, nb, 303)
+
+        def dev(Mx):
+            d = dp.BlockCyclic(lib, Mx.shape[0], Mx.shape[1], nb, nb, P, Q, rank, where=1)
+            t = torch.from_numpy(full_to_local(Mx, nb, nb, P, Q, rank).copy()).cuda() if d.elems else torch.zeros(1, dtype=torch.float64, device="cuda")
+            d.s.mat = t.data_ptr()
+            return d, t
+        dA, tA = dev(A)
+        dB, tB = dev(B)
+        alpha, beta = -0.75, 0.5
+        # dsyrk: only the lower triangle of C changes
+        dC, tC = dev(C0)
+        rc1 = lib.dplasma_dsyrk(ctx.ptr, dp.Lower, dp.NoTrans, alpha, dA.ref, beta, dC.ref)
+        torch.cuda.synchronize()
+        want = np.where(np.tril(np.ones((N, N), dtype=bool)), alpha * (A @ A.T) + beta * C0, C0)
+        got = tC.cpu().numpy()[:dC.elems]
+        e1 = float(np.abs(got - full_to_local(want, nb, nb, P, Q, rank)).max() / np.abs(want).max()) if dC.elems else 0.0
+        # dgemm NT: the whole of C
+        dC2, tC2 = dev(C0)
+        rc2 = lib.dplasma_dgemm(ctx.ptr, dp.NoTrans, dp.Trans, alpha, dA.ref, dB.ref, beta, dC2.ref)
+        torch.cuda.synchronize()
+        want2 = alpha * (A @ B.T) + beta * C0
+        got2 = tC2.cpu().numpy()[:dC2.elems]
+        e2 = float(np.abs(got2 - full_to_local(want2, nb, nb, P, Q, rank)).max() / np.abs(want2).max()) if dC2.elems else 0.0
+        q.put((rank, rc1, e1, rc2, e2))
+        ctx.close()
+    finally:
+        dist.destroy_process_group()

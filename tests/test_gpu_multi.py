@@ -220,3 +220,29 @@ def test_dpoinv_dpotri_dtrtri_grid_match_oracle(P, Q, uplo):
         assert e1 < 1e-11 and e2 < 1e-11 and e3 < 1e-11, (rank, e1, e2, e3)
         assert o1 and o2 and o3, (rank, o1, o2, o3)      # the other triangle is never touched
         assert info4 == res[0][10] and info4 > 0           # MAX-reduced, identical on every rank
+
+
+@pytest.mark.parametrize("P,Q", [(1, 2), (2, 1), (2, 2), (2, 4)])
+@pytest.mark.parametrize("N,K,nb", [(1000, 700, 128), (2048, 1024, 256)])
+def test_dgemm_dsyrk_grid(P, Q, N, K, nb):
+    """level-3 operations on a process grid (src/zgemm_NT.jdf, src/zsyrk_LN.jdf): the panels of the operands travel
+    like the factorization's, one grouped update launch per tile column of the operand; ragged last tiles included"""
+    import torch
+    import torch.multiprocessing as mp
+    from tests.dist_workers import nccl_blas3_worker
+    world = P * Q
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=nccl_blas3_worker, args=(r, world, port, P, Q, N, K, nb, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for rank, rc1, e1, rc2, e2 in res:
+        assert rc1 == 0 and rc2 == 0, (rank, rc1, rc2)
+        assert e1 < 1e-12 and e2 < 1e-12, (rank, e1, e2)
