@@ -103,15 +103,21 @@ __device__ __forceinline__ void warp_chol32(double (*S)[IB + 1], double* invd, d
         const double d = __shfl_sync(0xffffffffu, dg, c);
         if (firstBad < 0 && c < nvalid && !(d > 0.0)) firstBad = c;
         const double inv = rsqrt(d);
+        // branch-free on purpose: every lane computes, selects keep what is its own (a lane-dependent branch here
+        // becomes a divergent branch with a reconvergence point in front of every shuffle)
         const double l = a[c] * inv;   // lanes > c: the column entry
-        if (lane == c) { a[c] = d * inv; invd[o + c] = inv; }
-        else if (lane > c) { a[c] = l; dg = fma(-l, l, dg); }
+        const bool below = lane > c;
+        a[c] = (lane == c) ? d * inv : (below ? l : a[c]);
+        dg = below ? fma(-l, l, dg) : dg;
+        if (lane == c) invd[o + c] = inv;
         double lc[32];
 #pragma unroll
         for (int c2 = c + 1; c2 < 32; c2++) lc[c2] = __shfl_sync(0xffffffffu, l, c2);
 #pragma unroll
-        for (int c2 = c + 1; c2 < 32; c2++)
-            if (lane > c2) a[c2] = fma(-l, lc[c2], a[c2]);
+        for (int c2 = c + 1; c2 < 32; c2++) {
+            const double u = fma(-l, lc[c2], a[c2]);
+            a[c2] = (lane > c2) ? u : a[c2];
+        }
     }
     if (report && lane == 0 && firstBad >= 0 && !*failed) {
         *failed = 1;
@@ -139,14 +145,73 @@ __device__ __forceinline__ void warp_trinv32(double (*S)[IB + 1], double (*X)[IB
     for (int i = 0; i < 32; i++) X[o + i][o + lane] = (i >= lane) ? x[i] : 0.0;
 }
 
+// 32x32 Cholesky by the whole CTA (256 threads), left-looking by panels of 8 columns, block in shared memory:
+//   (1) all threads: panel(rows >= c0, 8 columns) -= B(rows, 0:c0) B(c0:c0+8, 0:c0)^T     one output per thread
+//   (2) warp 0, lane = row c0 + lane, its 8 panel entries in registers: the 8 columns in sequence
+//       (pivot shuffle -> rsqrt -> scale -> own-diagonal update on the chain; 7 shuffles + multiply-adds beside it)
+// The panel loop is rolled and its body is a few hundred instructions: the sequential part is 8 columns long,
+// everything else is parallel multiply-adds from shared memory.
+__device__ __forceinline__ void block_chol32(double (*S)[IB + 1], double* invd, int o, int tid, int nvalid, int* failed,
+                                             int* dInfo, int infoBase, bool report) {
+    const int lane = tid & 31, warp = tid >> 5;
+    int firstBad = -1;
+#pragma unroll 1
+    for (int c0 = 0; c0 < 32; c0 += 8) {
+        if (c0 > 0) {
+            const int c = c0 + (tid & 7), r = c0 + (tid >> 3);
+            if (r < 32 && r >= c) {
+                double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll 4
+                for (int k = 0; k < c0; k += 2) {
+                    acc0 = fma(S[o + r][o + k], S[o + c][o + k], acc0);
+                    acc1 = fma(S[o + r][o + k + 1], S[o + c][o + k + 1], acc1);
+                }
+                S[o + r][o + c] -= acc0 + acc1;
+            }
+            __syncthreads();
+        }
+        if (warp == 0) {
+            const int r = c0 + lane;          // my row; rows beyond the block idle with zeros
+            const bool live = r < 32;
+            double row[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) row[j] = (live && r >= c0 + j) ? S[o + r][o + c0 + j] : 0.0;
+            double dg = live ? S[o + r][o + r] : 1.0;   // running diagonal entry of my row (meaningful for lanes < 8 here)
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const double d = __shfl_sync(0xffffffffu, (lane == j) ? row[j] : dg, j);   // pivot of column c0+j lives in lane j
+                if (firstBad < 0 && c0 + j < nvalid && !(d > 0.0)) firstBad = c0 + j;
+                const double inv = rsqrt(d);
+                const double l = row[j] * inv;
+                const bool below = lane > j;
+                row[j] = (lane == j) ? d * inv : (below ? l : row[j]);
+                if (lane == j) invd[o + c0 + j] = inv;
+#pragma unroll
+                for (int j2 = j + 1; j2 < 8; j2++) {
+                    const double lj2 = __shfl_sync(0xffffffffu, l, j2);
+                    const double u = fma(-l, lj2, row[j2]);
+                    row[j2] = (lane >= j2) ? u : row[j2];
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 8; j++)
+                if (live && r >= c0 + j) S[o + r][o + c0 + j] = row[j];
+        }
+        __syncthreads();
+    }
+    if (report && tid == 0 && firstBad >= 0 && !*failed) {
+        *failed = 1;
+        if (*dInfo == 0) *dInfo = infoBase + o + firstBad + 1;
+    }
+}
+
 __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB + 1], int n, int tid, int* failed,
                                              int* dInfo, int infoBase, bool report) {
     const int warp = tid >> 5, lane = tid & 31;
     __shared__ double invd[IB];  // reciprocals of the diagonal of L
     LEAF_CLK(7);
     // 1. L11 = chol(A11)
-    if (warp == 0) warp_chol32(S, invd, &X[0][0], 0, lane, min(n, 32), failed, dInfo, infoBase, report);
-    __syncthreads();
+    block_chol32(S, invd, 0, tid, min(n, 32), failed, dInfo, infoBase, report);
     LEAF_CLK(0);
     // 2. warp 0: X11 = inv(L11) ; warp 1: L21 = A21 L11^-T (one row per lane, column-oriented forward substitution)
     if (warp == 0) warp_trinv32(S, X, invd, 0, lane);
@@ -182,8 +247,7 @@ __device__ __forceinline__ void leaf_fast_64(double (*S)[IB + 1], double (*X)[IB
     __syncthreads();
     LEAF_CLK(2);
     // 4. L22 = chol(A22)
-    if (warp == 0) warp_chol32(S, invd, &X[32][32], 32, lane, max(0, min(n - 32, 32)), failed, dInfo, infoBase, report);
-    __syncthreads();
+    block_chol32(S, invd, 32, tid, max(0, min(n - 32, 32)), failed, dInfo, infoBase, report);
     LEAF_CLK(3);
     // 5. warp 0: X22 = inv(L22) ; warps 1-4: T = L21 X11 parked in X's upper-right block (transposed), 8 outputs
     //    per thread side by side

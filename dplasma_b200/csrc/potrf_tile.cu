@@ -19,6 +19,7 @@
 // X_j goes to the workspace the panel TRSM of the step reads (winv, 64 x 64 column-major per block, zeros above
 // the diagonal).  The strict upper triangle of the tile is never written.
 #include <cstdio>
+#include <cstdlib>
 #include "internal.h"
 #include "leaf.cuh"
 
@@ -36,16 +37,25 @@ __device__ __forceinline__ int ld_acquire(const int* p) {
     return v;
 }
 
-// all CTAs of the grid arrive; `target` = arrivals expected so far (monotonic counter, never reset inside a launch)
-__device__ __forceinline__ void grid_barrier(int* counter, int target) {
+// Grid barrier on a monotonic counter (never reset inside a launch), split in two: a CTA that does not depend on
+// the others at this point arrives and goes on.  `target` = arrivals expected so far.
+__device__ __forceinline__ void grid_arrive(int* counter) {
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
         atomicAdd(counter, 1);
+    }
+}
+__device__ __forceinline__ void grid_wait(int* counter, int target) {
+    if (threadIdx.x == 0) {
         while (ld_acquire(counter) < target) __nanosleep(32);
         __threadfence();
     }
     __syncthreads();
+}
+__device__ __forceinline__ void grid_barrier(int* counter, int target) {
+    grid_arrive(counter);
+    grid_wait(counter, target);
 }
 
 // stage a 64 x 64 column-major block (rows r0.., cols c0.. of A) as dst[k][row] (k = column): column k of the block
@@ -100,6 +110,13 @@ __device__ __forceinline__ void block_product(const double* opA, const double* o
     }
 }
 
+#ifdef DPB_DEBUG_CLOCKS
+__device__ long long g_tile_clk[32 * 8];
+#define TILE_CLK(step, ph) do { if (tid == 0 && (step) < 32) g_tile_clk[(step) * 8 + (ph)] = clock64(); } while (0)
+#else
+#define TILE_CLK(step, ph) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(256) potrf_tile_kernel(double* __restrict__ A, int lda, int n, double* __restrict__ winv,
                                                          int* counter, int counterBase, int* dInfo, int infoBase) {
     extern __shared__ double pt_smem[];
@@ -118,7 +135,7 @@ __global__ void __launch_bounds__(256) potrf_tile_kernel(double* __restrict__ A,
     auto bsize = [&](int b) { return min(IB, n - b * IB); };
     // ONE CTA runs every leaf (and the solve / update product in front of it): the leaf is long straight-line code
     // that runs several times faster from a warm instruction cache than on an SM that sees it for the first time
-    auto leaf_cta = [&](int j) { (void)j; return 0; };
+    auto leaf_cta = [&](int j) { (void)j; return 0; };  // == leafCta below
 
     // factor the diagonal block held in S (lower triangle, identity padding), publish L(j,j) and X_j
     auto leaf_and_publish = [&](int j) {
@@ -146,21 +163,80 @@ __global__ void __launch_bounds__(256) potrf_tile_kernel(double* __restrict__ A,
         __syncthreads();
         leaf_and_publish(0);
     }
+    const int leafCta = 0;
     for (int j = 0; j < nblk; j++) {
         arrivals += G;
         grid_barrier(counter, arrivals);  // leaf(j) published, update(j-1) complete
         if (j == nblk - 1) break;
         const int nj = bsize(j);
-        const int nextLeaf = leaf_cta(j + 1);
-        // ---- solve(j): item i <-> row block b = j+1+i; item 0 belongs to the next leaf CTA ----
+        if (me == leafCta) TILE_CLK(j, 0);
+        if (me == leafCta) {
+            // ---- the chain of the tile, on one CTA, without waiting for anybody in between:
+            //      A(j+1,j) <- A(j+1,j) X_j^T ;  A(j+1,j+1) -= A(j+1,j) A(j+1,j)^T ;  leaf(j+1) ----
+            const int b = j + 1, nr = bsize(b);
+            // opB[k][c] = X_j(c,k), straight from the inverse this CTA has just computed (X is zero above its diagonal
+            // only where the leaf wrote it: mask)
+            for (int e = tid; e < IB * IB; e += 256) {
+                const int c = e % IB, k2 = e / IB;
+                opB[k2 * PT_LD + c] = (c >= k2) ? X[c][k2] : 0.0;
+            }
+            stage_block(opA, A, lda, b * IB, j * IB, nr, nj, fast, tid);
+            stage_commit_wait();
+            double o[4][2][2];
+            block_product(opA, opB, o, warp, lane);
+            double* Abj = A + (size_t)b * IB + (size_t)j * IB * lda;
+            __syncthreads();  // everybody has read opA: it now receives the solved block, as the operand of the update
+#pragma unroll
+            for (int jj = 0; jj < 2; jj++)
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int col = pn0 + frag_col(2 * t + h, jj);
+#pragma unroll
+                    for (int ii = 0; ii < 4; ii++) {
+                        const int row = pm0 + frag_row<32>(g, ii);
+                        const bool ok = row < nr && col < nj;
+                        if (ok) Abj[row + (size_t)col * lda] = o[ii][jj][h];
+                        opA[col * PT_LD + row] = ok ? o[ii][jj][h] : 0.0;
+                    }
+                }
+            TILE_CLK(j, 1);
+            arrivals += G;
+            grid_arrive(counter);  // solve(j): my block is out; the update below needs nobody else's
+            TILE_CLK(j, 2);
+            block_product(opA, opA, o, warp, lane);
+            for (int e = tid; e < IB * IB; e += 256) {
+                const int r = e % IB, q = e / IB;
+                S[r][q] = (r == q) ? 1.0 : 0.0;
+                X[r][q] = 0.0;
+            }
+            __syncthreads();
+            double* Abb = A + (size_t)b * IB + (size_t)b * IB * lda;
+#pragma unroll
+            for (int jj = 0; jj < 2; jj++)
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int col = pn0 + frag_col(2 * t + h, jj);
+#pragma unroll
+                    for (int ii = 0; ii < 4; ii++) {
+                        const int row = pm0 + frag_row<32>(g, ii);
+                        if (row >= nr || col >= nr || row < col) continue;  // lower triangle of the diagonal block
+                        S[row][col] = __ldcg(Abb + row + (size_t)col * lda) - o[ii][jj][h];
+                    }
+                }
+            __syncthreads();
+            TILE_CLK(j, 3);
+            leaf_and_publish(j + 1);
+            TILE_CLK(j, 4);
+            if (G > 1) continue;  // with one CTA the rest of the step is mine as well
+        }
+        // ---- solve(j): row blocks b = j+2 .. (item 0, b = j+1, was the leaf CTA's), spread over the other CTAs ----
+        const int others = (G > 1) ? G - 1 : 1, myIdx = (G > 1) ? me - 1 : 0;
         {
-            const int items = nblk - j - 1;
+            const int items = nblk - j - 2;
             bool haveX = false;
-            for (int i = 0; i < items; i++) {
-                const int owner = (i == 0) ? nextLeaf : ((G == 1) ? 0 : (nextLeaf + 1 + (i - 1) % (G - 1)) % G);
-                if (owner != me) continue;
-                const int b = j + 1 + i, nr = bsize(b);
-                if (!haveX) {  // opB[k][c] = X_j(c,k): the inverse as stored (column-major 64 x 64, zeros above the diagonal)
+            for (int i = myIdx; i < items; i += others) {
+                const int b = j + 2 + i, nr = bsize(b);
+                if (!haveX) {  // opB[k][c] = X_j(c,k): the inverse as published (column-major 64 x 64, zeros above the diagonal)
                     stage_block(opB, winv + (size_t)j * IB * IB, IB, 0, 0, IB, IB, true, tid);
                     haveX = true;
                 }
@@ -183,16 +259,21 @@ __global__ void __launch_bounds__(256) potrf_tile_kernel(double* __restrict__ A,
                 __syncthreads();  // operands free for the next item
             }
         }
-        arrivals += G;
-        grid_barrier(counter, arrivals);  // solve(j) complete
-        // ---- update(j): blocks (b,c), j < c <= b, column-major enumeration; item 0 = (j+1,j+1) for the next leaf CTA ----
+        if (G > 1) {
+            arrivals += G;
+            grid_barrier(counter, arrivals);  // solve(j) complete
+        } else {
+            __syncthreads();
+        }
+        // ---- update(j): blocks (b,c), j < c <= b, except (j+1,j+1) (the leaf CTA's), column-major enumeration ----
         {
             const int m = nblk - j - 1;  // block rows / columns of the trailing part
-            int item = 0;
+            int item = -1;
             for (int cc = 0; cc < m; cc++) {
-                for (int bb2 = cc; bb2 < m; bb2++, item++) {
-                    const int owner = (item == 0) ? nextLeaf : ((G == 1) ? 0 : (nextLeaf + 1 + (item - 1) % (G - 1)) % G);
-                    if (owner != me) continue;
+                for (int bb2 = cc; bb2 < m; bb2++) {
+                    if (cc == 0 && bb2 == 0) continue;
+                    item++;
+                    if (item % others != myIdx) continue;
                     const int b = j + 1 + bb2, c = j + 1 + cc, nr = bsize(b), nc = bsize(c);
                     stage_block(opA, A, lda, b * IB, j * IB, nr, nj, fast, tid);
                     stage_block(opB, A, lda, c * IB, j * IB, nc, nj, fast, tid);
@@ -201,16 +282,6 @@ __global__ void __launch_bounds__(256) potrf_tile_kernel(double* __restrict__ A,
                     block_product(opA, opB, o, warp, lane);
                     double* Abc = A + (size_t)b * IB + (size_t)c * IB * lda;
                     const bool diag = (b == c);
-                    const bool toLeaf = (item == 0);
-                    if (toLeaf) {
-                        // the updated diagonal block stays on chip: S = lower triangle with identity padding
-                        for (int e = tid; e < IB * IB; e += 256) {
-                            const int r = e % IB, q = e / IB;
-                            S[r][q] = (r == q) ? 1.0 : 0.0;
-                            X[r][q] = 0.0;
-                        }
-                        __syncthreads();
-                    }
 #pragma unroll
                     for (int jj = 0; jj < 2; jj++)
 #pragma unroll
@@ -222,13 +293,10 @@ __global__ void __launch_bounds__(256) potrf_tile_kernel(double* __restrict__ A,
                                 if (row >= nr || col >= nc) continue;
                                 if (diag && row < col) continue;  // the strict upper triangle of the tile is not ours
                                 double* p = Abc + row + (size_t)col * lda;
-                                const double v = __ldcg(p) - o[ii][jj][h];
-                                if (toLeaf) S[row][col] = v;
-                                else *p = v;
+                                *p = __ldcg(p) - o[ii][jj][h];
                             }
                         }
                     __syncthreads();
-                    if (toLeaf) leaf_and_publish(j + 1);
                 }
             }
         }
@@ -243,6 +311,11 @@ __global__ void __launch_bounds__(256) potrf_tile_kernel(double* __restrict__ A,
 extern "C" int dplasma_b200_debug_read_tile_leaf(long long* leaf) {
     return (int)cudaMemcpyFromSymbol(leaf, g_leaf_clk, sizeof(long long) * 8);
 }
+// per step j (rows of 8), clocks of the chain CTA: 0 after barrier 1, 1 after its solve product, 2 after its arrival at
+// barrier 2, 3 after its update product, 4 after leaf(j+1) is published
+extern "C" int dplasma_b200_debug_read_tile_steps(long long* steps) {
+    return (int)cudaMemcpyFromSymbol(steps, g_tile_clk, sizeof(long long) * 32 * 8);
+}
 #endif
 
 // One launch for the whole tile.  `counter`: a device int owned by the context, only ever incremented -- the launch is
@@ -253,7 +326,9 @@ int launch_potrf_tile(parsec_context_s* ctx, cudaStream_t s, double* A, int lda,
     if (n <= 0) return 0;
     DPB_SMEM_OPT_IN(potrf_tile_kernel, PT_SMEM);
     const int nblk = (n + IB - 1) / IB;
-    int G = nblk <= 1 ? 1 : std::min(2 * nblk, 32);
+    // enough CTAs that the first update phases (nblk (nblk - 1) / 2 block products) are two or three products deep
+    int G = nblk <= 1 ? 1 : (nblk <= 8 ? 2 * nblk : std::min(4 * nblk, 64));
+    if (const char* e = getenv("DPB_TILE_CTAS")) G = std::max(1, atoi(e));
     if (!ctx->tileSync) {
         DPB_CUDA(cudaMalloc(&ctx->tileSync, 64));
         DPB_CUDA(cudaMemset(ctx->tileSync, 0, 64));

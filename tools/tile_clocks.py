@@ -24,4 +24,13 @@ l = [leaf[7]] + [leaf[k] for k in range(5)]
 names = ["chol(A11)", "inv(L11)|L21", "A22 update", "chol(A22)", "inv(L22)|T"]
 print(f"n={n} (debug build) whole call {e0.elapsed_time(e1) * 1e3:.1f} us; last leaf, us: " +
       ", ".join(f"{nm} {(l[k + 1] - l[k]) / MHZ:.1f}" for k, nm in enumerate(names)))
+steps = (C.c_longlong * 256)()
+lib.dll.dplasma_b200_debug_read_tile_steps.argtypes = [C.c_void_p]
+assert lib.dll.dplasma_b200_debug_read_tile_steps(steps) == 0
+nblk = (n + 63) // 64
+for j in range(min(nblk - 1, 31)):
+    c = [steps[j * 8 + k] for k in range(5)]
+    nxt = steps[(j + 1) * 8] if j + 1 < nblk - 1 else None
+    print(f"  step {j:2d} (us): solve {(c[1]-c[0])/MHZ:5.1f}  arrive {(c[2]-c[1])/MHZ:4.1f}  update {(c[3]-c[2])/MHZ:5.1f}  leaf {(c[4]-c[3])/MHZ:5.1f}" +
+          (f"  barrier-1 wait {(nxt-c[4])/MHZ:5.1f}" if nxt else ""))
 ctx.close()
