@@ -523,6 +523,27 @@ def run_ours(args):
     except (MemoryError, AssertionError) as ex:  # host RAM too small for the pinned copy
         e2e = {"value": None, "unit": "TFLOP/s", "error": repr(ex)}
 
+    # ---- dplasmaUpper (what the reference's own testing_zpotrf.c:21 runs), outside the timed region ----
+    upper = None
+    try:
+        ts = []
+        for it in range(2):
+            assert lib.dplasma_dplgsy(ctx.ptr, float(N), dp.Upper, d0.ref, SEED) == 0
+            barrier()
+            info = lib.dplasma_dpotrf(ctx.ptr, dp.Upper, d0.ref)
+            assert info == 0, info
+            ts.append(_allmax(torch, dist, lib.dplasma_b200_last_elapsed(ctx.ptr))[0])
+        dU0 = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, where="device")
+        assert lib.dplasma_dplgsy(ctx.ptr, float(N), dp.Upper, dU0.ref, SEED) == 0
+        ubad = lib.check_dpotrf(ctx.ptr, 0, dp.Upper, d0.ref, dU0.ref)
+        ures = lib.dplasma_b200_last_check_result(ctx.ptr)
+        dU0.free()
+        ubad, ures = _allmax(torch, dist, ubad, ures)
+        upper = {"workload": "same matrix, uplo = dplasmaUpper (lower schedule on the transposed tile grid)",
+                 "seconds": min(ts), "tflops": flops / min(ts) / 1e12, "residual": ures, "passed": bool(ubad == 0 and ures < 60)}
+    except AssertionError as ex:
+        upper = {"error": repr(ex)}
+
     # ---- BASELINE.json configs[3] / configs[4], outside the timed region, on the grids they name ----
     d0.free()
     bufs = []
@@ -560,6 +581,7 @@ def run_ours(args):
             "residual": residual, "gpu_launches": int(launches), "clocks": clocks,
             "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
         }
+        out["upper"] = upper
         out.update(extra)
         print(json.dumps(out))
     ctx.close()
