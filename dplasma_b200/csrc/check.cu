@@ -162,14 +162,11 @@ int check_dpotrf(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec
     DevMatrix dA, dA0, R;
     double* diagCopy = nullptr;
     double Anorm = 0.0, Rnorm = 0.0, result = NAN;
+    bool swapped = false;
     const int N = A->n;
     const double eps = 0x1.0p-53;  // LAPACKE_dlamch_work('e'), src/dplasma_zcheck.c:77
     int rc = stage_in(parsec, A, &dA, true, uplo);
     if (!rc) rc = stage_in(parsec, A0, &dA0, true, uplo);
-    if (!rc && dA.esz == 2 && uplo != dplasmaLower && multi) {
-        fprintf(stderr, "check_zpotrf: dplasmaUpper on a process grid is not built yet\n");
-        rc = -2;
-    }
     if (!rc) rc = inf_norm(parsec, dA0, true, uplo, &Anorm);
     parsec->cplx = (!rc && dA.esz == 2);
     if (!rc) {
@@ -182,18 +179,21 @@ int check_dpotrf(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec
         if (!rc && cudaMemcpyAsync(R.base, dA0.base, elems * sizeof(double), cudaMemcpyDeviceToDevice, s) != cudaSuccess) rc = -201;
     }
     if (!rc && uplo == dplasmaUpper && multi) {
-        // grid: bring both the factor and A0 to lower form through the distributed transpose
+        // grid: both the factor and A0 in lower form on the swapped grid (local transposes, potrf_dist.cu)
         DevMatrix Lt, Rt;
+        Lt.base = Rt.base = nullptr;
         rc = ensure_grid_comms(parsec, dA.P, dA.Q, dA.ip, dA.jq);
-        if (!rc) rc = alloc_like(dA, &Lt);
-        if (!rc) rc = alloc_like(dA, &Rt);
-        if (!rc) rc = dist_transpose_tri(parsec, s, dA, dplasmaUpper, Lt);
-        if (!rc) rc = dist_transpose_tri(parsec, s, R, dplasmaUpper, Rt);
+        if (!rc) rc = transposed_copy(parsec, s, dA, dplasmaUpper, &Lt);
+        if (!rc) rc = transposed_copy(parsec, s, R, dplasmaUpper, &Rt);
         if (!rc) {
             stage_free(&dA);
             stage_free(&R);
             dA = Lt;
             R = Rt;
+            swapped = true;
+        } else {
+            if (Lt.base) cudaFree(Lt.base);
+            if (Rt.base) cudaFree(Rt.base);
         }
     }
     if (!rc && uplo == dplasmaUpper && !multi) {
@@ -211,7 +211,11 @@ int check_dpotrf(parsec_context_t* parsec, int loud, dplasma_enum_t uplo, parsec
         }
         if (!rc) rc = launch_transpose_grid(parsec, s, dA);
     }
-    if (!rc && multi) rc = check_update_multi(parsec, dA, R);
+    if (!rc && multi) {
+        if (swapped) swap_grid_comms(parsec);
+        rc = check_update_multi(parsec, dA, R);
+        if (swapped) swap_grid_comms(parsec);
+    }
     for (int k = 0; !rc && !multi && k < dA.nt; k++) {
         const int tk = dA.rowsOfTile(k), below = dA.nt - k - 1;
         // D = tril(L(k,k)) with the strict upper part zeroed (dplasma_zlacpy(uplo), src/dplasma_zcheck.c:90)

@@ -226,6 +226,9 @@ int launch_trtri_blocks(parsec_context_s* ctx, cudaStream_t s, const double* T, 
 int trsm_left_rec_entry(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int n, int ncols, double alpha,
                         const double* T, int ldt, const double* winv, double* B, int ldb);
 int launch_transpose_grid(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A);
+int transposed_copy(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int uplo, DevMatrix* W);  // potrf_dist.cu
+void swap_grid_comms(parsec_context_s* ctx);
+int launch_transpose_local(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& S, const DevMatrix& D, int uplo);
 int launch_transpose_upper_into(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst,
                                 int ldd, int n);
 int launch_transpose(parsec_context_s* ctx, cudaStream_t s, const double* src, int lds, double* dst, int ldd,

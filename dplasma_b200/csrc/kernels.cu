@@ -1048,6 +1048,47 @@ int launch_transpose_grid(parsec_context_s* ctx, cudaStream_t s, const DevMatrix
     return (int)cudaGetLastError();
 }
 
+// Transposition of the LOCAL part of a block-cyclic tile grid into a second buffer: local tile (il, jl) of S goes,
+// (conjugate-)transposed, to local tile (jl, il) of D.  On the process that holds tile (m, n) of a P x Q distribution the
+// result is tile (n, m) of the transposed matrix distributed over the Q x P grid whose coordinates are the swapped
+// ones, so no tile leaves its GPU.  Only the tiles of the `uplo` triangle of S are moved; full mb x nb buffers.
+template <typename T>
+__global__ void __launch_bounds__(256) transpose_local_kernel(DevMatrix S, DevMatrix D, int upper) {
+    __shared__ T t[32][33];
+    const int bi = blockIdx.x * 32, bj = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int nb = S.mb;
+    const long long tiles = (long long)S.lmt * S.lnt;
+    for (long long z = blockIdx.z; z < tiles; z += gridDim.z) {
+        const int il = (int)(z % S.lmt), jl = (int)(z / S.lmt);
+        const int gm = S.prow + il * S.P, gn = S.pcol + jl * S.Q;
+        if (gm >= S.mt || gn >= S.nt || (upper ? gm > gn : gm < gn)) continue;
+        const T* src = reinterpret_cast<const T*>(S.tile(il, jl));
+        T* dst = reinterpret_cast<T*>(D.tile(jl, il));
+        __syncthreads();
+        for (int j = ty; j < 32; j += 8)
+            if (bi + tx < nb && bj + j < nb) t[j][tx] = src[(bi + tx) + (size_t)(bj + j) * nb];
+        __syncthreads();
+        for (int j = ty; j < 32; j += 8)
+            if (bj + tx < nb && bi + j < nb) {
+                T v = t[tx][j];
+                if constexpr (sizeof(T) == 16) v.y = -v.y;
+                dst[(bj + tx) + (size_t)(bi + j) * nb] = v;
+            }
+    }
+}
+int launch_transpose_local(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& S, const DevMatrix& D, int uplo) {
+    if (S.mb != S.nb || S.lmt != D.lnt || S.lnt != D.lmt || S.tileElems != D.tileElems) return -3;
+    const long long tiles = (long long)S.lmt * S.lnt;
+    if (tiles == 0) return 0;
+    const int nblk = (S.mb + 31) / 32;
+    dim3 grid(nblk, nblk, (unsigned)(tiles > 65535 ? 65535 : tiles));
+    if (S.esz == 2) transpose_local_kernel<double2><<<grid, 256, 0, s>>>(S, D, uplo == dplasmaUpper);
+    else transpose_local_kernel<double><<<grid, 256, 0, s>>>(S, D, uplo == dplasmaUpper);
+    ctx->launches++;
+    return (int)cudaGetLastError();
+}
+
 // C <- beta C on an m x n column-major tile (part: 0 all, 1 lower, 2 upper); beta == 0 stores zeros
 __global__ void scale_tile_kernel(double* __restrict__ C, int ldc, int m, int n, double beta, int part) {
     for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < (long long)m * n;

@@ -270,31 +270,32 @@ int potrf_enqueue(parsec_context_s* ctx, parsec_taskpool_s* tp) {
         ctx->cplx = 0;
         return rc;
     }
-    if (ctx->cplx && A.P * A.Q != 1) {
-        ctx->cplx = 0;
-        fprintf(stderr, "dplasma_b200: zpotrf with dplasmaUpper on a process grid is not built yet\n");
-        return -2;
-    }
-    // dplasmaUpper (src/zpotrf_U.jdf): U(k,n) = L(n,k)^T and every tile operation of the upper
-    // DAG is the transpose of its lower counterpart, so the factorization runs as the lower
+    // dplasmaUpper (src/zpotrf_U.jdf): U(k,n) = L(n,k)^H and every tile operation of the upper
+    // DAG is the (conjugate) transpose of its lower counterpart, so the factorization runs as the lower
     // schedule on the transposed tile grid and is transposed back (two HBM-bound passes).
     if (A.P * A.Q != 1) {
-        // grid: factor the distributed transpose as a lower problem, transpose the factor back
-        if (A.P * A.Q != ctx->nranks) return -303;
+        // grid: the process that holds tile (m, n) of the P x Q distribution holds tile (n, m) of the transpose
+        // distributed over the Q x P grid with swapped coordinates -- each rank transposes its own tiles into a
+        // second buffer, the lower schedule runs on that view with the row and column communicators exchanged,
+        // and the factor is transposed back in place.  No tile crosses NVLink for the transposition.
+        if (A.P * A.Q != ctx->nranks) { ctx->cplx = 0; return -303; }
         int rc = ensure_grid_comms(ctx, A.P, A.Q, A.ip, A.jq);
         DevMatrix W;
-        if (!rc) rc = alloc_like(A, &W);
-        if (!rc) rc = dist_transpose_tri(ctx, ctx->sPanel, A, dplasmaUpper, W);
+        W.base = nullptr;
+        if (!rc) rc = transposed_copy(ctx, ctx->sPanel, A, dplasmaUpper, &W);
         if (!rc) {
+            swap_grid_comms(ctx);
             parsec_taskpool_s low = *tp;
             low.uplo = dplasmaLower;
             low.dA = W;
             low.dA.owned = false;
             rc = potrf_multi(ctx, &low);
+            swap_grid_comms(ctx);
         }
-        if (!rc) rc = dist_transpose_tri(ctx, ctx->sPanel, W, dplasmaLower, A);
+        if (!rc) rc = launch_transpose_local(ctx, ctx->sPanel, W, A, dplasmaLower);
         cudaStreamSynchronize(ctx->sPanel);
-        stage_free(&W);
+        if (W.base) cudaFree(W.base);
+        ctx->cplx = 0;
         return rc;
     }
     int rc = launch_transpose_grid(ctx, ctx->sPanel, A);  // conjugate transpose for complex tiles

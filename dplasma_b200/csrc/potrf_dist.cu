@@ -439,6 +439,33 @@ int alloc_like(const DevMatrix& A, DevMatrix* out) {
     return 0;
 }
 
+// The transpose of a P x Q block-cyclic matrix, seen on the Q x P grid with swapped coordinates: the process that
+// holds tile (m, n) holds tile (n, m) of the transpose, so the copy is local to each GPU (one HBM-bound launch) and
+// what changes is the description -- P <-> Q, prow <-> pcol, RSRC <-> CSRC, local tile rows <-> columns.  The row
+// communicator of the swapped grid is the column communicator of the original and vice versa (swap_grid_comms);
+// an operation that works on ONE matrix (factorization, residual) can run on the swapped grid as it stands.
+int transposed_copy(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& A, int uplo, DevMatrix* W) {
+    *W = A;
+    W->base = nullptr;
+    W->owned = true;
+    std::swap(W->P, W->Q); std::swap(W->prow, W->pcol); std::swap(W->ip, W->jq);
+    std::swap(W->lmt, W->lnt); std::swap(W->mt, W->nt); std::swap(W->M, W->N);
+    std::swap(W->mb, W->nb);
+    W->offR = W->offC = 0; W->userLmt = 0;
+    const size_t elems = std::max<size_t>((size_t)A.lmt * A.lnt * A.tileElems, 1);
+    if (cudaMalloc(&W->base, elems * sizeof(double)) != cudaSuccess) {
+        cudaGetLastError();
+        W->owned = false;
+        return -131;
+    }
+    return launch_transpose_local(ctx, s, A, *W, uplo);
+}
+void swap_grid_comms(parsec_context_s* ctx) {
+    std::swap(ctx->commRow, ctx->commCol);
+    std::swap(ctx->gridP, ctx->gridQ);
+    std::swap(ctx->gridIp, ctx->gridJq);
+}
+
 int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T, int uplo, const DevMatrix& Tt) {
     if (T.mb != T.nb || T.mt != T.nt) return -320;
     const size_t te = (size_t)T.tileElems;

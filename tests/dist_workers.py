@@ -120,7 +120,7 @@ def gloo_cholesky_worker(rank, world, port, P, Q, N, nb, q):
         dist.destroy_process_group()
 
 
-def nccl_potrf_worker(rank, world, port, P, Q, N, nb, q, check_values, cplx=False):
+def nccl_potrf_worker(rank, world, port, P, Q, N, nb, q, check_values, cplx=False, uplo_name="L"):
     """GPU: dplasma_dpotrf (or zpotrf) on a P x Q grid, one process per GPU, through the C ABI."""
     import torch
     import dplasma_b200 as dp
@@ -133,6 +133,8 @@ def nccl_potrf_worker(rank, world, port, P, Q, N, nb, q, check_values, cplx=Fals
         ids = [ctx.unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
         ctx.comm_init(ids[0], rank, world)
+        uplo = dp.Lower if uplo_name == "L" else dp.Upper
+        tri = np.tril if uplo == dp.Lower else np.triu
         dA = dp.BlockCyclic(lib, N, N, nb, nb, P, Q, rank, where=1, cplx=cplx)   # descriptor first, buffer from torch
         tA = torch.zeros(max(dA.elems, 1), dtype=torch.float64, device="cuda")
         dA.s.mat = tA.data_ptr()
@@ -140,31 +142,31 @@ def nccl_potrf_worker(rank, world, port, P, Q, N, nb, q, check_values, cplx=Fals
         gen = lib.dplasma_zplghe if cplx else lib.dplasma_dplgsy
         fac = lib.dplasma_zpotrf if cplx else lib.dplasma_dpotrf
         chk = lib.check_zpotrf if cplx else lib.check_dpotrf
-        assert gen(ctx.ptr, float(N), dp.Lower, dA.ref, 3872) == 0
-        assert gen(ctx.ptr, float(N), dp.Lower, dA0.ref, 3872) == 0
-        info = fac(ctx.ptr, dp.Lower, dA.ref)
+        assert gen(ctx.ptr, float(N), uplo, dA.ref, 3872) == 0
+        assert gen(ctx.ptr, float(N), uplo, dA0.ref, 3872) == 0
+        info = fac(ctx.ptr, uplo, dA.ref)
         t = lib.dplasma_b200_last_elapsed(ctx.ptr)
-        bad = chk(ctx.ptr, 0, dp.Lower, dA.ref, dA0.ref)
+        bad = chk(ctx.ptr, 0, uplo, dA.ref, dA0.ref)
         res = lib.dplasma_b200_last_check_result(ctx.ptr)
         err = -1.0
         if check_values:
             from oracle.oracle import Oracle
             orc = Oracle()
             pch = "z" if cplx else "d"
-            want = orc.plgsy(float(N), dp.Lower, N, nb, 3872, pch)
-            assert orc.potrf(dp.Lower, want, nb, pch) == 0
-            wl = full_to_local(np.tril(want), nb, nb, P, Q, rank)
+            want = orc.plgsy(float(N), uplo, N, nb, 3872, pch)
+            assert orc.potrf(uplo, want, nb, pch) == 0
+            wl = full_to_local(tri(want), nb, nb, P, Q, rank)
             from tests.util import local_to_full
             torch.cuda.synchronize()
             g = tA.cpu().numpy()[:dA.elems]
             if cplx:
                 g = g.view(np.complex128)
-            # compare only the lower-triangular entries (tiles above the diagonal are never touched)
-            gl = full_to_local(np.tril(local_to_full(g, N, N, nb, nb, P, Q, rank)), nb, nb, P, Q, rank)
+            # compare only the entries of the stored triangle (tiles of the other one are never touched)
+            gl = full_to_local(tri(local_to_full(g, N, N, nb, nb, P, Q, rank)), nb, nb, P, Q, rank)
             err = float(np.abs(gl - wl).max() / np.abs(want).max())
         # not positive definite: info must come back as the MAX over ranks of the global index
-        assert gen(ctx.ptr, 0.0, dp.Lower, dA.ref, 3872) == 0
-        info_bad = fac(ctx.ptr, dp.Lower, dA.ref)
+        assert gen(ctx.ptr, 0.0, uplo, dA.ref, 3872) == 0
+        info_bad = fac(ctx.ptr, uplo, dA.ref)
         q.put((rank, info, bad, res, err, t, info_bad))
         dA0.free()
         ctx.close()

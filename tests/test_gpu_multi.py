@@ -26,7 +26,7 @@ def free_port():
     raise RuntimeError("no free rendezvous port")
 
 
-def run_grid(P, Q, N, nb, check_values, cplx=False):
+def run_grid(P, Q, N, nb, check_values, cplx=False, uplo="L"):
     import torch
     import torch.multiprocessing as mp
     from tests.dist_workers import nccl_potrf_worker
@@ -36,7 +36,7 @@ def run_grid(P, Q, N, nb, check_values, cplx=False):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = free_port()
-    procs = [ctx.Process(target=nccl_potrf_worker, args=(r, world, port, P, Q, N, nb, q, check_values, cplx)) for r in range(world)]
+    procs = [ctx.Process(target=nccl_potrf_worker, args=(r, world, port, P, Q, N, nb, q, check_values, cplx, uplo)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=240) for _ in range(world)]
@@ -54,6 +54,18 @@ def test_dpotrf_grid_matches_oracle(P, Q, N, nb):
         assert info == 0 and bad == 0 and 0.0 <= resid < 60.0, (rank, info, bad, resid)
         assert err < 1e-11, (rank, err)
         assert info_bad == res[0][6] and info_bad > 0     # MAX-reduced, identical on every rank
+
+
+@pytest.mark.parametrize("P,Q", [(1, 2), (2, 1), (2, 2), (2, 4)])
+@pytest.mark.parametrize("cplx", [False, True])
+def test_potrf_grid_upper_matches_oracle(P, Q, cplx):
+    """dplasmaUpper (what testing_zpotrf.c:21 runs by default) on a grid: each rank transposes its own tiles and the
+    lower schedule runs on the Q x P grid with swapped coordinates; real and complex, ragged last tile"""
+    res = run_grid(P, Q, 1000, 128, True, cplx=cplx, uplo="U")
+    for rank, info, bad, resid, err, t, info_bad in res:
+        assert info == 0 and bad == 0 and 0.0 <= resid < 60.0, (rank, info, bad, resid)
+        assert err < 1e-11, (rank, err)
+        assert info_bad == res[0][6] and info_bad > 0
 
 
 @pytest.mark.parametrize("P,Q,N,nb", [(1, 2, 32768, 1024), (2, 2, 49152, 1024), (2, 4, 65536, 1024), (2, 4, 131072, 1024)])
