@@ -265,10 +265,10 @@ def run_reference(args):
 
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel from the committed
 # `ncu --set full` capture (16384 x 16384 x 512 NT update = one bulk launch of C2 at k ~ 32); see profiles/
-GEMM_TRAFFIC = {"bytes": 7.30e9,
-                "note": "profiles/ncu_gemm_r02_summary.md: dram read 5.15 GB + write 2.15 GB for a launch whose "
-                        "algorithmic bytes are 4.43 GB (C read + write, both operand panels once) -> 1.65 x, "
-                        "14 % of the HBM roof"}
+GEMM_TRAFFIC = {"bytes": 5.39e9,
+                "note": "profiles/ncu_gemm_order_r02_grouped.csv: dram read 3.29 GB + write 2.10 GB for a launch whose "
+                        "algorithmic bytes are 4.43 GB (C read + write, both operand panels once) -> 1.22 x, "
+                        "10 % of the HBM roof (was 7.30 GB with the strip-by-strip work order and plain C accesses)"}
 
 
 def flops_zpotrf(n):

@@ -1,4 +1,6 @@
 // Host launchers for the DMMA GEMM engine (see gemm_dmma.cuh).
+#include <algorithm>
+#include <cstdlib>
 #include "gemm_dmma.cuh"
 #include <cstdio>
 #include <cstdlib>
@@ -102,6 +104,17 @@ int gemm_launch(const GemmDesc& din, int nItems, int cfg, cudaStream_t stream) {
     if (nItems <= 0) return 0;
     GemmDesc d = din;
     if (d.fast && !(d.a_kmajor && d.b_kmajor) && !prepare_tensor_maps(d)) d.fast = 0;
+    // work order (decode_work): DPB_GEMM_ORDER=0 keeps the strip-by-strip order of round 1 (A/B measurements)
+    static const int order = [] { const char* e = getenv("DPB_GEMM_ORDER"); return e ? atoi(e) : -1; }();
+    d.colGroup = d.blkGroup = 0;
+    if (d.mode == GEMM_SINGLE) {
+        d.blkGroup = order >= 0 ? order : 16;
+    } else {
+        int g = order >= 0 ? order : std::max(1, std::min(8, 4096 / std::max(d.nb, 1)));
+        for (int c = 1; c < d.ncols && g > 0; c++)
+            if (d.rowFirst[c] < d.rowFirst[c - 1]) g = 0;  // not a trapezoid: the level walk of decode_work does not apply
+        d.colGroup = std::min(g, 8);
+    }
     if (d.a_kmajor && d.b_kmajor)
         gemm_dmma_kernel<CfgSmall, true, true><<<nItems, CfgSmall::THREADS, CfgSmall::smem(true, true), stream>>>(d);
     else if (d.a_kmajor)

@@ -79,6 +79,9 @@ struct GemmDesc {
     int rowEnd;               // local tile rows end (exclusive)
     int full;                 // 1: general product, diagonal tiles are updated in full (no SYRK mask)
     int itemStart[kMaxCols + 1];  // prefix sum of work items (CTA tiles) per column
+    // ---- work order (both modes): which CTA tiles are resident together decides what the L2 has to hold ----
+    int colGroup;  // TRAILING: tile columns walked together, tile row by tile row (0: one 64-wide strip at a time)
+    int blkGroup;  // SINGLE: CTA block columns walked together, block row by block row (0: one block column at a time)
     // ---- tensor maps of the M-major operands (fast mode): 4-D views {rows, k, tile | batch, k-tile}
     alignas(64) CUtensorMap tmA;
     alignas(64) CUtensorMap tmB;
@@ -209,7 +212,7 @@ struct BlockWork {
 };
 
 template <class Cfg>
-__device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
+__host__ __device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
     BlockWork w;
     w.valid = true;
     if (d.mode == GEMM_SINGLE) {
@@ -217,6 +220,15 @@ __device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
         const int per = d.gridM * d.gridN;
         const int bt = bid / per, r = bid - bt * per;
         int bj = r / d.gridM, bi = r - bj * d.gridM;
+        if (d.blkGroup > 0) {
+            // groups of blkGroup block columns, block row by block row inside a group: the CTAs resident together
+            // (3 x 148) cover a ~28 x 16 patch of C and share 28 + 16 operand blocks instead of 444 + 2
+            const int per_g = d.gridM * d.blkGroup;
+            const int cg = r / per_g, rem = r - cg * per_g;
+            const int gc = min(d.blkGroup, d.gridN - cg * d.blkGroup);
+            bi = rem / gc;
+            bj = cg * d.blkGroup + (rem - bi * gc);
+        }
         int i0 = bi * Cfg::BM, j0 = bj * Cfg::BN;
         const int Mtot = (bt == d.batch - 1) ? d.lastBatchM : d.M;
         w.M = min(Cfg::BM, Mtot - i0);
@@ -243,13 +255,43 @@ __device__ __forceinline__ BlockWork decode_work(const GemmDesc& d, int bid) {
         if (d.itemStart[mid] <= bid) lo = mid; else hi = mid;
     }
     int c = lo;
-    int r = bid - d.itemStart[c];
-    int j = d.colFirst + c;                 // local tile column
-    int rowsInCol = (d.rowEnd - d.rowFirst[c]) * d.bptM;   // CTA block-rows in this tile column
-    int bj = r / rowsInCol;                 // CTA block column inside the tile
-    int rr = r - bj * rowsInCol;
-    int i = d.rowFirst[c] + rr / d.bptM;    // local tile row
-    int bi = rr - (rr / d.bptM) * d.bptM;
+    int i, j, bi, bj;
+    if (d.colGroup > 0) {
+        // Tile columns in groups of colGroup; inside a group tile row by tile row, the tiles of a row one after the
+        // other, the CTA blocks of a tile together.  The CTAs resident at one time work on a few neighbouring tiles:
+        // a row-panel tile is fetched once per group (not once per 64-wide strip) and the group's column-panel tiles
+        // stay in the L2 while the rows stream by.  rowFirst is non-decreasing inside a group (the host checks):
+        // rows [rowFirst[c0+l], rowFirst[c0+l+1]) hold the l+1 columns c0 .. c0+l, the last level runs to rowEnd.
+        const int c0 = (c / d.colGroup) * d.colGroup, gc = min(d.colGroup, d.ncols - c0);
+        const int bpt = d.bptM * d.bptN;
+        const int r = bid - d.itemStart[c0];
+        int q = r / bpt;
+        const int e = r - q * bpt;
+        i = d.rowEnd; c = c0;
+        for (int lev = 0; lev < gc; lev++) {
+            const int r0 = d.rowFirst[c0 + lev];
+            const int r1 = (lev + 1 < gc) ? d.rowFirst[c0 + lev + 1] : d.rowEnd;
+            const int cnt = (r1 - r0) * (lev + 1);
+            if (q < cnt) {
+                const int ri = q / (lev + 1);
+                i = r0 + ri;
+                c = c0 + (q - ri * (lev + 1));
+                break;
+            }
+            q -= cnt;
+        }
+        j = d.colFirst + c;
+        bj = e / d.bptM;
+        bi = e - bj * d.bptM;
+    } else {
+        const int r = bid - d.itemStart[c];
+        j = d.colFirst + c;                 // local tile column
+        const int rowsInCol = (d.rowEnd - d.rowFirst[c]) * d.bptM;   // CTA block-rows in this tile column
+        bj = r / rowsInCol;                 // CTA block column inside the tile
+        const int rr = r - bj * rowsInCol;
+        i = d.rowFirst[c] + rr / d.bptM;    // local tile row
+        bi = rr - (rr / d.bptM) * d.bptM;
+    }
     int gm = i * d.P + d.prow, gn = j * d.Q + d.pcol;   // global tile coordinates
     int tm = (gm == d.mtGlobal - 1) ? d.lastM : d.nb;
     int tn = (gn == d.ntGlobal - 1) ? d.lastN : d.nb;
@@ -393,7 +435,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
                 const double* cp = w.C + (size_t)ccol(2 * t + h, j) * w.ldc + wm0;
 #pragma unroll
                 for (int i = 0; i < MF; i += 2) {
-                    const double2 x = *reinterpret_cast<const double2*>(cp + mrow(g, i));
+                    const double2 x = __ldcs(reinterpret_cast<const double2*>(cp + mrow(g, i)));  // C streams: evict first
                     acc[i][j][h] = cscale * x.x;
                     acc[i + 1][j][h] = cscale * x.y;
                 }
@@ -499,11 +541,11 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB) gemm_dmma_kernel(cons
                     x.x = alpha * acc[i][j][h];
                     x.y = alpha * acc[i + 1][j][h];
                     if (ebeta != 0.0) {
-                        const double2 c0 = *reinterpret_cast<const double2*>(cp + mrow(g, i));
+                        const double2 c0 = __ldcs(reinterpret_cast<const double2*>(cp + mrow(g, i)));
                         x.x += ebeta * c0.x;
                         x.y += ebeta * c0.y;
                     }
-                    *reinterpret_cast<double2*>(cp + mrow(g, i)) = x;
+                    __stcs(reinterpret_cast<double2*>(cp + mrow(g, i)), x);
                 }
             }
         return;
