@@ -98,6 +98,8 @@ struct parsec_context_s {
     double* wNorm = nullptr;    // row-sum scratch for norms
     double* wSolve = nullptr;   // solved RHS tile row of the grid solves
     size_t wSolveLen = 0;
+    double* wXpose = nullptr;   // send + receive staging of the distributed transposition (grown on demand)
+    size_t wXposeLen = 0;
     size_t wNormLen = 0;
     // multi-GPU panel workspaces: panelSets sets of panelSetElems doubles in one allocation (two alternate in
     // steady state; more are kept alive while a host matrix is still arriving, see potrf_dist.cu)

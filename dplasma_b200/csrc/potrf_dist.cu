@@ -466,42 +466,108 @@ void swap_grid_comms(parsec_context_s* ctx) {
     std::swap(ctx->gridIp, ctx->gridJq);
 }
 
+// Tt <- T^T on the same grid (the `uplo` triangle of T; tile (m, n) goes, transposed, to tile (n, m) on process
+// (n % P, m % Q)).  An all-to-all in rounds over blocks of tile columns: every rank transposes its outgoing tiles
+// straight into a send staging area, packed by destination, ONE send and ONE receive per peer move the round's tiles
+// (all pairs of the grid at the same time, large messages), and the received tiles are copied into place.  Both ends
+// of a pair walk the tiles in the same order (column n ascending, row m ascending).  The staging is context-owned.
 int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T, int uplo, const DevMatrix& Tt) {
     if (T.mb != T.nb || T.mt != T.nt) return -320;
+    if (T.esz != 1) return -2;  // real tiles only
     const size_t te = (size_t)T.tileElems;
-    const int me = T.prow * T.Q + T.pcol;
-    double* tmp = nullptr;
-    const int maxRecv = T.mt / std::min(T.P, T.Q) + 2;
-    DPB_CUDA(cudaMalloc(&tmp, (size_t)maxRecv * te * sizeof(double)));
-    std::vector<int> recvM;
-    int rc = 0;
-    for (int n = 0; n < T.nt && !rc; n++) {
-        const int m0 = (uplo == dplasmaLower) ? n : 0, m1 = (uplo == dplasmaLower) ? T.mt : n + 1;
-        recvM.clear();
-        bool grouped = false;
-        for (int m = m0; m < m1 && !rc; m++) {
-            const int src = (m % T.P) * T.Q + (n % T.Q), dst = (n % T.P) * T.Q + (m % T.Q);
-            if (src == me && dst == me) {
-                // both ends local: transpose straight into place (full nb x nb buffers, ragged edges included)
-                rc = launch_transpose(ctx, s, T.tile(m / T.P, n / T.Q), T.mb, Tt.tile(n / T.P, m / T.Q), T.mb, T.mb, T.nb);
-                continue;
-            }
-            if (src != me && dst != me) continue;
-            if (!grouped) { group_start(ctx); grouped = true; }
-            if (src == me) rc = p2p_send(ctx, T.tile(m / T.P, n / T.Q), te, world_rank_of(T, dst / T.Q, dst % T.Q), s);
-            else {
-                rc = p2p_recv(ctx, tmp + recvM.size() * te, te, world_rank_of(T, src / T.Q, src % T.Q), s);
-                recvM.push_back(m);
-            }
-        }
-        if (grouped && group_end(ctx)) rc = -321;
-        for (size_t i = 0; i < recvM.size() && !rc; i++) {
-            const int m = recvM[i];
-            rc = launch_transpose(ctx, s, tmp + i * te, T.mb, Tt.tile(n / T.P, m / T.Q), T.mb, T.mb, T.nb);
-        }
+    const int P = T.P, Q = T.Q, np = P * Q, me = T.prow * Q + T.pcol;
+    // per round: at most `cap` outgoing and `cap` incoming tiles (1 GB each way, at least one full tile column)
+    const size_t cap = std::max<size_t>((size_t)T.mt + 1, std::min<size_t>(((size_t)1 << 30) / (te * sizeof(double)),
+                                                                           (size_t)T.mt * (T.mt + 1) / 2));
+    if (ctx->wXposeLen < 2 * cap * te) {
+        if (ctx->wXpose) { cudaStreamSynchronize(s); cudaFree(ctx->wXpose); }
+        ctx->wXpose = nullptr;
+        ctx->wXposeLen = 0;
+        DPB_CUDA(cudaMalloc(&ctx->wXpose, 2 * cap * te * sizeof(double)));
+        ctx->wXposeLen = 2 * cap * te;
     }
-    cudaStreamSynchronize(s);
-    cudaFree(tmp);
+    double* sendBuf = ctx->wXpose;
+    double* recvBuf = ctx->wXpose + cap * te;
+    auto rows_of = [&](int n, int* m0, int* m1) {
+        *m0 = (uplo == dplasmaLower) ? n : 0;
+        *m1 = (uplo == dplasmaLower) ? T.mt : n + 1;
+    };
+    std::vector<size_t> sendCnt(np), recvCnt(np), sendOff(np), recvOff(np), sendIdx(np), recvIdx(np), outQ(Q), inP(P);
+    int rc = 0;
+    for (int nA = 0; nA < T.nt && !rc;) {
+        // ---- the columns of this round: the same on every rank (bounds on what any rank sends or receives:
+        //      column n is sent by grid column n % Q, at most ceil(len / P) tiles per rank, and received by grid row
+        //      n % P, at most ceil(len / Q) tiles per rank) ----
+        int nB = nA;
+        std::fill(outQ.begin(), outQ.end(), 0);
+        std::fill(inP.begin(), inP.end(), 0);
+        while (nB < T.nt) {
+            int m0, m1;
+            rows_of(nB, &m0, &m1);
+            const size_t o = (size_t)(m1 - m0 + P - 1) / P, i = (size_t)(m1 - m0 + Q - 1) / Q;
+            if (nB > nA && (outQ[nB % Q] + o > cap || inP[nB % P] + i > cap)) break;
+            outQ[nB % Q] += o; inP[nB % P] += i; nB++;
+        }
+        std::fill(sendCnt.begin(), sendCnt.end(), 0);
+        std::fill(recvCnt.begin(), recvCnt.end(), 0);
+        for (int n = nA; n < nB; n++) {
+            int m0, m1;
+            rows_of(n, &m0, &m1);
+            for (int m = m0; m < m1; m++) {
+                const int src = (m % P) * Q + (n % Q), dst = (n % P) * Q + (m % Q);
+                if (src == me && dst != me) sendCnt[dst]++;
+                if (dst == me && src != me) recvCnt[src]++;
+            }
+        }
+        size_t so = 0, ro = 0;
+        for (int r = 0; r < np; r++) {
+            sendOff[r] = so; so += sendCnt[r];
+            recvOff[r] = ro; ro += recvCnt[r];
+            sendIdx[r] = recvIdx[r] = 0;
+        }
+        // ---- pack: my tiles, transposed, by destination; tiles that stay go straight into place ----
+        for (int n = nA; n < nB && !rc; n++) {
+            if (n % Q != T.pcol) continue;
+            int m0, m1;
+            rows_of(n, &m0, &m1);
+            for (int m = m0; m < m1 && !rc; m++) {
+                if (m % P != T.prow) continue;
+                const int dst = (n % P) * Q + (m % Q);
+                double* to = (dst == me) ? Tt.tile(n / P, m / Q) : sendBuf + (sendOff[dst] + sendIdx[dst]++) * te;
+                rc = launch_transpose(ctx, s, T.tile(m / P, n / Q), T.mb, to, T.mb, T.mb, T.nb);
+            }
+        }
+        if (rc) break;
+        // ---- exchange: one message per peer and direction ----
+        bool any = false;
+        for (int r = 0; r < np; r++) any = any || sendCnt[r] || recvCnt[r];
+        if (any) {
+            group_start(ctx);
+            for (int r = 0; r < np && !rc; r++) {
+                if (r == me) continue;
+                const int peer = world_rank_of(T, r / Q, r % Q);
+                if (sendCnt[r]) rc = p2p_send(ctx, sendBuf + sendOff[r] * te, sendCnt[r] * te, peer, s);
+                if (!rc && recvCnt[r]) rc = p2p_recv(ctx, recvBuf + recvOff[r] * te, recvCnt[r] * te, peer, s);
+            }
+            if (group_end(ctx) && !rc) rc = -321;
+        }
+        // ---- unpack: received tiles into place, in the order their sender packed them ----
+        for (int n = nA; n < nB && !rc; n++) {
+            if (n % P != T.prow) continue;
+            int m0, m1;
+            rows_of(n, &m0, &m1);
+            for (int m = m0; m < m1 && !rc; m++) {
+                if (m % Q != T.pcol) continue;
+                const int src = (m % P) * Q + (n % Q);
+                if (src == me) continue;
+                if (cudaMemcpyAsync(Tt.tile(n / P, m / Q), recvBuf + (recvOff[src] + recvIdx[src]++) * te, te * sizeof(double),
+                                    cudaMemcpyDeviceToDevice, s) != cudaSuccess)
+                    rc = -322;
+            }
+        }
+        nA = nB;
+    }
+    cudaStreamSynchronize(s);  // the staging area may be reused by a later call on another stream
     return rc;
 }
 
@@ -516,6 +582,10 @@ int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T
 // The tile columns of Tm are final data: their broadcast along the grid rows for step k+1 is posted on the
 // communication stream while step k computes (two panel sets alternate); the solved RHS row travels down the grid
 // columns on the compute stream, where the next update needs it.
+// Look-ahead: the chain of a step -- solve tile row k, send it down the columns, update the ONE tile row the next
+// step solves -- stays on the compute stream; the update of all the other remaining rows goes to the update stream
+// and runs underneath the chain of the next step (ztrsm_LLN.jdf gets the same overlap from its dataflow: the GEMM
+// tasks of step k and the TRSM task of step k+1 are independent once row k+1 has its update).
 static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower, int diag, double alpha,
                               const DevMatrix& Tm, const DevMatrix& B) {
     int rc = ensure_grid_comms(ctx, Tm.P, Tm.Q, Tm.ip, Tm.jq);
@@ -527,21 +597,25 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
     const int rowEnd = std::min(Tm.firstLocalRowGE(Tm.mt), Tm.lmt);
     const int colEndB = std::min(B.firstLocalColGE(B.nt), B.lnt);
     // solved tile row k of the RHS, one tile per local RHS tile column (context-owned, grown on demand)
-    const size_t xNeed = (size_t)std::max(colEndB, 1) * teB;
-    if (ctx->wSolveLen < xNeed) {
+    const size_t xSet = (size_t)std::max(colEndB, 1) * teB, xNeed = 2 * xSet;  // two sets: the bulk update of step k
+    if (ctx->wSolveLen < xNeed) {                                               // reads its row while step k+1 receives
         if (ctx->wSolve) { cudaStreamSynchronize(s); cudaFree(ctx->wSolve); }
         ctx->wSolve = nullptr;
         DPB_CUDA(cudaMalloc(&ctx->wSolve, xNeed * sizeof(double)));
         ctx->wSolveLen = xNeed;
     }
-    double* xrow = ctx->wSolve;
     cudaStream_t sc = ctx->sComm;
+    cudaStream_t su = (ctx->sUpdate != s) ? ctx->sUpdate : ctx->sPanel;  // bulk updates
     const size_t evBase = 900;  // events of this routine (a factorization's own count up from 0)
     cudaEvent_t evRecv[2] = {dist_event(ctx, evBase), dist_event(ctx, evBase + 1)};
     cudaEvent_t evFree[2] = {dist_event(ctx, evBase + 2), dist_event(ctx, evBase + 3)};
     cudaEvent_t evStart = dist_event(ctx, evBase + 4);
+    cudaEvent_t evBulk[2] = {dist_event(ctx, evBase + 6), dist_event(ctx, evBase + 7)};   // bulk update of step kk done
+    cudaEvent_t evX[2] = {dist_event(ctx, evBase + 8), dist_event(ctx, evBase + 9)};      // solved row kk is in place
+    cudaEvent_t evStep[2] = {dist_event(ctx, evBase + 10), dist_event(ctx, evBase + 11)};  // chain of step kk done
     DPB_CUDA(cudaEventRecord(evStart, s));
     DPB_CUDA(cudaStreamWaitEvent(sc, evStart, 0));  // Tm may have been produced on s just before
+    DPB_CUDA(cudaStreamWaitEvent(su, evStart, 0));
     auto rows_of = [&](int k, int* ilA, int* cnt) {
         // local tile rows that take part in step k: the diagonal tile's row and the rows still to update
         const int a = lower ? std::min(Tm.firstLocalRowGE(k), rowEnd) : 0;
@@ -590,29 +664,59 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
                                          B.colsOfTile(jl * B.Q + B.pcol), lalpha, Tkk, Tm.mb, winv, B.tile(ilk, jl), B.mb);
             if (rc) break;
         }
-        // (c) solved tile row k down the grid columns
+        // (c) solved tile row k down the grid columns.  The receive buffer of this parity was last read by the bulk
+        //     update of step kk-2.
+        double* xrow = ctx->wSolve + (size_t)set * xSet;
         const double* xPtr = xrow;
         long long xStride = (long long)teB;
         if (Tm.P == 1) { xPtr = B.tile(ilk, 0); xStride = (long long)B.lmt * teB; }
         else if (colEndB > 0) {
+            if (kk >= 2) DPB_CUDA(cudaStreamWaitEvent(s, evBulk[set], 0));
             group_start(ctx);
             for (int jl = 0; jl < colEndB && !rc; jl++)
                 rc = bcast(ctx, ctx->commCol, B.tile(std::min(ilk, std::max(B.lmt - 1, 0)), jl), xrow + (size_t)jl * teB, teB, kp, s);
             if (group_end(ctx)) rc = -313;
             if (rc) break;
         }
-        // (d) update my remaining RHS tile rows
+        DPB_CUDA(cudaEventRecord(evX[set], s));
+        // (d) update my remaining RHS tile rows [u0, u1): the row the next step solves here on the chain, the others
+        //     on the update stream
         const int u0 = lower ? std::min(Tm.firstLocalRowGE(k + 1), rowEnd) : 0;
         const int u1 = lower ? rowEnd : std::min(Tm.firstLocalRowGE(k), rowEnd);
-        if (u1 > u0) {
-            const int lastGm = (u1 - 1) * Tm.P + Tm.prow;
-            for (int jl = 0; jl < colEndB && !rc; jl++)
-                rc = gemm_single(ctx, s, B.mb, B.colsOfTile(jl * B.Q + B.pcol), tk, -1.0, rowPtr + (size_t)u0 * te, Tm.mb,
-                                 false, xPtr + (size_t)jl * xStride, B.mb, true, lalpha, B.tile(u0, jl), B.mb, 0, u1 - u0,
-                                 (long long)te, 0, (long long)teB, B.rowsOfTile(lastGm));
+        const int kn = lower ? k + 1 : k - 1;  // global tile row of the next step
+        const bool nextHere = kk + 1 < mt && kn % Tm.P == Tm.prow && u1 > u0;
+        int la0 = u0, la1 = u0, b0 = u0, b1 = u1;  // look-ahead rows [la0, la1), bulk rows [b0, b1)
+        if (nextHere) {
+            if (lower) { la0 = u0; la1 = u0 + 1; b0 = u0 + 1; }
+            else { la0 = u1 - 1; la1 = u1; b1 = u1 - 1; }
         }
-        DPB_CUDA(cudaEventRecord(evFree[set], s));
+        auto update_rows = [&](cudaStream_t st, int a, int b) -> int {
+            if (b <= a) return 0;
+            const int lastGm = (b - 1) * Tm.P + Tm.prow;
+            int r = 0;
+            for (int jl = 0; jl < colEndB && !r; jl++)
+                r = gemm_single(ctx, st, B.mb, B.colsOfTile(jl * B.Q + B.pcol), tk, -1.0, rowPtr + (size_t)a * te, Tm.mb,
+                                false, xPtr + (size_t)jl * xStride, B.mb, true, lalpha, B.tile(a, jl), B.mb, 0, b - a,
+                                (long long)te, 0, (long long)teB, B.rowsOfTile(lastGm));
+            return r;
+        };
+        if (la1 > la0) {
+            // the bulk update of the previous step also writes this row: it has to be through first
+            if (kk >= 1) DPB_CUDA(cudaStreamWaitEvent(s, evBulk[set ^ 1], 0));
+            rc = update_rows(s, la0, la1);
+            if (rc) break;
+        }
+        DPB_CUDA(cudaEventRecord(evStep[set], s));
+        DPB_CUDA(cudaStreamWaitEvent(su, evX[set], 0));
+        rc = update_rows(su, b0, b1);
+        if (rc) break;
+        DPB_CUDA(cudaEventRecord(evBulk[set], su));
+        // panel set `set` is free again when both the chain and the bulk update of this step have read it
+        DPB_CUDA(cudaStreamWaitEvent(su, evStep[set], 0));
+        DPB_CUDA(cudaEventRecord(evFree[set], su));
     }
+    // everything back on the caller's stream
+    for (int e = 0; e < 2; e++) DPB_CUDA(cudaStreamWaitEvent(s, evBulk[e], 0));
     // the communication stream must be idle before the caller reuses or frees the operands
     cudaEvent_t evDone = dist_event(ctx, evBase + 5);
     DPB_CUDA(cudaEventRecord(evDone, sc));
