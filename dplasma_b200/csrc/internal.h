@@ -98,6 +98,9 @@ struct parsec_context_s {
     double* wNorm = nullptr;    // row-sum scratch for norms
     double* wSolve = nullptr;   // solved RHS tile row of the grid solves
     size_t wSolveLen = 0;
+    double* wSolveInv = nullptr;  // large inverse blocks of the tile solves: 2 x [n x n | scratch] + solved-tile buffer
+    size_t wSolveInvLen = 0;
+    int wSolveInvNb = 0;
     double* wXpose = nullptr;   // send + receive staging of the distributed transposition (grown on demand)
     size_t wXposeLen = 0;
     size_t wNormLen = 0;
@@ -253,6 +256,14 @@ int trsm_panel_lower(parsec_context_s* ctx, cudaStream_t s, const double* L, int
 int trsm_left(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, int diag, int m, int n, double alpha,
               const double* T, int ldt, double* B, int ldb, double* winv);
 int ensure_winv(parsec_context_s* ctx, int nb);
+int solve_ibs_for(int n);
+int ensure_solve_ws(parsec_context_s* ctx, int nb, int ncols);
+double* solve_ws_big(parsec_context_s* ctx, int set);
+double* solve_ws_xt(parsec_context_s* ctx);
+int build_inverse_blocks(parsec_context_s* ctx, cudaStream_t s, int uplo, int diag, int n, const double* T, int ldt,
+                         double* winv64, double* wbig, int ldw, double* y, int ibs);
+int trsm_left_big_entry(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int n, int ncols, double alpha,
+                        const double* T, int ldt, const double* wbig, int ldw, int ibs, double* xt, double* B, int ldb);
 int ensure_wnorm(parsec_context_s* ctx, size_t n);
 // staging.cu
 int stage_in(parsec_context_s* ctx, const parsec_tiled_matrix_t* A, DevMatrix* out, bool copyData, int uploOnly);

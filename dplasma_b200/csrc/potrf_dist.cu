@@ -9,6 +9,7 @@
 // solve, broadcasts) runs on the high-priority panel stream underneath the bulk update of
 // step k; panel buffers are double-buffered.
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <vector>
 #include "internal.h"
@@ -591,6 +592,7 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
     int rc = ensure_grid_comms(ctx, Tm.P, Tm.Q, Tm.ip, Tm.jq);
     if (!rc) rc = ensure_winv(ctx, Tm.nb);
     if (!rc) rc = ensure_panel_bufs(ctx, Tm);
+    if (!rc) rc = ensure_solve_ws(ctx, Tm.mb, B.nb);
     if (rc) return rc;
     const size_t te = (size_t)Tm.tileElems, teB = (size_t)B.tileElems;
     const int mt = Tm.mt;
@@ -637,8 +639,31 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
             int r = bcast(ctx, ctx->commRow, buf, buf, (size_t)cnt * te, kq, sc);
             if (r) return r;
         }
+        // the inverse blocks of the diagonal tile do not depend on the right-hand side: built here, one step ahead of
+        // the chain that uses them (solve.cu, build_inverse_blocks)
+        if (Tm.prow == k % Tm.P) {
+            const int tk = Tm.rowsOfTile(k), ibs = solve_ibs_for(tk);
+            const double* rowPtr = (Tm.Q == 1 || Tm.pcol == kq) ? Tm.tile(0, jlk) : panel_bufs(ctx, Tm, set).row;
+            const double* Tkk = rowPtr + (size_t)(k / Tm.P) * te;
+            double* winv64 = ctx->wInv + (size_t)set * ctx->wInvSlot;
+            double* wbig = solve_ws_big(ctx, set);
+            int r = build_inverse_blocks(ctx, sc, lower ? dplasmaLower : dplasmaUpper, diag, tk, Tkk, Tm.mb, winv64, wbig, Tm.mb,
+                                         wbig + (size_t)Tm.mb * Tm.mb, ibs);
+            if (r) return r;
+        }
         DPB_CUDA(cudaEventRecord(evRecv[set], sc));
         return 0;
+    };
+    // DPB_TRACE_SOLVE: timing events per step -- chain: [0] start (panel there), [1] row solved, [2] row sent,
+    // [3] look-ahead update done; bulk: [4], [5] around the bulk update on the update stream
+    static const bool traceSolve = getenv("DPB_TRACE_SOLVE") != nullptr;
+    std::vector<cudaEvent_t> tev;
+    auto tmark = [&](cudaStream_t st) {
+        if (!traceSolve) return;
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, st);
+        tev.push_back(e);
     };
     rc = post_panel(0);
     for (int kk = 0; kk < mt && !rc; kk++) {
@@ -651,19 +676,27 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
             if (rc) break;
         }
         DPB_CUDA(cudaStreamWaitEvent(s, evRecv[set], 0));
+        tmark(s);
         const double* rowPtr = panel_bufs(ctx, Tm, set).row;
         if (Tm.Q == 1 || Tm.pcol == kq) rowPtr = Tm.tile(0, jlk);
         // (b) solve the RHS tiles of tile row k (ranks of grid row kp, each for its own RHS columns)
         const int ilk = k / Tm.P;
         if (Tm.prow == kp) {
             const double* Tkk = rowPtr + (size_t)ilk * te;
-            double* winv = ctx->wInv;
-            rc = launch_trtri_blocks(ctx, s, Tkk, Tm.mb, tk, lower ? dplasmaLower : dplasmaUpper, diag == dplasmaUnit, winv);
-            for (int jl = 0; jl < colEndB && !rc; jl++)
-                rc = trsm_left_rec_entry(ctx, s, lower ? dplasmaLower : dplasmaUpper, false, tk,
-                                         B.colsOfTile(jl * B.Q + B.pcol), lalpha, Tkk, Tm.mb, winv, B.tile(ilk, jl), B.mb);
+            const int ibs = solve_ibs_for(tk);
+            const int ul = lower ? dplasmaLower : dplasmaUpper;
+            for (int jl = 0; jl < colEndB && !rc; jl++) {
+                const int nc = B.colsOfTile(jl * B.Q + B.pcol);
+                if (ibs > IB)
+                    rc = trsm_left_big_entry(ctx, s, ul, false, tk, nc, lalpha, Tkk, Tm.mb, solve_ws_big(ctx, set), Tm.mb, ibs,
+                                             solve_ws_xt(ctx), B.tile(ilk, jl), B.mb);
+                else
+                    rc = trsm_left_rec_entry(ctx, s, ul, false, tk, nc, lalpha, Tkk, Tm.mb, ctx->wInv + (size_t)set * ctx->wInvSlot,
+                                             B.tile(ilk, jl), B.mb);
+            }
             if (rc) break;
         }
+        tmark(s);
         // (c) solved tile row k down the grid columns.  The receive buffer of this parity was last read by the bulk
         //     update of step kk-2.
         double* xrow = ctx->wSolve + (size_t)set * xSet;
@@ -679,6 +712,7 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
             if (rc) break;
         }
         DPB_CUDA(cudaEventRecord(evX[set], s));
+        tmark(s);
         // (d) update my remaining RHS tile rows [u0, u1): the row the next step solves here on the chain, the others
         //     on the update stream
         const int u0 = lower ? std::min(Tm.firstLocalRowGE(k + 1), rowEnd) : 0;
@@ -707,9 +741,12 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
             if (rc) break;
         }
         DPB_CUDA(cudaEventRecord(evStep[set], s));
+        tmark(s);
         DPB_CUDA(cudaStreamWaitEvent(su, evX[set], 0));
+        tmark(su);
         rc = update_rows(su, b0, b1);
         if (rc) break;
+        tmark(su);
         DPB_CUDA(cudaEventRecord(evBulk[set], su));
         // panel set `set` is free again when both the chain and the bulk update of this step have read it
         DPB_CUDA(cudaStreamWaitEvent(su, evStep[set], 0));
@@ -717,6 +754,25 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
     }
     // everything back on the caller's stream
     for (int e = 0; e < 2; e++) DPB_CUDA(cudaStreamWaitEvent(s, evBulk[e], 0));
+    if (traceSolve && !tev.empty()) {
+        cudaStreamSynchronize(s);
+        cudaStreamSynchronize(su);
+        double sum[5] = {0, 0, 0, 0, 0};  // solve, send, look-ahead, bulk, start-to-start
+        const size_t steps = tev.size() / 6;
+        for (size_t q = 0; q < steps; q++) {
+            float ms;
+            cudaEventElapsedTime(&ms, tev[6 * q], tev[6 * q + 1]); sum[0] += ms;
+            cudaEventElapsedTime(&ms, tev[6 * q + 1], tev[6 * q + 2]); sum[1] += ms;
+            cudaEventElapsedTime(&ms, tev[6 * q + 2], tev[6 * q + 3]); sum[2] += ms;
+            cudaEventElapsedTime(&ms, tev[6 * q + 4], tev[6 * q + 5]); sum[3] += ms;
+            if (q + 1 < steps) { cudaEventElapsedTime(&ms, tev[6 * q], tev[6 * q + 6]); sum[4] += ms; }
+        }
+        if (ctx->rank == 0)
+            fprintf(stderr, "[solve]   %zu steps (%s): row solve %.2f ms, row send %.2f ms, look-ahead update (incl. wait for the "
+                            "previous bulk) %.2f ms, bulk updates %.2f ms, step starts span %.2f ms\n",
+                    steps, lower ? "forward" : "backward", sum[0], sum[1], sum[2], sum[3], sum[4]);
+        for (cudaEvent_t e : tev) cudaEventDestroy(e);
+    }
     // the communication stream must be idle before the caller reuses or frees the operands
     cudaEvent_t evDone = dist_event(ctx, evBase + 5);
     DPB_CUDA(cudaEventRecord(evDone, sc));
@@ -733,14 +789,32 @@ int trsm_left_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, 
     if (A.P * A.Q != ctx->nranks) return -303;
     int rc = ensure_grid_comms(ctx, A.P, A.Q, A.ip, A.jq);
     if (rc) return rc;
-    if (trans == dplasmaNoTrans) return solve_panels_multi(ctx, s, uplo == dplasmaLower, diag, alpha, A, B);
+    // DPB_TRACE_SOLVE=1: wall-clock phases of the call on stderr (synchronises the stream: measurement runs only)
+    static const bool traceSolve = getenv("DPB_TRACE_SOLVE") != nullptr;
+    auto now = [&]() {
+        cudaStreamSynchronize(s);
+        return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+    };
+    double t0 = traceSolve ? now() : 0.0;
+    if (trans == dplasmaNoTrans) {
+        rc = solve_panels_multi(ctx, s, uplo == dplasmaLower, diag, alpha, A, B);
+        if (traceSolve && ctx->rank == 0)
+            fprintf(stderr, "[solve] N=%d nrhs=%d %dx%d NoTrans: panels %.2f ms\n", A.M, B.N, A.P, A.Q, (now() - t0) * 1e3);
+        return rc;
+    }
     // op(A) = A^T: solve with the transposed factor, which is triangular the other way round
     DevMatrix At;
     rc = alloc_like(A, &At);
+    double t1 = traceSolve ? now() : 0.0;
     if (!rc) rc = dist_transpose_tri(ctx, s, A, uplo, At);
+    double t2 = traceSolve ? now() : 0.0;
     if (!rc) rc = solve_panels_multi(ctx, s, uplo != dplasmaLower, diag, alpha, At, B);
     cudaStreamSynchronize(s);
+    double t3 = traceSolve ? now() : 0.0;
     stage_free(&At);
+    if (traceSolve && ctx->rank == 0)
+        fprintf(stderr, "[solve] N=%d nrhs=%d %dx%d Trans: alloc %.2f ms, transposition %.2f ms, panels %.2f ms, free %.2f ms\n", A.M,
+                B.N, A.P, A.Q, (t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3, (now() - t3) * 1e3);
     return rc;
 }
 

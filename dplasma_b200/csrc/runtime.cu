@@ -54,6 +54,7 @@ int parsec_fini(parsec_context_t** pctx) {
     if (ctx->wNorm) cudaFree(ctx->wNorm);
     if (ctx->wSolve) cudaFree(ctx->wSolve);
     if (ctx->wXpose) cudaFree(ctx->wXpose);
+    if (ctx->wSolveInv) cudaFree(ctx->wSolveInv);
     if (ctx->panelBase) cudaFree(ctx->panelBase);
     if (ctx->tileSync) cudaFree(ctx->tileSync);
     for (int i = 0; i < 2; i++)

@@ -7,6 +7,7 @@
 // engine: the diagonal tile's IB x IB diagonal blocks are inverted once (trtri leaf) and the
 // tile solve becomes a recursion of products.
 #include <cstdio>
+#include <cstdlib>
 #include <algorithm>
 #include "internal.h"
 
@@ -24,59 +25,176 @@ static int invert_diag_blocks(parsec_context_s* ctx, cudaStream_t s, int uplo, i
     return launch_trtri_blocks(ctx, s, T, ldt, n, uplo, diag == dplasmaUnit, winv);
 }
 
-int trsm_left_rec_entry(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int n, int ncols, double alpha,
-                        const double* T, int ldt, const double* winv, double* B, int ldb);
+// ---------------------------------------------------------------------------------------
+// Left-side tile solve with LARGE inverted diagonal blocks.
+//
+// The recursion over 64-blocks costs 2 n/64 - 1 dependent launches per RHS tile (31 at n = 1024), each with a handful of
+// CTAs: measured 0.76 ms for a 1024 x 256 RHS tile, the whole critical path of a step of the grid solves
+// (profiles/solve_trace_r02.md).  Here the diagonal blocks of size `ibs` (256 by default, DPB_SOLVE_IBS) of the lower
+// form of T are inverted explicitly -- built bottom-up from the 64 x 64 inverses,
+//     inv [T11 0; T21 T22] = [W1 0; -W2 T21 W1, W2],
+// two batched products per level, none of which depends on the right-hand side (the grid solve does them one step
+// ahead on the communication stream) -- and the solve recurses only down to ibs: 2 n/ibs - 1 launches plus one copy.
+// cuBLAS / MAGMA dtrsm invert diagonal blocks the same way; the error constant involves the conditioning of the
+// ibs x ibs diagonal blocks of the factor instead of the 64 x 64 ones.
+// Storage: wbig is an n x n array (ld = ldw >= n) that holds the inverse blocks on its block diagonal.
+// ---------------------------------------------------------------------------------------
+__global__ void place_inverse_blocks_kernel(const double* __restrict__ winv64, double* __restrict__ wbig, int ldw, int n,
+                                            int ibs) {
+    // element (i, j) of big block b: the 64 x 64 inverse when i and j fall into the same 64-block, else zero
+    const long long total = (long long)((n + ibs - 1) / ibs) * ibs * ibs;
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+        const int b = (int)(e / ((long long)ibs * ibs)), r = (int)(e % ((long long)ibs * ibs));
+        const int i = b * ibs + r % ibs, j = b * ibs + r / ibs;
+        if (i >= n || j >= n) continue;
+        double v = 0.0;
+        if (i / IB == j / IB) v = winv64[(size_t)(i / IB) * IB * IB + (i % IB) + (size_t)(j % IB) * IB];
+        wbig[i + (size_t)j * ldw] = v;
+    }
+}
+
+int solve_ibs_for(int n) {
+    static const int want = [] {
+        const char* e = getenv("DPB_SOLVE_IBS");
+        int v = e ? atoi(e) : 256;
+        int p = IB;
+        while (p * 2 <= v && p < 1024) p *= 2;
+        return p;
+    }();
+    int ibs = want;
+    while (ibs > IB && (n % ibs) != 0) ibs /= 2;  // ragged tiles fall back to the block size that divides them
+    if (n % IB != 0) ibs = IB;
+    return ibs;
+}
+
+int ensure_solve_ws(parsec_context_s* ctx, int nb, int ncols) {
+    // two sets of [wbig (nb x nb) | y (nb x nb / 2)] and one solved-tile buffer (nb x ncols)
+    const size_t set = (size_t)nb * nb + (size_t)nb * nb / 2, need = 2 * set + (size_t)nb * std::max(ncols, 1);
+    if (ctx->wSolveInv && ctx->wSolveInvLen >= need && ctx->wSolveInvNb == nb) return 0;
+    if (ctx->wSolveInv) { cudaDeviceSynchronize(); cudaFree(ctx->wSolveInv); }
+    ctx->wSolveInv = nullptr;
+    ctx->wSolveInvLen = 0;
+    DPB_CUDA(cudaMalloc(&ctx->wSolveInv, need * sizeof(double)));
+    ctx->wSolveInvLen = need;
+    ctx->wSolveInvNb = nb;
+    return 0;
+}
+double* solve_ws_big(parsec_context_s* ctx, int set) {
+    const size_t nb = (size_t)ctx->wSolveInvNb;
+    return ctx->wSolveInv + (size_t)set * (nb * nb + nb * nb / 2);
+}
+double* solve_ws_xt(parsec_context_s* ctx) {
+    const size_t nb = (size_t)ctx->wSolveInvNb;
+    return ctx->wSolveInv + 2 * (nb * nb + nb * nb / 2);
+}
+
+// inverse blocks of size ibs of the lower form of T (n x n, n % ibs == 0) into wbig (ld ldw); winv64 and y are scratch
+int build_inverse_blocks(parsec_context_s* ctx, cudaStream_t s, int uplo, int diag, int n, const double* T, int ldt,
+                         double* winv64, double* wbig, int ldw, double* y, int ibs) {
+    int rc = launch_trtri_blocks(ctx, s, T, ldt, n, uplo, diag == dplasmaUnit, winv64);
+    if (rc || ibs <= IB) return rc;
+    const long long total = (long long)(n / ibs) * ibs * ibs;
+    place_inverse_blocks_kernel<<<(int)std::min<long long>((total + 255) / 256, 1184), 256, 0, s>>>(winv64, wbig, ldw, n, ibs);
+    ctx->launches++;
+    if (cudaGetLastError() != cudaSuccess) return -9;
+    const bool upper = (uplo != dplasmaLower);
+    for (int m = IB; m < ibs && !rc; m *= 2) {
+        const int pairs = n / (2 * m);
+        // lower-form block (rows of the second block, columns of the first): T(o1.., o0..) or T(o0.., o1..)^T
+        const double* L21 = upper ? T + (size_t)m * ldt : T + m;
+        // Y = L21 W1
+        rc = gemm_single(ctx, s, m, m, m, 1.0, L21, ldt, upper, wbig, ldw, true, 0.0, y, m, 0, pairs,
+                         2LL * m * (ldt + 1), 2LL * m * (ldw + 1), (long long)m * m, -1);
+        // Z = -W2 Y, into the lower-left quarter of the merged block
+        if (!rc)
+            rc = gemm_single(ctx, s, m, m, m, -1.0, wbig + (size_t)m * (ldw + 1), ldw, false, y, m, true, 0.0, wbig + m, ldw, 0,
+                             pairs, 2LL * m * (ldw + 1), (long long)m * m, 2LL * m * (ldw + 1), -1);
+    }
+    return rc;
+}
+
+struct LeftWs {
+    const double* winv;  // ibs == IB: 64 x 64 inverse blocks (block b at winv + b IB IB, ld IB); else wbig
+    int ldw, ibs;
+    double* xt;          // ibs > IB: solved rows are written here (ld ldx), B keeps the updated right-hand side
+    int ldx;
+};
 
 // B(r0:r0+n, :) <- alpha * op(T(r0:r0+n, r0:r0+n))^-1 * B(r0:r0+n, :)      (B is m x ncols, Left side)
 // lowerEff: op(T) is lower triangular  (Lower/NoTrans or Upper/Trans)
 static int trsm_left_rec(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int r0, int n, int ncols,
-                         double alpha, const double* T, int ldt, const double* winv, double* B, int ldb) {
+                         double alpha, const double* T, int ldt, const LeftWs& w, double* B, int ldb) {
     const bool lowerEff = (uplo == dplasmaLower) != trans;
-    if (n <= IB) {
-        // X = alpha * inv(op(Tjj)) * B.  winv holds W = inv(lower form of the block):
+    const bool big = w.ibs > IB;
+    if (n <= w.ibs) {
+        // X = alpha * inv(op(Tjj)) * B.  W = inv(lower form of the block):
         //   Lower/NoTrans: inv = W     Lower/Trans: inv = W^T
         //   Upper/NoTrans: inv = W^T   Upper/Trans: inv = W      (W = inv(U^T))
         const bool useWT = (uplo == dplasmaLower) == trans;
-        const double* W = winv + (size_t)(r0 / IB) * IB * IB;
         double* Br = B + r0;
+        if (big)  // out of place: several CTA row blocks read all of B(r0:r0+n, cols)
+            return gemm_single(ctx, s, n, ncols, n, alpha, w.winv + (size_t)r0 * (w.ldw + 1), w.ldw, useWT, Br, ldb, true, 0.0,
+                               w.xt + r0, w.ldx, 0);
         // in place: M = n <= 64 rows -> a single CTA row block per column block, which loads all
         // of B(:, cols) before it writes
-        return gemm_single(ctx, s, n, ncols, n, alpha, W, IB, useWT, Br, ldb, true, 0.0, Br, ldb, 0);
+        return gemm_single(ctx, s, n, ncols, n, alpha, w.winv + (size_t)(r0 / IB) * IB * IB, IB, useWT, Br, ldb, true, 0.0, Br, ldb, 0);
     }
-    const int n1 = split_of(n), n2 = n - n1;
+    const int n1 = big ? (n / w.ibs / 2) * w.ibs : split_of(n), n2 = n - n1;
+    const double* X = big ? w.xt : B;  // where solved rows are read from
+    const int ldx = big ? w.ldx : ldb;
     int rc;
     if (lowerEff) {
         // forward: X1 = inv(T11) B1 ; B2 = alpha B2 - opT21 X1 ; X2 = inv(T22) B2
-        rc = trsm_left_rec(ctx, s, uplo, trans, r0, n1, ncols, alpha, T, ldt, winv, B, ldb);
+        rc = trsm_left_rec(ctx, s, uplo, trans, r0, n1, ncols, alpha, T, ldt, w, B, ldb);
         if (rc) return rc;
         // op(T)21 (n2 x n1): Lower/NoTrans -> T(r0+n1.., r0..) M-major ; Upper/Trans -> T(r0.., r0+n1..)^T K-major
         const double* T21 = trans ? T + r0 + (size_t)(r0 + n1) * ldt : T + (r0 + n1) + (size_t)r0 * ldt;
-        rc = gemm_single(ctx, s, n2, ncols, n1, -1.0, T21, ldt, trans, B + r0, ldb, true, alpha, B + r0 + n1, ldb, 0);
+        rc = gemm_single(ctx, s, n2, ncols, n1, -1.0, T21, ldt, trans, X + r0, ldx, true, alpha, B + r0 + n1, ldb, 0);
         if (rc) return rc;
-        return trsm_left_rec(ctx, s, uplo, trans, r0 + n1, n2, ncols, 1.0, T, ldt, winv, B, ldb);
+        return trsm_left_rec(ctx, s, uplo, trans, r0 + n1, n2, ncols, 1.0, T, ldt, w, B, ldb);
     }
     // backward: X2 = inv(T22) B2 ; B1 = alpha B1 - opT12 X2 ; X1 = inv(T11) B1
-    rc = trsm_left_rec(ctx, s, uplo, trans, r0 + n1, n2, ncols, alpha, T, ldt, winv, B, ldb);
+    rc = trsm_left_rec(ctx, s, uplo, trans, r0 + n1, n2, ncols, alpha, T, ldt, w, B, ldb);
     if (rc) return rc;
     // op(T)12 (n1 x n2): Upper/NoTrans -> T(r0.., r0+n1..) M-major ; Lower/Trans -> T(r0+n1.., r0..)^T K-major
     const double* T12 = trans ? T + (r0 + n1) + (size_t)r0 * ldt : T + r0 + (size_t)(r0 + n1) * ldt;
-    rc = gemm_single(ctx, s, n1, ncols, n2, -1.0, T12, ldt, trans, B + r0 + n1, ldb, true, alpha, B + r0, ldb, 0);
+    rc = gemm_single(ctx, s, n1, ncols, n2, -1.0, T12, ldt, trans, X + r0 + n1, ldx, true, alpha, B + r0, ldb, 0);
     if (rc) return rc;
-    return trsm_left_rec(ctx, s, uplo, trans, r0, n1, ncols, 1.0, T, ldt, winv, B, ldb);
+    return trsm_left_rec(ctx, s, uplo, trans, r0, n1, ncols, 1.0, T, ldt, w, B, ldb);
+}
+
+// the 64-block recursion, in place (winv: 64 x 64 inverse blocks)
+int trsm_left_rec_entry(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int n, int ncols, double alpha,
+                        const double* T, int ldt, const double* winv, double* B, int ldb) {
+    LeftWs w{winv, IB, IB, nullptr, 0};
+    return trsm_left_rec(ctx, s, uplo, trans, 0, n, ncols, alpha, T, ldt, w, B, ldb);
+}
+// with inverse blocks of size ibs in wbig (build_inverse_blocks); xt: n x ncols scratch (ld n)
+int trsm_left_big_entry(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int n, int ncols, double alpha,
+                        const double* T, int ldt, const double* wbig, int ldw, int ibs, double* xt, double* B, int ldb) {
+    LeftWs w{wbig, ldw, ibs, xt, n};
+    int rc = trsm_left_rec(ctx, s, uplo, trans, 0, n, ncols, alpha, T, ldt, w, B, ldb);
+    if (!rc && cudaMemcpy2DAsync(B, (size_t)ldb * sizeof(double), xt, (size_t)n * sizeof(double), (size_t)n * sizeof(double), ncols,
+                                 cudaMemcpyDeviceToDevice, s) != cudaSuccess)
+        rc = -10;
+    return rc;
 }
 
 // One tile solve, Left side: B <- alpha op(T)^-1 B, T m x m triangular, B m x n.
 int trsm_left(parsec_context_s* ctx, cudaStream_t s, int uplo, int trans, int diag, int m, int n, double alpha,
               const double* T, int ldt, double* B, int ldb, double* winv) {
     if (m <= 0 || n <= 0) return 0;
+    const int ibs = ctx->cplx ? IB : solve_ibs_for(m);
+    if (ibs > IB) {
+        int rc = ensure_solve_ws(ctx, m, n);
+        double* wbig = solve_ws_big(ctx, 0);
+        if (!rc) rc = build_inverse_blocks(ctx, s, uplo, diag, m, T, ldt, winv, wbig, m, wbig + (size_t)m * m, ibs);
+        if (!rc) rc = trsm_left_big_entry(ctx, s, uplo, trans != dplasmaNoTrans, m, n, alpha, T, ldt, wbig, m, ibs, solve_ws_xt(ctx), B, ldb);
+        return rc;
+    }
     int rc = invert_diag_blocks(ctx, s, uplo, diag, m, T, ldt, winv);
     if (rc) return rc;
-    return trsm_left_rec(ctx, s, uplo, trans != dplasmaNoTrans, 0, m, n, alpha, T, ldt, winv, B, ldb);
-}
-
-int trsm_left_rec_entry(parsec_context_s* ctx, cudaStream_t s, int uplo, bool trans, int n, int ncols, double alpha,
-                        const double* T, int ldt, const double* winv, double* B, int ldb) {
-    return trsm_left_rec(ctx, s, uplo, trans, 0, n, ncols, alpha, T, ldt, winv, B, ldb);
+    return trsm_left_rec_entry(ctx, s, uplo, trans != dplasmaNoTrans, m, n, alpha, T, ldt, winv, B, ldb);
 }
 
 // dplasma_ztrsm, Left side, on staged matrices (single process).
@@ -93,11 +211,23 @@ static int trsm_left_tiled(parsec_context_s* ctx, cudaStream_t s, int uplo, int 
         const double lalpha = (kk == 0) ? alpha : 1.0;  // src/ztrsm_LLN.jdf:44
         double* winv = ctx->wInv + (size_t)(kk & 1) * ctx->wInvSlot;
         const double* Akk = A.tile(k, k);
-        rc = invert_diag_blocks(ctx, s, uplo, diag, tk, Akk, A.mb, winv);
-        if (rc) return rc;
-        for (int n = 0; n < ntr; n++) {
-            rc = trsm_left_rec(ctx, s, uplo, tr, 0, tk, B.colsOfTile(n), lalpha, Akk, A.mb, winv, B.tile(k, n), B.mb);
+        const int ibs = ctx->cplx ? IB : solve_ibs_for(tk);
+        if (ibs > IB) {
+            rc = ensure_solve_ws(ctx, A.mb, B.nb);
             if (rc) return rc;
+            double* wbig = solve_ws_big(ctx, kk & 1);
+            rc = build_inverse_blocks(ctx, s, uplo, diag, tk, Akk, A.mb, winv, wbig, A.mb, wbig + (size_t)A.mb * A.mb, ibs);
+            for (int n = 0; n < ntr && !rc; n++)
+                rc = trsm_left_big_entry(ctx, s, uplo, tr, tk, B.colsOfTile(n), lalpha, Akk, A.mb, wbig, A.mb, ibs, solve_ws_xt(ctx),
+                                         B.tile(k, n), B.mb);
+            if (rc) return rc;
+        } else {
+            rc = invert_diag_blocks(ctx, s, uplo, diag, tk, Akk, A.mb, winv);
+            if (rc) return rc;
+            for (int n = 0; n < ntr; n++) {
+                rc = trsm_left_rec_entry(ctx, s, uplo, tr, tk, B.colsOfTile(n), lalpha, Akk, A.mb, winv, B.tile(k, n), B.mb);
+                if (rc) return rc;
+            }
         }
         // B(m,:) = lalpha B(m,:) - op(A)(m,k) B(k,:) for all remaining m (src/ztrsm_LLN.jdf:131-135,
         // ztrsm_LLT.jdf:132-137): one launch per RHS tile column, batched over the tile rows m
