@@ -697,17 +697,20 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
             if (rc) break;
         }
         tmark(s);
-        // (c) solved tile row k down the grid columns.  The receive buffer of this parity was last read by the bulk
-        //     update of step kk-2.
+        // (c) solved tile row k, TRANSPOSED (nc x tk, ld = B.nb), down the grid columns: as the second operand of the
+        //     updates C(m,:) -= T(m,k) X(k,:) the transposed tile is an M-major operand (tensor-map TMA path of the
+        //     engine) where the tile itself would be a K-major one (128-byte bulk rows, measured 19 TFLOP/s).  The buffer
+        //     of this parity was last read by the bulk update of step kk-2.
         double* xrow = ctx->wSolve + (size_t)set * xSet;
-        const double* xPtr = xrow;
-        long long xStride = (long long)teB;
-        if (Tm.P == 1) { xPtr = B.tile(ilk, 0); xStride = (long long)B.lmt * teB; }
-        else if (colEndB > 0) {
-            if (kk >= 2) DPB_CUDA(cudaStreamWaitEvent(s, evBulk[set], 0));
+        if (kk >= 2) DPB_CUDA(cudaStreamWaitEvent(s, evBulk[set], 0));
+        if (Tm.prow == kp)
+            for (int jl = 0; jl < colEndB && !rc; jl++)
+                rc = launch_transpose(ctx, s, B.tile(ilk, jl), B.mb, xrow + (size_t)jl * teB, B.nb, tk, B.colsOfTile(jl * B.Q + B.pcol));
+        if (rc) break;
+        if (Tm.P > 1 && colEndB > 0) {
             group_start(ctx);
             for (int jl = 0; jl < colEndB && !rc; jl++)
-                rc = bcast(ctx, ctx->commCol, B.tile(std::min(ilk, std::max(B.lmt - 1, 0)), jl), xrow + (size_t)jl * teB, teB, kp, s);
+                rc = bcast(ctx, ctx->commCol, xrow + (size_t)jl * teB, xrow + (size_t)jl * teB, teB, kp, s);
             if (group_end(ctx)) rc = -313;
             if (rc) break;
         }
@@ -730,7 +733,7 @@ static int solve_panels_multi(parsec_context_s* ctx, cudaStream_t s, bool lower,
             int r = 0;
             for (int jl = 0; jl < colEndB && !r; jl++)
                 r = gemm_single(ctx, st, B.mb, B.colsOfTile(jl * B.Q + B.pcol), tk, -1.0, rowPtr + (size_t)a * te, Tm.mb,
-                                false, xPtr + (size_t)jl * xStride, B.mb, true, lalpha, B.tile(a, jl), B.mb, 0, b - a,
+                                false, xrow + (size_t)jl * teB, B.nb, false, lalpha, B.tile(a, jl), B.mb, 0, b - a,
                                 (long long)te, 0, (long long)teB, B.rowsOfTile(lastGm));
             return r;
         };

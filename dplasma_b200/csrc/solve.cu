@@ -205,6 +205,19 @@ static int trsm_left_tiled(parsec_context_s* ctx, cudaStream_t s, int uplo, int 
     const int mt = B.mt, ntr = B.nt;
     const bool tr = trans != dplasmaNoTrans;
     const bool forward = (uplo == dplasmaLower) != tr;
+    // one transposed solved tile (nb_rhs x mb), context-owned
+    double* xT = nullptr;
+    if (!ctx->cplx) {
+        const size_t need = (size_t)B.tileElems;
+        if (ctx->wSolveLen < need) {
+            if (ctx->wSolve) { cudaStreamSynchronize(s); cudaFree(ctx->wSolve); }
+            ctx->wSolve = nullptr;
+            ctx->wSolveLen = 0;
+            DPB_CUDA(cudaMalloc(&ctx->wSolve, need * sizeof(double)));
+            ctx->wSolveLen = need;
+        }
+        xT = ctx->wSolve;
+    }
     for (int kk = 0; kk < mt; kk++) {
         const int k = forward ? kk : mt - 1 - kk;
         const int tk = B.rowsOfTile(k);
@@ -237,7 +250,16 @@ static int trsm_left_tiled(parsec_context_s* ctx, cudaStream_t s, int uplo, int 
             const double* A0 = stored_mk ? A.tile(lo, k) : A.tile(k, lo);
             const long long sA = stored_mk ? A.tileElems : (long long)A.lmt * A.tileElems;
             for (int n = 0; n < ntr; n++) {
-                rc = gemm_single(ctx, s, B.mb, B.colsOfTile(n), tk, -1.0, A0, A.mb, !stored_mk, B.tile(k, n), B.mb, true,
+                // the solved tile as an M-major operand: its transpose (nc x tk, ld = B.nb); see solve_panels_multi
+                const double* Xn = B.tile(k, n);
+                int ldx = B.mb;
+                bool xK = true;
+                if (!ctx->cplx && xT) {
+                    rc = launch_transpose(ctx, s, B.tile(k, n), B.mb, xT, B.nb, tk, B.colsOfTile(n));
+                    if (rc) return rc;
+                    Xn = xT; ldx = B.nb; xK = false;
+                }
+                rc = gemm_single(ctx, s, B.mb, B.colsOfTile(n), tk, -1.0, A0, A.mb, !stored_mk, Xn, ldx, xK,
                                  lalpha, B.tile(lo, n), B.mb, 0, hi - lo, sA, 0, B.tileElems, B.rowsOfTile(hi - 1));
                 if (rc) return rc;
             }
