@@ -81,6 +81,9 @@ class Lib:
         proto("dplasma_b200_rank_of", i, [pBC, i, i])
         proto("dplasma_b200_panel_plan", i, [pBC, i, i, C.POINTER(i), C.POINTER(i), C.POINTER(i)])
         proto("dplasma_b200_rowpanel_plan", i, [pBC, i, C.POINTER(i), C.POINTER(i), C.POINTER(i)])
+        proto("dplasma_b200_transpose_cap", C.c_longlong, [i, C.c_longlong])
+        proto("dplasma_b200_transpose_plan", i, [i, i, i, i, C.c_longlong, i, i, C.POINTER(i), C.POINTER(i), i, C.POINTER(i),
+                                                 C.POINTER(i), i, C.POINTER(i)])
         proto("dplasma_dpotrf_New", vp, [i, pBC, C.POINTER(i)])
         proto("dplasma_dpotrf_Destruct", None, [vp])
         proto("dplasma_dpotrf_Destroy", None, [vp])

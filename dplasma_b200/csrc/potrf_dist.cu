@@ -467,19 +467,78 @@ void swap_grid_comms(parsec_context_s* ctx) {
     std::swap(ctx->gridIp, ctx->gridJq);
 }
 
+// ---- plan of the distributed transposition: host arithmetic, shared by dist_transpose_tri below and by
+//      dplasma_b200_transpose_plan (exercised over gloo on the CPU, tests/test_dist_gloo.py) ----
+struct XposeTile { int m, n, peer; };  // tile (m, n) of T; peer: logical rank it goes to (send list) / comes from (receive list)
+struct XposePlan {
+    int P, Q, mt;
+    bool lower;
+    size_t cap;  // per round: at most `cap` outgoing and `cap` incoming tiles per rank
+    void rows_of(int n, int* m0, int* m1) const {
+        *m0 = lower ? n : 0;
+        *m1 = lower ? mt : n + 1;
+    }
+    static size_t cap_for(int mt, size_t tileBytes) {  // 1 GB each way, at least one full tile column, at most the triangle
+        return std::max<size_t>((size_t)mt + 1, std::min<size_t>(((size_t)1 << 30) / std::max<size_t>(tileBytes, 1),
+                                                                 (size_t)mt * (mt + 1) / 2));
+    }
+    // The columns [nA, nB) of the round that starts at nA: the same on every rank (bounds on what any rank sends or
+    // receives: column n is sent by grid column n % Q, at most ceil(len / P) tiles per rank, and received by grid row
+    // n % P, at most ceil(len / Q) tiles per rank).
+    int round_end(int nA) const {
+        std::vector<size_t> outQ(Q, 0), inP(P, 0);
+        int nB = nA;
+        while (nB < mt) {
+            int m0, m1;
+            rows_of(nB, &m0, &m1);
+            const size_t o = (size_t)(m1 - m0 + P - 1) / P, i = (size_t)(m1 - m0 + Q - 1) / Q;
+            if (nB > nA && (outQ[nB % Q] + o > cap || inP[nB % P] + i > cap)) break;
+            outQ[nB % Q] += o; inP[nB % P] += i; nB++;
+        }
+        return nB;
+    }
+    // Both ends of a pair walk the tiles in the same order: column n ascending, row m ascending.
+    // my tiles of the round, with where they go (peer == me: the tile stays)
+    void send_list(int me, int nA, int nB, std::vector<XposeTile>* out) const {
+        out->clear();
+        const int prow = me / Q, pcol = me % Q;
+        for (int n = nA; n < nB; n++) {
+            if (n % Q != pcol) continue;
+            int m0, m1;
+            rows_of(n, &m0, &m1);
+            for (int m = m0; m < m1; m++)
+                if (m % P == prow) out->push_back({m, n, (n % P) * Q + (m % Q)});
+        }
+    }
+    // the tiles that reach me from another rank
+    void recv_list(int me, int nA, int nB, std::vector<XposeTile>* out) const {
+        out->clear();
+        const int prow = me / Q, pcol = me % Q;
+        for (int n = nA; n < nB; n++) {
+            if (n % P != prow) continue;
+            int m0, m1;
+            rows_of(n, &m0, &m1);
+            for (int m = m0; m < m1; m++) {
+                if (m % Q != pcol) continue;
+                const int src = (m % P) * Q + (n % Q);
+                if (src != me) out->push_back({m, n, src});
+            }
+        }
+    }
+};
+
 // Tt <- T^T on the same grid (the `uplo` triangle of T; tile (m, n) goes, transposed, to tile (n, m) on process
 // (n % P, m % Q)).  An all-to-all in rounds over blocks of tile columns: every rank transposes its outgoing tiles
 // straight into a send staging area, packed by destination, ONE send and ONE receive per peer move the round's tiles
-// (all pairs of the grid at the same time, large messages), and the received tiles are copied into place.  Both ends
-// of a pair walk the tiles in the same order (column n ascending, row m ascending).  The staging is context-owned.
+// (all pairs of the grid at the same time, large messages), and the received tiles are copied into place.  The staging
+// is context-owned.
 int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T, int uplo, const DevMatrix& Tt) {
     if (T.mb != T.nb || T.mt != T.nt) return -320;
     if (T.esz != 1) return -2;  // real tiles only
     const size_t te = (size_t)T.tileElems;
     const int P = T.P, Q = T.Q, np = P * Q, me = T.prow * Q + T.pcol;
-    // per round: at most `cap` outgoing and `cap` incoming tiles (1 GB each way, at least one full tile column)
-    const size_t cap = std::max<size_t>((size_t)T.mt + 1, std::min<size_t>(((size_t)1 << 30) / (te * sizeof(double)),
-                                                                           (size_t)T.mt * (T.mt + 1) / 2));
+    XposePlan plan{P, Q, T.mt, uplo == dplasmaLower, XposePlan::cap_for(T.mt, te * sizeof(double))};
+    const size_t cap = plan.cap;
     if (ctx->wXposeLen < 2 * cap * te) {
         if (ctx->wXpose) { cudaStreamSynchronize(s); cudaFree(ctx->wXpose); }
         ctx->wXpose = nullptr;
@@ -489,60 +548,34 @@ int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T
     }
     double* sendBuf = ctx->wXpose;
     double* recvBuf = ctx->wXpose + cap * te;
-    auto rows_of = [&](int n, int* m0, int* m1) {
-        *m0 = (uplo == dplasmaLower) ? n : 0;
-        *m1 = (uplo == dplasmaLower) ? T.mt : n + 1;
-    };
-    std::vector<size_t> sendCnt(np), recvCnt(np), sendOff(np), recvOff(np), sendIdx(np), recvIdx(np), outQ(Q), inP(P);
+    std::vector<size_t> sendCnt(np), recvCnt(np), sendOff(np), recvOff(np), sendIdx(np), recvIdx(np);
+    std::vector<XposeTile> sends, recvs;
     int rc = 0;
     for (int nA = 0; nA < T.nt && !rc;) {
-        // ---- the columns of this round: the same on every rank (bounds on what any rank sends or receives:
-        //      column n is sent by grid column n % Q, at most ceil(len / P) tiles per rank, and received by grid row
-        //      n % P, at most ceil(len / Q) tiles per rank) ----
-        int nB = nA;
-        std::fill(outQ.begin(), outQ.end(), 0);
-        std::fill(inP.begin(), inP.end(), 0);
-        while (nB < T.nt) {
-            int m0, m1;
-            rows_of(nB, &m0, &m1);
-            const size_t o = (size_t)(m1 - m0 + P - 1) / P, i = (size_t)(m1 - m0 + Q - 1) / Q;
-            if (nB > nA && (outQ[nB % Q] + o > cap || inP[nB % P] + i > cap)) break;
-            outQ[nB % Q] += o; inP[nB % P] += i; nB++;
-        }
+        const int nB = plan.round_end(nA);
+        plan.send_list(me, nA, nB, &sends);
+        plan.recv_list(me, nA, nB, &recvs);
         std::fill(sendCnt.begin(), sendCnt.end(), 0);
         std::fill(recvCnt.begin(), recvCnt.end(), 0);
-        for (int n = nA; n < nB; n++) {
-            int m0, m1;
-            rows_of(n, &m0, &m1);
-            for (int m = m0; m < m1; m++) {
-                const int src = (m % P) * Q + (n % Q), dst = (n % P) * Q + (m % Q);
-                if (src == me && dst != me) sendCnt[dst]++;
-                if (dst == me && src != me) recvCnt[src]++;
-            }
-        }
+        for (const XposeTile& t : sends)
+            if (t.peer != me) sendCnt[t.peer]++;
+        for (const XposeTile& t : recvs) recvCnt[t.peer]++;
         size_t so = 0, ro = 0;
         for (int r = 0; r < np; r++) {
             sendOff[r] = so; so += sendCnt[r];
             recvOff[r] = ro; ro += recvCnt[r];
             sendIdx[r] = recvIdx[r] = 0;
         }
+        if (so > cap || ro > cap) return -323;  // the bounds of round_end do not hold: a bug, not a size limit
         // ---- pack: my tiles, transposed, by destination; tiles that stay go straight into place ----
-        for (int n = nA; n < nB && !rc; n++) {
-            if (n % Q != T.pcol) continue;
-            int m0, m1;
-            rows_of(n, &m0, &m1);
-            for (int m = m0; m < m1 && !rc; m++) {
-                if (m % P != T.prow) continue;
-                const int dst = (n % P) * Q + (m % Q);
-                double* to = (dst == me) ? Tt.tile(n / P, m / Q) : sendBuf + (sendOff[dst] + sendIdx[dst]++) * te;
-                rc = launch_transpose(ctx, s, T.tile(m / P, n / Q), T.mb, to, T.mb, T.mb, T.nb);
-            }
+        for (size_t q = 0; q < sends.size() && !rc; q++) {
+            const XposeTile& t = sends[q];
+            double* to = (t.peer == me) ? Tt.tile(t.n / P, t.m / Q) : sendBuf + (sendOff[t.peer] + sendIdx[t.peer]++) * te;
+            rc = launch_transpose(ctx, s, T.tile(t.m / P, t.n / Q), T.mb, to, T.mb, T.mb, T.nb);
         }
         if (rc) break;
         // ---- exchange: one message per peer and direction ----
-        bool any = false;
-        for (int r = 0; r < np; r++) any = any || sendCnt[r] || recvCnt[r];
-        if (any) {
+        if (so || ro) {
             group_start(ctx);
             for (int r = 0; r < np && !rc; r++) {
                 if (r == me) continue;
@@ -553,18 +586,11 @@ int dist_transpose_tri(parsec_context_s* ctx, cudaStream_t s, const DevMatrix& T
             if (group_end(ctx) && !rc) rc = -321;
         }
         // ---- unpack: received tiles into place, in the order their sender packed them ----
-        for (int n = nA; n < nB && !rc; n++) {
-            if (n % P != T.prow) continue;
-            int m0, m1;
-            rows_of(n, &m0, &m1);
-            for (int m = m0; m < m1 && !rc; m++) {
-                if (m % Q != T.pcol) continue;
-                const int src = (m % P) * Q + (n % Q);
-                if (src == me) continue;
-                if (cudaMemcpyAsync(Tt.tile(n / P, m / Q), recvBuf + (recvOff[src] + recvIdx[src]++) * te, te * sizeof(double),
-                                    cudaMemcpyDeviceToDevice, s) != cudaSuccess)
-                    rc = -322;
-            }
+        for (size_t q = 0; q < recvs.size() && !rc; q++) {
+            const XposeTile& t = recvs[q];
+            if (cudaMemcpyAsync(Tt.tile(t.n / P, t.m / Q), recvBuf + (recvOff[t.peer] + recvIdx[t.peer]++) * te, te * sizeof(double),
+                                cudaMemcpyDeviceToDevice, s) != cudaSuccess)
+                rc = -322;
         }
         nA = nB;
     }
@@ -886,6 +912,28 @@ int symm_residual_multi(parsec_context_s* ctx, cudaStream_t s, int uplo, const D
 
 // Host-only view of the plan, for tests of the multi-rank logic without GPUs.
 // out[0..5] = kq, kp, il0, nrows, jl0, ncols ; colRoot / colSrcIl must hold lnt ints.
+// The plan of one round of the distributed transposition (dist_transpose_tri) for logical rank `me` of a P x Q grid:
+// *nB = end of the round that starts at tile column nA; sendTiles / recvTiles = (m, n, peer) triples in the order the
+// tiles are packed / unpacked (send list: peer == me for tiles that stay).  Returns 0, or -1 when a list is too short.
+extern "C" long long dplasma_b200_transpose_cap(int mt, long long tileBytes) {
+    return (long long)dpb::XposePlan::cap_for(mt, (size_t)tileBytes);
+}
+extern "C" int dplasma_b200_transpose_plan(int P, int Q, int mt, int uplo, long long cap, int me, int nA, int* nB,
+                                           int* sendTiles, int maxSend, int* nSend, int* recvTiles, int maxRecv, int* nRecv) {
+    if (P < 1 || Q < 1 || mt < 0 || me < 0 || me >= P * Q || nA < 0 || nA > mt || cap < 1 || !nB || !nSend || !nRecv) return -2;
+    dpb::XposePlan plan{P, Q, mt, uplo == dplasmaLower, (size_t)cap};
+    *nB = plan.round_end(nA);
+    std::vector<dpb::XposeTile> sends, recvs;
+    plan.send_list(me, nA, *nB, &sends);
+    plan.recv_list(me, nA, *nB, &recvs);
+    *nSend = (int)sends.size();
+    *nRecv = (int)recvs.size();
+    if ((int)sends.size() > maxSend || (int)recvs.size() > maxRecv) return -1;
+    for (size_t q = 0; q < sends.size(); q++) { sendTiles[3 * q] = sends[q].m; sendTiles[3 * q + 1] = sends[q].n; sendTiles[3 * q + 2] = sends[q].peer; }
+    for (size_t q = 0; q < recvs.size(); q++) { recvTiles[3 * q] = recvs[q].m; recvTiles[3 * q + 1] = recvs[q].n; recvTiles[3 * q + 2] = recvs[q].peer; }
+    return 0;
+}
+
 extern "C" int dplasma_b200_panel_plan(const parsec_tiled_matrix_t* A, int k, int gmFirst, int* out, int* colRoot,
                                        int* colSrcIl) {
     using namespace dpb;

@@ -141,6 +141,15 @@ int dplasma_b200_panel_plan(const parsec_tiled_matrix_t *A, int k, int gmFirst, 
  * down the grid columns, and m / Q, its local column index there (the root and source of the broadcast along the
  * grid row that the products A(m,n) += A(k,m)^T A(k,n) need).  Host arithmetic only. */
 int dplasma_b200_rowpanel_plan(const parsec_tiled_matrix_t *A, int k, int *out, int *rowRootCol, int *rowSrcJl);
+/* One round of the distributed transposition behind the transposed solves on a grid (the explicit form of the
+ * A(n,k)^T dependencies of src/ztrsm_LLT.jdf:132-137): for logical rank `me` of a P x Q grid and the round that starts
+ * at tile column nA of an mt x mt tile matrix (triangle `uplo`), *nB = first column after the round, and the (m, n, peer)
+ * triples of the tiles it packs for each destination / unpacks from each source, in order (send list: peer == me for a
+ * tile that stays on its rank).  cap = tiles a rank may send or receive per round (dplasma_b200_transpose_cap: 1 GB each
+ * way).  Host arithmetic only; returns 0, -1 when a list is too short (counts are still set), -2 on bad arguments. */
+long long dplasma_b200_transpose_cap(int mt, long long tileBytes);
+int dplasma_b200_transpose_plan(int P, int Q, int mt, int uplo, long long cap, int me, int nA, int *nB,
+                                int *sendTiles, int maxSend, int *nSend, int *recvTiles, int maxRecv, int *nRecv);
 /* rank owning global tile (m,n): the data collection's rank_of (src/zpotrf_L.jdf:105) */
 int dplasma_b200_rank_of(const parsec_tiled_matrix_t *A, int m, int n);
 

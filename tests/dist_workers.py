@@ -713,3 +713,83 @@ def nccl_blas3_worker(rank, world, port, P, Q, N, K, nb, q):
         ctx.close()
     finally:
         dist.destroy_process_group()
+
+
+def gloo_transpose_worker(rank, world, port, P, Q, N, nb, uplo_name, cap, q):
+    """CPU: the distributed transposition behind the transposed grid solves (dist_transpose_tri), driven by the
+    library's own round plan (dplasma_b200_transpose_plan): tiles packed by destination in plan order, one message per
+    peer and direction and round over gloo, unpacked in plan order; result == the transpose's own block-cyclic tiles."""
+    import ctypes as C
+    import torch
+    import dplasma_b200 as dp
+    dist = _init(rank, world, port, "gloo")
+    try:
+        lib = dp.load()
+        uplo = dp.Lower if uplo_name == "L" else dp.Upper
+        mt = (N + nb - 1) // nb
+        rng = np.random.default_rng(1234)
+        F = rng.standard_normal((N, N))
+        prow, pcol = rank // Q, rank % Q
+
+        def tile(Mx, m, n):
+            t = np.zeros((nb, nb))
+            blk = Mx[m * nb:(m + 1) * nb, n * nb:(n + 1) * nb]
+            t[:blk.shape[0], :blk.shape[1]] = blk
+            return t
+        in_tri = (lambda m, n: m >= n) if uplo == dp.Lower else (lambda m, n: m <= n)
+        mine = {(m, n): tile(F, m, n) for m in range(mt) for n in range(mt)
+                if in_tri(m, n) and m % P == prow and n % Q == pcol}
+        if cap <= 0:
+            cap = lib.dplasma_b200_transpose_cap(mt, nb * nb * 8)
+        got = {}
+        nA, rounds, max_out, max_in = 0, 0, 0, 0
+        IntArr = C.c_int * (3 * mt * mt + 3)
+        while nA < mt:
+            nB, ns, nr = C.c_int(0), C.c_int(0), C.c_int(0)
+            sl, rl = IntArr(), IntArr()
+            rc = lib.dplasma_b200_transpose_plan(P, Q, mt, uplo, cap, rank, nA, C.byref(nB), sl, mt * mt + 1, C.byref(ns),
+                                                 rl, mt * mt + 1, C.byref(nr))
+            assert rc == 0 and nB.value > nA, (rc, nA, nB.value)
+            sends = [(sl[3 * i], sl[3 * i + 1], sl[3 * i + 2]) for i in range(ns.value)]
+            recvs = [(rl[3 * i], rl[3 * i + 1], rl[3 * i + 2]) for i in range(nr.value)]
+            packed = {}
+            for m, n, dst in sends:
+                assert nA <= n < nB.value and (m, n) in mine, (m, n)
+                if dst == rank:
+                    got[(n, m)] = mine[(m, n)].T.copy()
+                else:
+                    packed.setdefault(dst, []).append(mine[(m, n)].T.copy())
+            incoming = {}
+            for m, n, src in recvs:
+                assert src != rank
+                incoming[src] = incoming.get(src, 0) + 1
+            max_out = max(max_out, sum(len(v) for v in packed.values()))
+            max_in = max(max_in, sum(incoming.values()))
+            reqs, bufs = [], {}
+            for r in range(world):
+                if r == rank:
+                    continue
+                if r in packed:
+                    reqs.append(dist.isend(torch.from_numpy(np.stack(packed[r])), dst=r))
+                if r in incoming:
+                    bufs[r] = torch.empty((incoming[r], nb, nb), dtype=torch.float64)
+                    reqs.append(dist.irecv(bufs[r], src=r))
+            for rq in reqs:
+                rq.wait()
+            idx = {}
+            for m, n, src in recvs:
+                k = idx.get(src, 0)
+                idx[src] = k + 1
+                got[(n, m)] = bufs[src][k].numpy().copy()
+            nA = nB.value
+            rounds += 1
+        # what I must hold now: the tiles of F^T in the opposite triangle that the distribution gives me
+        Ft = F.T
+        want = {(a, b) for a in range(mt) for b in range(mt) if in_tri(b, a) and a % P == prow and b % Q == pcol}
+        err = 0.0
+        ok = set(got) == want
+        for (a, b) in want & set(got):
+            err = max(err, float(np.abs(got[(a, b)] - tile(Ft, a, b)).max()))
+        q.put((rank, ok, err, rounds, max_out, max_in, int(cap)))
+    finally:
+        dist.destroy_process_group()

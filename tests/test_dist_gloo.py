@@ -86,3 +86,28 @@ def test_distributed_gemm_syrk_plan_over_gloo(P, Q, M, N, K, nb):
         assert p.exitcode == 0
     for rank, err_gemm, err_syrk in res:
         assert err_gemm < 1e-12 and err_syrk < 1e-12, (rank, err_gemm, err_syrk)
+
+
+@pytest.mark.parametrize("P,Q,N,nb,uplo,cap", [(1, 2, 200, 32, "L", 0), (2, 1, 200, 32, "U", 0), (2, 2, 232, 24, "L", 11),
+                                               (2, 3, 250, 24, "U", 12), (2, 2, 232, 24, "U", 0)])
+def test_distributed_transposition_plan_over_gloo(P, Q, N, nb, uplo, cap):
+    """the all-to-all in rounds behind the transposed solves on a grid (csrc/potrf_dist.cu: dist_transpose_tri) with the
+    library's own round plan; cap > 0 forces several rounds"""
+    import torch.multiprocessing as mp
+    from tests.dist_workers import gloo_transpose_worker
+    world = P * Q
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=gloo_transpose_worker, args=(r, world, port, P, Q, N, nb, uplo, cap, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, ok, err, rounds, max_out, max_in, used_cap in res:
+        assert ok and err == 0.0, (rank, ok, err)
+        assert max_out <= used_cap and max_in <= used_cap, (rank, max_out, max_in, used_cap)
+        if cap:
+            assert rounds > 1
